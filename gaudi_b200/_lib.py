@@ -1,0 +1,72 @@
+"""ctypes binding of libgaudimm_b200.so (the C ABI declared in include/gaudimm_b200.h).
+
+There is no CPU fallback: if the shared library has not been built (``python -c "import
+__graft_entry__ as g; g.build()"``) importing this module's ``lib()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgaudimm_b200.so")
+
+GMM_OK, GMM_EINVAL, GMM_ECUDA, GMM_ESTATE, GMM_ELIMIT = 0, -1, -2, -3, -4
+OPT_ONLY_INTERNAL, OPT_NO_CULL = 1, 2
+MAX_MOBILE_ATOMS, MAX_TORSIONS = 1024, 1024
+
+_vp, _i, _d = C.c_void_p, C.c_int, C.c_double
+
+# name -> (restype, argtypes); must list every symbol of include/gaudimm_b200.h
+SIGNATURES = {
+    "gmm_create": (_i, [C.POINTER(_vp), _i]),
+    "gmm_destroy": (_i, [_vp]),
+    "gmm_last_error": (C.c_char_p, []),
+    "gmm_version": (_i, []),
+    "gmm_reserve": (_i, [_vp, _i]),
+    "gmm_set_mobile": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i]),
+    "gmm_set_rotamers": (_i, [_vp, _i, _vp, _vp]),
+    "gmm_set_receptor": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_set_params": (_i, [_vp, _d, _d, _d, _d, _d, _d, _d, _i]),
+    "gmm_express": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_contacts": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
+    "gmm_evaluate": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_evaluate_host": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),
+    "gmm_contacts_pairs": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, C.POINTER(_i), _vp]),
+    "gmm_measure_fp32_peak": (_i, [_i, C.POINTER(_d)]),
+    "gmm_last_pair_tests": (_i, [_vp, C.POINTER(C.c_ulonglong)]),
+    "gmm_launch_count": (C.c_ulonglong, []),
+}
+
+_lib = None
+
+
+class GmmError(RuntimeError):
+    def __init__(self, code, message):
+        RuntimeError.__init__(self, "libgaudimm_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+def lib():
+    """The loaded library (loads on first use; raises if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                "%s not found: the CUDA extension has not been built and gaudi_b200 has no "
+                "CPU fallback. Run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "from the repository root." % LIB_PATH)
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(code):
+    if code != GMM_OK:
+        raise GmmError(code, lib().gmm_last_error().decode("utf-8", "replace"))
+    return code

@@ -1,0 +1,514 @@
+// C ABI of libgaudimm_b200 (see include/gaudimm_b200.h): context management, upload of the
+// static model (with the host-side re-ordering the kernels rely on) and the batched entry
+// points.  No arithmetic of the hot path runs on the host.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+
+#include "common.cuh"
+
+namespace gmm {
+
+static thread_local char g_err[512] = "";
+unsigned long long g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+template <typename T>
+static int upload(T** dst, const T* src, size_t n) {
+    if (*dst) { cudaFree(*dst); *dst = nullptr; }
+    if (n == 0) return GMM_OK;
+    GMM_CUDA(cudaMalloc((void**)dst, n * sizeof(T)));
+    GMM_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    return GMM_OK;
+}
+
+template <typename T>
+static void release(T*& p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+int ensure_scratch(gmm_ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return GMM_OK;
+    if (c->d_scratch) { GMM_CUDA(cudaDeviceSynchronize()); cudaFree(c->d_scratch); c->d_scratch = nullptr; }
+    c->scratch_bytes = 0;
+    GMM_CUDA(cudaMalloc(&c->d_scratch, bytes));
+    c->scratch_bytes = bytes;
+    return GMM_OK;
+}
+
+static inline uint32_t spread10(uint32_t v) {
+    v &= 0x3ff;
+    v = (v | (v << 16)) & 0x030000ff;
+    v = (v | (v << 8)) & 0x0300f00f;
+    v = (v | (v << 4)) & 0x030c30c3;
+    v = (v | (v << 2)) & 0x09249249;
+    return v;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace gmm
+
+using namespace gmm;
+
+#define REQUIRE(cond, code, ...)              \
+    do {                                      \
+        if (!(cond)) {                        \
+            gmm::set_error(__VA_ARGS__);      \
+            return code;                      \
+        }                                     \
+    } while (0)
+
+extern "C" {
+
+const char* gmm_last_error(void) { return gmm::g_err; }
+int gmm_version(void) { return 100; }
+unsigned long long gmm_launch_count(void) { return gmm::g_launches; }
+
+int gmm_create(gmm_ctx** out, int device) {
+    REQUIRE(out != nullptr, GMM_EINVAL, "gmm_create: out is NULL");
+    int n = 0;
+    GMM_CUDA(cudaGetDeviceCount(&n));
+    REQUIRE(device >= 0 && device < n, GMM_EINVAL, "gmm_create: device %d not in [0,%d)", device, n);
+    DeviceGuard g(device);
+    gmm_ctx* c = new gmm_ctx();
+    c->device = device;
+    if (cudaMalloc((void**)&c->d_counters, 4 * sizeof(unsigned long long)) != cudaSuccess) {
+        set_error("gmm_create: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+        delete c;
+        return GMM_ECUDA;
+    }
+    cudaMemset(c->d_counters, 0, 4 * sizeof(unsigned long long));
+    *out = c;
+    return GMM_OK;
+}
+
+int gmm_destroy(gmm_ctx* c) {
+    if (!c) return GMM_OK;
+    DeviceGuard g(c->device);
+    cudaDeviceSynchronize();
+    release(c->d_xyz0); release(c->d_mflags_atom); release(c->d_tfixed); release(c->d_tmoving);
+    release(c->d_tsrc); release(c->d_tsnap); release(c->d_tmask); release(c->d_slot2atom);
+    release(c->d_mrad_slot); release(c->d_mflags_slot); release(c->d_mm_pairs);
+    release(c->d_rot_ptr); release(c->d_rot_delta);
+    release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
+    release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
+    release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx);
+    release(c->d_counters);
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    if (c->d_stage) cudaFree(c->d_stage);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    delete c;
+    return GMM_OK;
+}
+
+int gmm_set_params(gmm_ctx* c, double zone_radius, double clash_threshold, double hydrophobic_threshold,
+                   double hbond_allowance, double assumed_max_vdw, double cutoff, double weight, int options) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_params: ctx is NULL");
+    REQUIRE(zone_radius >= 0.0, GMM_EINVAL, "gmm_set_params: radius must be >= 0 (contacts.py:90)");
+    REQUIRE(!c->has_receptor, GMM_ESTATE,
+            "gmm_set_params: parameters are baked into the receptor's static pair values; "
+            "create a new context (or call before gmm_set_receptor)");
+    c->prm.zone_radius = zone_radius; c->prm.clash_thr = clash_threshold;
+    c->prm.hydro_thr = hydrophobic_threshold; c->prm.hb_allow = hbond_allowance;
+    c->prm.amv = assumed_max_vdw; c->prm.cutoff = cutoff; c->prm.weight = weight;
+    c->prm.options = options;
+    c->has_params = true;
+    return GMM_OK;
+}
+
+int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_h, const uint8_t* flags_h,
+                   int T, const int32_t* tors_fixed_h, const int32_t* tors_moving_h,
+                   const uint64_t* tors_mask_h, const uint8_t* tors_snap_h, const int32_t* tors_src_h,
+                   const uint64_t* excl_mask_h, int origin_atom, int torsion_before_search) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_mobile: ctx is NULL");
+    REQUIRE(M >= 1 && M <= GMM_MAX_MOBILE_ATOMS, GMM_ELIMIT, "gmm_set_mobile: M=%d outside [1,%d]", M, GMM_MAX_MOBILE_ATOMS);
+    REQUIRE(T >= 0 && T <= GMM_MAX_TORSIONS, GMM_ELIMIT, "gmm_set_mobile: T=%d outside [0,%d]", T, GMM_MAX_TORSIONS);
+    REQUIRE(xyz0_h && radius_h && flags_h && excl_mask_h, GMM_EINVAL, "gmm_set_mobile: NULL array");
+    REQUIRE(T == 0 || (tors_fixed_h && tors_moving_h && tors_mask_h && tors_snap_h && tors_src_h), GMM_EINVAL,
+            "gmm_set_mobile: NULL torsion array");
+    REQUIRE(origin_atom >= 0 && origin_atom < M, GMM_EINVAL, "gmm_set_mobile: origin_atom out of range");
+    REQUIRE(!c->has_receptor, GMM_ESTATE, "gmm_set_mobile: set the mobile model before the receptor");
+    DeviceGuard g(c->device);
+    const int W = (M + 63) / 64;
+    int n_allele = 0;
+    for (int t = 0; t < T; ++t) {
+        REQUIRE(tors_fixed_h[t] >= 0 && tors_fixed_h[t] < M && tors_moving_h[t] >= 0 && tors_moving_h[t] < M,
+                GMM_EINVAL, "gmm_set_mobile: torsion %d references an atom out of range", t);
+        if (tors_src_h[t] >= 0) n_allele = std::max(n_allele, tors_src_h[t] + 1);
+    }
+    c->M = M; c->T = T; c->W = W; c->n_allele_tors = n_allele;
+    c->origin_atom = origin_atom; c->tors_before_search = torsion_before_search ? 1 : 0;
+    int rc;
+    if ((rc = upload(&c->d_xyz0, xyz0_h, (size_t)M * 3))) return rc;
+    if ((rc = upload(&c->d_mflags_atom, flags_h, (size_t)M))) return rc;
+    if ((rc = upload(&c->d_tfixed, tors_fixed_h, (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tmoving, tors_moving_h, (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tsrc, tors_src_h, (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tsnap, tors_snap_h, (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tmask, tors_mask_h, (size_t)T * W))) return rc;
+
+    // slot order for the Contacts kernels: zone seeds first (their min-distance decides zone
+    // membership of receptor atoms), the other mobile atoms after; padded to an even count.
+    std::vector<int32_t> order(M);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_partition(order.begin(), order.end(), [&](int i) { return (flags_h[i] & GMM_F_SEED) != 0; });
+    int n_seed = 0;
+    for (int i = 0; i < M; ++i) n_seed += (flags_h[i] & GMM_F_SEED) ? 1 : 0;
+    const int Mp = (M + 1) & ~1;
+    c->Mp = Mp; c->n_seed = n_seed; c->all_seed = (n_seed == M);
+    c->h_slot2atom.assign(Mp, -1);
+    c->h_atom2slot.assign(M, -1);
+    std::vector<float> rad(Mp, 0.f);
+    std::vector<uint8_t> fl(Mp, 0);
+    float rmax = 0.f;
+    for (int s = 0; s < M; ++s) {
+        const int a = order[s];
+        c->h_slot2atom[s] = a; c->h_atom2slot[a] = s;
+        rad[s] = radius_h[a]; fl[s] = flags_h[a];
+        rmax = std::max(rmax, radius_h[a]);
+    }
+    c->rmax_mobile = rmax;
+    c->h_mrad = rad;
+    if ((rc = upload(&c->d_slot2atom, c->h_slot2atom.data(), (size_t)Mp))) return rc;
+    if ((rc = upload(&c->d_mrad_slot, rad.data(), (size_t)Mp))) return rc;
+    if ((rc = upload(&c->d_mflags_slot, fl.data(), (size_t)Mp))) return rc;
+    // intra-mobile pairs more than bond_separation bonds apart, in slot indices
+    std::vector<uint32_t> mm;
+    for (int a = 0; a < M; ++a)
+        for (int b = a + 1; b < M; ++b) {
+            const bool excl = (excl_mask_h[(size_t)a * W + (b >> 6)] >> (b & 63)) & 1ull;
+            if (!excl) mm.push_back((uint32_t)c->h_atom2slot[a] | ((uint32_t)c->h_atom2slot[b] << 16));
+        }
+    c->n_mm = (int)mm.size();
+    if ((rc = upload(&c->d_mm_pairs, mm.data(), mm.size()))) return rc;
+    c->has_mobile = true;
+    return GMM_OK;
+}
+
+int gmm_set_rotamers(gmm_ctx* c, int n_res, const int32_t* rot_ptr_h, const double* rot_delta_h) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_rotamers: ctx is NULL");
+    REQUIRE(n_res >= 0, GMM_EINVAL, "gmm_set_rotamers: n_res < 0");
+    DeviceGuard g(c->device);
+    c->n_res = n_res;
+    if (n_res == 0) { release(c->d_rot_ptr); release(c->d_rot_delta); return GMM_OK; }
+    REQUIRE(rot_ptr_h && rot_delta_h, GMM_EINVAL, "gmm_set_rotamers: NULL array");
+    for (int r = 0; r < n_res; ++r)
+        REQUIRE(rot_ptr_h[r + 1] > rot_ptr_h[r], GMM_EINVAL, "gmm_set_rotamers: residue %d has no rotamers", r);
+    int rc;
+    if ((rc = upload(&c->d_rot_ptr, rot_ptr_h, (size_t)n_res + 1))) return rc;
+    if ((rc = upload(&c->d_rot_delta, rot_delta_h, (size_t)rot_ptr_h[n_res] * 4))) return rc;
+    return GMM_OK;
+}
+
+int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius_h, const uint8_t* flags_h,
+                     const int32_t* rr_ptr_h, const int32_t* rr_idx_h, const int32_t* ms_ptr_h,
+                     const int32_t* ms_idx_h, const double* centre_h) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_receptor: ctx is NULL");
+    REQUIRE(c->has_params, GMM_ESTATE, "gmm_set_receptor: call gmm_set_params first");
+    REQUIRE(c->has_mobile, GMM_ESTATE, "gmm_set_receptor: call gmm_set_mobile first");
+    REQUIRE(R >= 0 && R < (1 << 24), GMM_ELIMIT, "gmm_set_receptor: R=%d outside [0,2^24)", R);
+    REQUIRE(centre_h, GMM_EINVAL, "gmm_set_receptor: centre is NULL");
+    REQUIRE(R == 0 || (xyz_h && radius_h && flags_h), GMM_EINVAL, "gmm_set_receptor: NULL array");
+    DeviceGuard g(c->device);
+    for (int k = 0; k < 3; ++k) c->centre[k] = centre_h[k];
+    c->R = R;
+    c->n_tiles = (R + kTileAtoms - 1) / kTileAtoms;
+    c->Rpad = c->n_tiles * kTileAtoms;
+
+    // Morton order of the device-frame coordinates -> spatially compact 128-atom tiles
+    std::vector<float> fx((size_t)R * 3);
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+    for (int i = 0; i < R; ++i)
+        for (int k = 0; k < 3; ++k) {
+            const float v = (float)(xyz_h[(size_t)i * 3 + k] - centre_h[k]);
+            fx[(size_t)i * 3 + k] = v;
+            lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v);
+        }
+    float span = 1e-6f;
+    for (int k = 0; k < 3; ++k) span = std::max(span, hi[k] - lo[k]);
+    std::vector<uint32_t> code(R);
+    for (int i = 0; i < R; ++i) {
+        uint32_t q[3];
+        for (int k = 0; k < 3; ++k) {
+            float t = (fx[(size_t)i * 3 + k] - lo[k]) / span * 1023.f;
+            q[k] = (uint32_t)std::min(1023.f, std::max(0.f, t));
+        }
+        code[i] = spread10(q[0]) | (spread10(q[1]) << 1) | (spread10(q[2]) << 2);
+    }
+    std::vector<int32_t> s2o(R);
+    std::iota(s2o.begin(), s2o.end(), 0);
+    std::stable_sort(s2o.begin(), s2o.end(), [&](int a, int b) { return code[a] < code[b]; });
+    std::vector<int32_t> o2s(R);
+    for (int s = 0; s < R; ++s) o2s[s2o[s]] = s;
+    c->h_sorted2orig = s2o;
+
+    std::vector<float4> rec(c->Rpad, make_float4(kFar, kFar, kFar, 0.f));
+    std::vector<uint8_t> rfl(c->Rpad, 0);
+    std::vector<float> box((size_t)c->n_tiles * 8, 0.f);
+    std::vector<float4> sseed;
+    float rmax = 0.f;
+    for (int s = 0; s < R; ++s) {
+        const int o = s2o[s];
+        rec[s] = make_float4(fx[(size_t)o * 3], fx[(size_t)o * 3 + 1], fx[(size_t)o * 3 + 2], radius_h[o]);
+        rfl[s] = flags_h[o];
+        rmax = std::max(rmax, radius_h[o]);
+        if (flags_h[o] & GMM_F_SEED) sseed.push_back(rec[s]);
+    }
+    c->rmax_static = rmax;
+    for (int t = 0; t < c->n_tiles; ++t) {
+        float* b = &box[(size_t)t * 8];
+        b[0] = b[1] = b[2] = 3e38f; b[3] = b[4] = b[5] = -3e38f; b[6] = 0.f; b[7] = 0.f;
+        for (int s = t * kTileAtoms; s < std::min(R, (t + 1) * kTileAtoms); ++s) {
+            b[0] = std::min(b[0], rec[s].x); b[3] = std::max(b[3], rec[s].x);
+            b[1] = std::min(b[1], rec[s].y); b[4] = std::max(b[4], rec[s].y);
+            b[2] = std::min(b[2], rec[s].z); b[5] = std::max(b[5], rec[s].z);
+            b[6] = std::max(b[6], rec[s].w);
+        }
+    }
+    int rc;
+    if ((rc = upload(&c->d_rec4, rec.data(), rec.size()))) return rc;
+    if ((rc = upload(&c->d_rflags, rfl.data(), rfl.size()))) return rc;
+    if ((rc = upload(&c->d_tile_box, box.data(), box.size()))) return rc;
+    c->n_sseed = (int)sseed.size();
+    if ((rc = upload(&c->d_sseed, sseed.data(), sseed.size()))) return rc;
+    release(c->d_always);
+    if (c->Rpad) GMM_CUDA(cudaMalloc((void**)&c->d_always, sizeof(uint32_t) * c->n_tiles * 4));
+
+    // static-static candidate pairs -> sorted index space, row = smaller sorted index
+    c->rr_nnz = 0;
+    release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
+    if (R > 0 && rr_ptr_h && rr_idx_h && rr_ptr_h[R] > 0) {
+        const int nnz = rr_ptr_h[R];
+        std::vector<std::pair<int32_t, int32_t>> pr;
+        pr.reserve(nnz);
+        for (int a = 0; a < R; ++a)
+            for (int e = rr_ptr_h[a]; e < rr_ptr_h[a + 1]; ++e) {
+                const int b = rr_idx_h[e];
+                REQUIRE(b >= 0 && b < R && b != a, GMM_EINVAL, "gmm_set_receptor: rr_idx[%d]=%d invalid", e, b);
+                const int sa = o2s[a], sb = o2s[b];
+                pr.emplace_back(std::min(sa, sb), std::max(sa, sb));
+            }
+        std::sort(pr.begin(), pr.end());
+        pr.erase(std::unique(pr.begin(), pr.end()), pr.end());
+        std::vector<int32_t> ptr(R + 1, 0), idx(pr.size());
+        for (auto& p : pr) ptr[p.first + 1]++;
+        for (int a = 0; a < R; ++a) ptr[a + 1] += ptr[a];
+        for (size_t e = 0; e < pr.size(); ++e) idx[e] = pr[e].second;
+        c->rr_nnz = (int)pr.size();
+        if ((rc = upload(&c->d_rr_ptr, ptr.data(), ptr.size()))) return rc;
+        if ((rc = upload(&c->d_rr_idx, idx.data(), idx.size()))) return rc;
+        GMM_CUDA(cudaMalloc((void**)&c->d_rr_val, sizeof(long long) * 2 * pr.size()));
+        GMM_CUDA(cudaMalloc((void**)&c->d_rr_kind, pr.size()));
+    }
+    // mobile-static exclusions (flexible side chains bonded to the static backbone)
+    c->ms_nnz = 0;
+    release(c->d_ms_ptr); release(c->d_ms_idx);
+    if (ms_ptr_h && ms_idx_h && ms_ptr_h[c->M] > 0) {
+        std::vector<int32_t> ptr(c->Mp + 1, 0), idx;
+        for (int s = 0; s < c->M; ++s) {
+            const int a = c->h_slot2atom[s];
+            for (int e = ms_ptr_h[a]; e < ms_ptr_h[a + 1]; ++e) {
+                REQUIRE(ms_idx_h[e] >= 0 && ms_idx_h[e] < R, GMM_EINVAL, "gmm_set_receptor: ms_idx[%d] invalid", e);
+                idx.push_back(o2s[ms_idx_h[e]]);
+            }
+            ptr[s + 1] = (int32_t)idx.size();
+        }
+        for (int s = c->M; s < c->Mp; ++s) ptr[s + 1] = ptr[s];
+        c->ms_nnz = (int)idx.size();
+        if ((rc = upload(&c->d_ms_ptr, ptr.data(), ptr.size()))) return rc;
+        if ((rc = upload(&c->d_ms_idx, idx.data(), idx.size()))) return rc;
+    }
+    if ((rc = launch_rr_values(c, 0))) return rc;
+    GMM_CUDA(cudaDeviceSynchronize());
+    c->has_receptor = true;
+    return GMM_OK;
+}
+
+int gmm_reserve(gmm_ctx* c, int max_pop) {
+    REQUIRE(c && c->has_receptor, GMM_ESTATE, "gmm_reserve: model not complete");
+    REQUIRE(max_pop >= 0, GMM_EINVAL, "gmm_reserve: max_pop < 0");
+    DeviceGuard g(c->device);
+    const size_t need = contacts_scratch_bytes(c, max_pop);
+    return ensure_scratch(c, need);
+}
+
+static int check_ready(gmm_ctx* c, int P, const char* fn) {
+    REQUIRE(c, GMM_EINVAL, "%s: ctx is NULL", fn);
+    REQUIRE(c->has_mobile, GMM_ESTATE, "%s: gmm_set_mobile has not been called", fn);
+    REQUIRE(P >= 0, GMM_EINVAL, "%s: P < 0", fn);
+    return GMM_OK;
+}
+
+int gmm_express(gmm_ctx* c, int P, const double* torsion_deg_d, const double* xform_d,
+                const double* rot_allele_d, float* out_xyz_d, void* stream) {
+    int rc = check_ready(c, P, "gmm_express");
+    if (rc) return rc;
+    REQUIRE(out_xyz_d || P == 0, GMM_EINVAL, "gmm_express: out_xyz_d is NULL");
+    REQUIRE(c->n_allele_tors == 0 || torsion_deg_d || P == 0, GMM_EINVAL, "gmm_express: torsion_deg_d is NULL but the model has %d allele torsions", c->n_allele_tors);
+    bool needs_rot = false;
+    REQUIRE(c->T == c->n_allele_tors || c->n_res > 0, GMM_ESTATE, "gmm_express: rotamer-driven torsions but gmm_set_rotamers not called");
+    needs_rot = c->n_res > 0;
+    REQUIRE(!needs_rot || rot_allele_d || P == 0, GMM_EINVAL, "gmm_express: rot_allele_d is NULL but the model has rotamers");
+    DeviceGuard g(c->device);
+    return launch_express(c, P, torsion_deg_d, xform_d, rot_allele_d, out_xyz_d, (cudaStream_t)stream);
+}
+
+int gmm_contacts(gmm_ctx* c, int P, const float* xyz_d, double* out_scores_d, int32_t* out_counts_d, void* stream) {
+    int rc = check_ready(c, P, "gmm_contacts");
+    if (rc) return rc;
+    REQUIRE(c->has_receptor, GMM_ESTATE, "gmm_contacts: gmm_set_receptor has not been called");
+    REQUIRE((xyz_d && out_scores_d) || P == 0, GMM_EINVAL, "gmm_contacts: NULL buffer");
+    DeviceGuard g(c->device);
+    if ((rc = ensure_scratch(c, contacts_scratch_bytes(c, P)))) return rc;
+    return launch_contacts(c, P, xyz_d, out_scores_d, out_counts_d, (cudaStream_t)stream);
+}
+
+int gmm_evaluate(gmm_ctx* c, int P, const double* torsion_deg_d, const double* xform_d, const double* rot_allele_d,
+                 float* out_xyz_d, double* out_scores_d, int32_t* out_counts_d, void* stream) {
+    int rc = check_ready(c, P, "gmm_evaluate");
+    if (rc) return rc;
+    REQUIRE(c->has_receptor, GMM_ESTATE, "gmm_evaluate: gmm_set_receptor has not been called");
+    REQUIRE(out_scores_d || P == 0, GMM_EINVAL, "gmm_evaluate: out_scores_d is NULL");
+    DeviceGuard g(c->device);
+    if ((rc = ensure_scratch(c, contacts_scratch_bytes(c, P)))) return rc;
+    float* xyz = out_xyz_d ? out_xyz_d : static_cast<float*>(c->d_scratch);
+    if ((rc = gmm_express(c, P, torsion_deg_d, xform_d, rot_allele_d, xyz, stream))) return rc;
+    return launch_contacts(c, P, xyz, out_scores_d, out_counts_d, (cudaStream_t)stream);
+}
+
+int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const double* xform_h, const double* rot_allele_h,
+                      float* out_xyz_h, double* out_scores_h, int32_t* out_counts_h, void* stream) {
+    int rc = check_ready(c, P, "gmm_evaluate_host");
+    if (rc) return rc;
+    REQUIRE(c->has_receptor, GMM_ESTATE, "gmm_evaluate_host: gmm_set_receptor has not been called");
+    REQUIRE(out_scores_h || P == 0, GMM_EINVAL, "gmm_evaluate_host: out_scores_h is NULL");
+    if (P == 0) return GMM_OK;
+    DeviceGuard g(c->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t nt = (size_t)P * c->n_allele_tors * sizeof(double);
+    const size_t nx = xform_h ? (size_t)P * 12 * sizeof(double) : 0;
+    const size_t nr = (c->n_res && rot_allele_h) ? (size_t)P * c->n_res * sizeof(double) : 0;
+    const size_t ns = (size_t)P * 2 * sizeof(double);
+    const size_t nc = (size_t)P * 2 * sizeof(int32_t);
+    const size_t nxyz = out_xyz_h ? (size_t)P * c->M * 3 * sizeof(float) : 0;
+    auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_t = 0, o_x = o_t + al(nt), o_r = o_x + al(nx), o_s = o_r + al(nr), o_c = o_s + al(ns),
+                 o_xyz = o_c + al(nc), total = o_xyz + al(nxyz) + 256;
+    if (total > c->stage_bytes) {
+        if (c->d_stage) { GMM_CUDA(cudaDeviceSynchronize()); cudaFree(c->d_stage); c->d_stage = nullptr; }
+        if (c->h_pin) { cudaFreeHost(c->h_pin); c->h_pin = nullptr; }
+        c->stage_bytes = 0;
+        GMM_CUDA(cudaMalloc(&c->d_stage, total));
+        GMM_CUDA(cudaMallocHost(&c->h_pin, total));
+        c->stage_bytes = total;
+    }
+    unsigned char* hp = static_cast<unsigned char*>(c->h_pin);
+    unsigned char* dp = static_cast<unsigned char*>(c->d_stage);
+    if (nt) memcpy(hp + o_t, torsion_deg_h, nt);
+    if (nx) memcpy(hp + o_x, xform_h, nx);
+    if (nr) memcpy(hp + o_r, rot_allele_h, nr);
+    const size_t in_bytes = o_s;   // contiguous block of inputs
+    if (in_bytes) GMM_CUDA(cudaMemcpyAsync(dp, hp, in_bytes, cudaMemcpyHostToDevice, s));
+    rc = gmm_evaluate(c, P, nt ? (const double*)(dp + o_t) : nullptr, nx ? (const double*)(dp + o_x) : nullptr,
+                      nr ? (const double*)(dp + o_r) : nullptr, nxyz ? (float*)(dp + o_xyz) : nullptr,
+                      (double*)(dp + o_s), (int32_t*)(dp + o_c), stream);
+    if (rc) return rc;
+    GMM_CUDA(cudaMemcpyAsync(hp + o_s, dp + o_s, (o_xyz - o_s) + nxyz, cudaMemcpyDeviceToHost, s));
+    GMM_CUDA(cudaStreamSynchronize(s));
+    memcpy(out_scores_h, hp + o_s, ns);
+    if (out_counts_h) memcpy(out_counts_h, hp + o_c, nc);
+    if (nxyz) memcpy(out_xyz_h, hp + o_xyz, nxyz);
+    return GMM_OK;
+}
+
+int gmm_rmsd_matrix(gmm_ctx* c, int N, int A, const float* xyz_d, int row0, int row1, float* out_rmsd_d,
+                    uint32_t* out_similar_d, double threshold, void* stream) {
+    REQUIRE(c, GMM_EINVAL, "gmm_rmsd_matrix: ctx is NULL");
+    REQUIRE(N >= 0 && A >= 1, GMM_EINVAL, "gmm_rmsd_matrix: N=%d A=%d invalid", N, A);
+    REQUIRE(row0 >= 0 && row0 <= row1 && row1 <= N, GMM_EINVAL, "gmm_rmsd_matrix: rows [%d,%d) outside [0,%d]", row0, row1, N);
+    REQUIRE(xyz_d || N == 0, GMM_EINVAL, "gmm_rmsd_matrix: xyz_d is NULL");
+    REQUIRE(out_rmsd_d || out_similar_d || row0 == row1, GMM_EINVAL, "gmm_rmsd_matrix: no output buffer");
+    DeviceGuard g(c->device);
+    return launch_rmsd(c, N, A, xyz_d, row0, row1, out_rmsd_d, out_similar_d, threshold, (cudaStream_t)stream);
+}
+
+int gmm_contacts_pairs(gmm_ctx* c, const float* xyz_one_d, int max_pairs, int32_t* out_pairs_h, int32_t* out_kind_h,
+                       double* out_overlap_h, double* out_value_h, int* n_out_h, void* stream) {
+    int rc = check_ready(c, 1, "gmm_contacts_pairs");
+    if (rc) return rc;
+    REQUIRE(c->has_receptor, GMM_ESTATE, "gmm_contacts_pairs: gmm_set_receptor has not been called");
+    REQUIRE(xyz_one_d && n_out_h && max_pairs >= 0, GMM_EINVAL, "gmm_contacts_pairs: bad argument");
+    REQUIRE(max_pairs == 0 || (out_pairs_h && out_kind_h && out_overlap_h && out_value_h), GMM_EINVAL, "gmm_contacts_pairs: NULL output");
+    DeviceGuard g(c->device);
+    return launch_pairs_dump(c, xyz_one_d, max_pairs, out_pairs_h, out_kind_h, out_overlap_h, out_value_h, n_out_h, (cudaStream_t)stream);
+}
+
+int gmm_last_pair_tests(gmm_ctx* c, unsigned long long* n_out) {
+    REQUIRE(c && n_out, GMM_EINVAL, "gmm_last_pair_tests: NULL argument");
+    DeviceGuard g(c->device);
+    GMM_CUDA(cudaDeviceSynchronize());
+    GMM_CUDA(cudaMemcpy(n_out, c->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return GMM_OK;
+}
+
+}  // extern "C"
+
+// ---- FP32 peak microbenchmark -------------------------------------------------------
+namespace gmm {
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, float a, float b) {
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = (float)(threadIdx.x + k);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = fmaf(v[k], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += v[k];
+    if (s == 123.456f) out[0] = s;
+}
+}  // namespace gmm
+
+extern "C" int gmm_measure_fp32_peak(int device, double* tflops_out) {
+    REQUIRE(tflops_out, GMM_EINVAL, "gmm_measure_fp32_peak: NULL output");
+    DeviceGuard g(device);
+    cudaDeviceProp prop;
+    GMM_CUDA(cudaGetDeviceProperties(&prop, device));
+    float* d = nullptr;
+    GMM_CUDA(cudaMalloc((void**)&d, 4));
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    cudaEvent_t e0, e1;
+    GMM_CUDA(cudaEventCreate(&e0));
+    GMM_CUDA(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        GMM_CUDA(cudaEventRecord(e0, 0));
+        gmm::ffma_peak_kernel<<<blocks, 256>>>(d, iters, 0.999f, 0.001f);
+        GMM_LAUNCH_CHECK("ffma_peak_kernel");
+        GMM_CUDA(cudaEventRecord(e1, 0));
+        GMM_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        GMM_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = 2.0 * 16.0 * iters * 256.0 * blocks;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops_out = best;
+    return GMM_OK;
+}

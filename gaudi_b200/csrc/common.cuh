@@ -1,0 +1,185 @@
+// Shared declarations of libgaudimm_b200 (context, parameters, pair scoring).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/gaudimm_b200.h"
+
+namespace gmm {
+
+// ---- error handling ---------------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern unsigned long long g_launches;
+
+#define GMM_CUDA(call)                                                              \
+    do {                                                                            \
+        cudaError_t _e = (call);                                                    \
+        if (_e != cudaSuccess) {                                                    \
+            gmm::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e),  \
+                           __FILE__, __LINE__);                                     \
+            return GMM_ECUDA;                                                       \
+        }                                                                           \
+    } while (0)
+
+#define GMM_LAUNCH_CHECK(name)                                                      \
+    do {                                                                            \
+        ++gmm::g_launches;                                                          \
+        cudaError_t _e = cudaGetLastError();                                        \
+        if (_e != cudaSuccess) {                                                    \
+            gmm::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));\
+            return GMM_ECUDA;                                                       \
+        }                                                                           \
+    } while (0)
+
+// ---- tunables ---------------------------------------------------------------------
+constexpr int kTileAtoms = 128;      // receptor atoms per tile (4 per lane)
+constexpr int kSweepWarps = 4;       // warps per sweep CTA
+constexpr int kGroup = 8;            // individuals per sweep CTA
+constexpr int kCandQ = 256;          // per-warp candidate queue entries
+constexpr int kPairQ = 128;          // per-warp pair queue entries
+constexpr double kFxScale = 4294967296.0;  // 2^32 fixed-point scale of score sums
+constexpr float kFar = 1.0e15f;      // coordinate of padding atoms
+
+// Contacts settings (gaudi/objectives/contacts.py:101-121,142-145), device copy.
+struct Params {
+    double zone_radius;
+    double clash_thr;
+    double hydro_thr;
+    double hb_allow;
+    double amv;          // assumedMaxVdw
+    double cutoff;
+    double weight;
+    int options;
+};
+
+struct PairScore {
+    long long clash_fx;  // |volume overlap| * 2^32 (0 if not a clash)
+    long long hydro_fx;  // LJ-like energy * 2^32   (0 if not a hydrophobic contact)
+    int kind;            // bit0 clash counted, bit1 hydrophobic counted
+    double overlap;
+    double clash_val, hydro_val;
+};
+
+// One unordered atom pair through DetectClash's acceptance rule and Contacts' scoring.
+//   d, overlap, allowance:          SURVEY.md A.3 / contacts.py:142-145
+//   positive / negative split:      contacts.py:176-187
+//   LJ-like energy:                 contacts.py:215-241
+//   spherical-cap overlap volume:   contacts.py:243-268 (pi literal 3.14159265359)
+__device__ __forceinline__ PairScore score_pair(float ax, float ay, float az, float ra, unsigned fa,
+                                                float bx, float by, float bz, float rb, unsigned fb,
+                                                const Params& p) {
+    PairScore o;
+    o.clash_fx = 0; o.hydro_fx = 0; o.kind = 0; o.clash_val = 0.0; o.hydro_val = 0.0;
+    const double dx = (double)ax - (double)bx;
+    const double dy = (double)ay - (double)by;
+    const double dz = (double)az - (double)bz;
+    const double d = sqrt(dx * dx + dy * dy + dz * dz);
+    const double Ra = (double)ra, Rb = (double)rb;
+    const bool hb = ((fa & GMM_F_DONOR) && (fb & GMM_F_ACCEPTOR)) ||
+                    ((fb & GMM_F_DONOR) && (fa & GMM_F_ACCEPTOR));
+    const double ov = Ra + Rb - d - ((hb && p.hb_allow != 0.0) ? p.hb_allow : 0.0);
+    o.overlap = ov;
+    const double maxr = fmax(Ra, Rb);
+    // which == 'hydrophobic': DetectClash threshold = hydrophobic_threshold
+    if (d <= maxr + p.amv - p.hydro_thr && ov >= p.hydro_thr && ov <= p.clash_thr &&
+        (fa & GMM_F_HYDROPHOBIC) && (fb & GMM_F_HYDROPHOBIC)) {
+        const double r0 = Ra + Rb;
+        const double dist = r0 - ov;
+        double x = r0 / dist;
+        x = x * x; x = x * x * x;                 // (r0 / distance) ** 6
+        double e = x * x - 2.0 * x;
+        e = fmin(fmax(e, -1.0e9), 1.0e9);
+        o.hydro_val = e;
+        o.hydro_fx = __double2ll_rn(e * kFxScale);
+        o.kind |= 2;
+    }
+    // which == 'clashes': DetectClash threshold = clash_threshold, then overlap > clash_threshold
+    if (d <= maxr + p.amv - p.clash_thr && ov >= p.clash_thr && ov > p.clash_thr) {
+        const double dd = Ra + Rb - ov;
+        double v;
+        if (dd == 0.0) {
+            v = 1000.0;
+        } else {
+            double ha = 0.0, hbb = 0.0;
+            if (dd < Ra + Rb) {
+                ha = (Rb * Rb - (dd - Ra) * (dd - Ra)) / (2.0 * dd);
+                hbb = (Ra * Ra - (dd - Rb) * (dd - Rb)) / (2.0 * dd);
+            }
+            v = (3.14159265359 / 3.0) * (ha * ha * (3.0 * Ra - ha) + hbb * hbb * (3.0 * Rb - hbb));
+        }
+        v = fmin(fabs(v), 1.0e9);
+        o.clash_val = v;
+        o.clash_fx = __double2ll_rn(v * kFxScale);
+        o.kind |= 1;
+    }
+    return o;
+}
+
+}  // namespace gmm
+
+// ---- the context ------------------------------------------------------------------
+struct gmm_ctx {
+    int device = 0;
+    bool has_params = false, has_mobile = false, has_receptor = false;
+    gmm::Params prm{};
+
+    // mobile model (slot order = seeds first; d_slot2atom maps back to the caller's order)
+    int M = 0, Mp = 0, T = 0, W = 0, n_allele_tors = 0, n_seed = 0;
+    int origin_atom = 0, tors_before_search = 1;
+    double* d_xyz0 = nullptr;        // [M,3]   caller order
+    uint8_t* d_mflags_atom = nullptr;// [M]     caller order (express needs F_XFORM)
+    int32_t* d_tfixed = nullptr; int32_t* d_tmoving = nullptr; int32_t* d_tsrc = nullptr;
+    uint8_t* d_tsnap = nullptr; uint64_t* d_tmask = nullptr;
+    int32_t* d_slot2atom = nullptr;  // [Mp]    slot -> caller atom index (-1 = padding)
+    float* d_mrad_slot = nullptr;    // [Mp]
+    uint8_t* d_mflags_slot = nullptr;// [Mp]
+    uint32_t* d_mm_pairs = nullptr;  // [n_mm]  slotA | slotB << 16, not excluded
+    int n_mm = 0;
+    float rmax_mobile = 0.f;
+    bool all_seed = true;
+    std::vector<int32_t> h_slot2atom, h_atom2slot;
+    std::vector<float> h_mrad;
+    // rotamers
+    int n_res = 0; int32_t* d_rot_ptr = nullptr; double* d_rot_delta = nullptr;
+
+    // receptor (Morton-sorted, padded to whole tiles)
+    int R = 0, Rpad = 0, n_tiles = 0;
+    float4* d_rec4 = nullptr;        // [Rpad] x,y,z (device frame), radius
+    uint8_t* d_rflags = nullptr;     // [Rpad]
+    float* d_tile_box = nullptr;     // [n_tiles, 8] lo.xyz, hi.xyz, max radius, pad
+    uint32_t* d_always = nullptr;    // [n_tiles*4] zone words of always-in-zone atoms
+    int32_t* d_rr_ptr = nullptr; int32_t* d_rr_idx = nullptr;   // sorted index space
+    long long* d_rr_val = nullptr;   // [nnz,2] clash_fx, hydro_fx
+    uint8_t* d_rr_kind = nullptr;    // [nnz]
+    int rr_nnz = 0;
+    float4* d_sseed = nullptr; int n_sseed = 0;                  // static zone seeds (CB atoms)
+    int32_t* d_ms_ptr = nullptr; int32_t* d_ms_idx = nullptr;   // CSR over slots -> sorted static idx
+    int ms_nnz = 0;
+    std::vector<int32_t> h_sorted2orig;
+    float rmax_static = 0.f;
+    double centre[3] = {0, 0, 0};
+
+    // scratch (grown on demand)
+    void* d_scratch = nullptr; size_t scratch_bytes = 0;
+    unsigned long long* d_counters = nullptr;   // [4] pair tests, ...
+    // pinned staging for gmm_evaluate_host
+    void* h_pin = nullptr; size_t pin_bytes = 0;
+    void* d_stage = nullptr; size_t stage_bytes = 0;
+};
+
+namespace gmm {
+// kernels' host launchers (each returns a GMM_* code)
+int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, const double* rot,
+                   float* out_xyz, cudaStream_t s);
+int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts,
+                    cudaStream_t s);
+int launch_rr_values(gmm_ctx* c, cudaStream_t s);
+int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
+                uint32_t* out_bits, double thr, cudaStream_t s);
+int launch_pairs_dump(gmm_ctx* c, const float* xyz_one, int max_pairs, int32_t* pairs_h,
+                      int32_t* kind_h, double* ov_h, double* val_h, int* n_out, cudaStream_t s);
+int ensure_scratch(gmm_ctx* c, size_t bytes);
+size_t contacts_scratch_bytes(const gmm_ctx* c, int P);
+}  // namespace gmm

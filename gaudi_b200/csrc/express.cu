@@ -1,0 +1,143 @@
+// Genome expression for a whole population: Rotamers.express (gaudi/genes/rotamers.py:141-152,
+// 186-189), Torsion.express (gaudi/genes/torsion.py:153-164), Search.express
+// (gaudi/genes/search.py:201-214) and the coordinate read-back of
+// MolecularIndividual.post_express (gaudi/base.py:301-303).
+//
+// One warp owns one individual.  The template coordinates are copied into that warp's
+// slice of shared memory (fp64, SoA), the bond rotations are applied there in the
+// reference's bond order on the *current* coordinates (exactly what the sequence of
+// BondRot.adjustAngle calls does), then the rigid transform x' = R (x - origin) + t is
+// applied and the result is written as float32 in the re-centred device frame with fully
+// coalesced stores.  All arithmetic is fp64: the whole stage is ~6 kflop per individual,
+// three orders of magnitude below the Contacts stage, so precision is free here.
+#include "common.cuh"
+
+namespace gmm {
+
+constexpr int kExprWarps = 4;
+
+struct ExpressArgs {
+    int P, M, Mp, T, n_allele_tors, n_res, origin_atom, tors_before_search;
+    const double* xyz0; const uint8_t* mflags;
+    const int32_t* tfixed; const int32_t* tmoving; const int32_t* tsrc; const uint8_t* tsnap;
+    const uint64_t* tmask; int W;
+    const int32_t* rot_ptr; const double* rot_delta;
+    const double* tors; const double* xform; const double* rot;
+    float* out; double cx, cy, cz;
+};
+
+__global__ void __launch_bounds__(kExprWarps * 32)
+express_kernel(const ExpressArgs a) {
+    extern __shared__ double sm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double* sx = sm + (size_t)warp * 3 * a.Mp;
+    double* sy = sx + a.Mp;
+    double* sz = sy + a.Mp;
+    const int stride = gridDim.x * kExprWarps;
+    for (int p = blockIdx.x * kExprWarps + warp; p < a.P; p += stride) {
+        for (int i = lane; i < a.M; i += 32) {
+            sx[i] = a.xyz0[3 * i]; sy[i] = a.xyz0[3 * i + 1]; sz[i] = a.xyz0[3 * i + 2];
+        }
+        __syncwarp();
+        for (int t = 0; t < a.T; ++t) {
+            const int src = a.tsrc[t];
+            double alpha;
+            if (src >= 0) {
+                alpha = a.tors[(size_t)p * a.n_allele_tors + src];
+                if (a.tsnap[t]) alpha = (alpha <= 0.0) ? 0.0 : 180.0;   // torsion.py:159-160
+            } else {
+                const int code = -(src + 1), res = code >> 2, chi = code & 3;
+                const int r0 = a.rot_ptr[res], n = a.rot_ptr[res + 1] - r0;
+                int k = (int)(a.rot[(size_t)p * a.n_res + res] * (double)n);  // rotamers.py:150
+                k = min(max(k, 0), n - 1);
+                alpha = a.rot_delta[(size_t)(r0 + k) * 4 + chi];
+            }
+            if (alpha != 0.0) {   // warp-uniform
+                const int f = a.tfixed[t], m = a.tmoving[t];
+                const double bx = sx[m], by = sy[m], bz = sz[m];
+                double ux = bx - sx[f], uy = by - sy[f], uz = bz - sz[f];
+                const double inv = 1.0 / sqrt(ux * ux + uy * uy + uz * uz);
+                ux *= inv; uy *= inv; uz *= inv;
+                double s, c;
+                sincos(alpha * (3.14159265358979323846 / 180.0), &s, &c);
+                const double omc = 1.0 - c;
+                __syncwarp();
+                const uint64_t* mask = a.tmask + (size_t)t * a.W;
+                for (int i = lane; i < a.M; i += 32) {
+                    if ((mask[i >> 6] >> (i & 63)) & 1ull) {
+                        const double vx = sx[i] - bx, vy = sy[i] - by, vz = sz[i] - bz;
+                        const double crx = uy * vz - uz * vy;
+                        const double cry = uz * vx - ux * vz;
+                        const double crz = ux * vy - uy * vx;
+                        const double dot = ux * vx + uy * vy + uz * vz;
+                        sx[i] = bx + vx * c + crx * s + ux * dot * omc;
+                        sy[i] = by + vy * c + cry * s + uy * dot * omc;
+                        sz[i] = bz + vz * c + crz * s + uz * dot * omc;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        // Search: xform = T . R . to_zero(origin)  ->  x' = R (x - origin) + t
+        double m[12];
+        const bool has_x = a.xform != nullptr;
+        double ox = 0, oy = 0, oz = 0;
+        if (has_x) {
+#pragma unroll
+            for (int k = 0; k < 12; ++k) m[k] = a.xform[(size_t)p * 12 + k];
+            if (a.tors_before_search) {
+                ox = sx[a.origin_atom]; oy = sy[a.origin_atom]; oz = sz[a.origin_atom];
+            } else {
+                ox = a.xyz0[3 * a.origin_atom]; oy = a.xyz0[3 * a.origin_atom + 1];
+                oz = a.xyz0[3 * a.origin_atom + 2];
+            }
+        }
+        __syncwarp();
+        for (int i = lane; i < a.M; i += 32) {
+            double x = sx[i], y = sy[i], z = sz[i];
+            if (has_x && (a.mflags[i] & GMM_F_XFORM)) {
+                const double dx = x - ox, dy = y - oy, dz = z - oz;
+                x = m[0] * dx + m[1] * dy + m[2] * dz + m[3];
+                y = m[4] * dx + m[5] * dy + m[6] * dz + m[7];
+                z = m[8] * dx + m[9] * dy + m[10] * dz + m[11];
+            }
+            sx[i] = x - a.cx; sy[i] = y - a.cy; sz[i] = z - a.cz;
+        }
+        __syncwarp();
+        float* o = a.out + (size_t)p * a.M * 3;
+        for (int e = lane; e < 3 * a.M; e += 32) {
+            const int i = e / 3, k = e - 3 * i;
+            o[e] = (float)(k == 0 ? sx[i] : (k == 1 ? sy[i] : sz[i]));
+        }
+        __syncwarp();
+    }
+}
+
+int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, const double* rot,
+                   float* out_xyz, cudaStream_t s) {
+    if (P == 0) return GMM_OK;
+    ExpressArgs a;
+    a.P = P; a.M = c->M; a.Mp = c->M; a.T = c->T; a.n_allele_tors = c->n_allele_tors;
+    a.n_res = c->n_res; a.origin_atom = c->origin_atom; a.tors_before_search = c->tors_before_search;
+    a.xyz0 = c->d_xyz0; a.mflags = c->d_mflags_atom;
+    a.tfixed = c->d_tfixed; a.tmoving = c->d_tmoving; a.tsrc = c->d_tsrc; a.tsnap = c->d_tsnap;
+    a.tmask = c->d_tmask; a.W = c->W;
+    a.rot_ptr = c->d_rot_ptr; a.rot_delta = c->d_rot_delta;
+    a.tors = tors; a.xform = xform; a.rot = rot; a.out = out_xyz;
+    a.cx = c->centre[0]; a.cy = c->centre[1]; a.cz = c->centre[2];
+    const size_t smem = (size_t)kExprWarps * 3 * a.Mp * sizeof(double);
+    static bool attr_set = false;
+    if (smem > 48 * 1024 && !attr_set) {
+        GMM_CUDA(cudaFuncSetAttribute(express_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      200 * 1024));
+        attr_set = true;
+    }
+    int blocks = (P + kExprWarps - 1) / kExprWarps;
+    const int cap = 148 * 16;
+    if (blocks > cap) blocks = cap;
+    express_kernel<<<blocks, kExprWarps * 32, smem, s>>>(a);
+    GMM_LAUNCH_CHECK("express_kernel");
+    return GMM_OK;
+}
+
+}  // namespace gmm

@@ -1,0 +1,208 @@
+"""Python face of the C ABI: one ``Engine`` = one ``gmm_ctx`` (one GPU, one static model).
+
+PyTorch is used only as the owner of device buffers and streams; every computation is a
+call into ``libgaudimm_b200.so`` with raw ``data_ptr()`` device pointers on torch's current
+stream.  There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .model import ContactParams, MobileModel, ReceptorModel
+
+
+def _np_ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _dev_ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class Engine(object):
+    """Batched express + Contacts + RMSD on one B200.
+
+    Mirrors, for a whole population, what ``Environment.evaluate`` (gaudi/base.py:353-364)
+    does for one individual and what ``gaudi.similarity.rmsd`` (gaudi/similarity.py:36-70)
+    does for one pair.
+    """
+
+    def __init__(self, mobile: MobileModel, receptor: ReceptorModel,
+                 params: ContactParams | None = None, device: int = 0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("gaudi_b200 needs a CUDA device (there is no CPU fallback)")
+        self._L = _lib.lib()
+        self.device = int(device)
+        self.torch_device = torch.device("cuda", self.device)
+        self.mobile, self.receptor = mobile, receptor
+        self.params = params or ContactParams()
+        h = C.c_void_p()
+        _lib.check(self._L.gmm_create(C.byref(h), self.device))
+        self._h = h
+        p = self.params
+        opts = (_lib.OPT_ONLY_INTERNAL if p.only_internal else 0) | (0 if p.cull else _lib.OPT_NO_CULL)
+        _lib.check(self._L.gmm_set_params(h, p.radius, p.clash_threshold, p.hydrophobic_threshold,
+                                          p.hbond_allowance, p.assumed_max_vdw, p.cutoff, p.weight,
+                                          opts))
+        m = mobile
+        keep = [np.ascontiguousarray(m.xyz0, np.float64), np.ascontiguousarray(m.radius, np.float32),
+                np.ascontiguousarray(m.flags, np.uint8), np.ascontiguousarray(m.tors_fixed, np.int32),
+                np.ascontiguousarray(m.tors_moving, np.int32), np.ascontiguousarray(m.tors_mask, np.uint64),
+                np.ascontiguousarray(m.tors_snap, np.uint8), np.ascontiguousarray(m.tors_src, np.int32),
+                np.ascontiguousarray(m.excl_mask, np.uint64)]
+        _lib.check(self._L.gmm_set_mobile(h, m.n_atoms, _np_ptr(keep[0]), _np_ptr(keep[1]), _np_ptr(keep[2]),
+                                          m.n_torsions, _np_ptr(keep[3]), _np_ptr(keep[4]), _np_ptr(keep[5]),
+                                          _np_ptr(keep[6]), _np_ptr(keep[7]), _np_ptr(keep[8]),
+                                          m.origin_atom, int(m.torsion_before_search)))
+        if m.n_rotamer_residues:
+            rp = np.ascontiguousarray(m.rot_ptr, np.int32)
+            rd = np.ascontiguousarray(m.rot_delta, np.float64)
+            _lib.check(self._L.gmm_set_rotamers(h, m.n_rotamer_residues, _np_ptr(rp), _np_ptr(rd)))
+        r = receptor
+        rk = [np.ascontiguousarray(r.xyz, np.float64), np.ascontiguousarray(r.radius, np.float32),
+              np.ascontiguousarray(r.flags, np.uint8), np.ascontiguousarray(r.rr_ptr, np.int32),
+              np.ascontiguousarray(r.rr_idx, np.int32), np.ascontiguousarray(r.centre, np.float64)]
+        ms_ptr = ms_idx = None
+        if len(r.ms_excl_idx):
+            ms_ptr = np.ascontiguousarray(r.ms_excl_ptr, np.int32)
+            ms_idx = np.ascontiguousarray(r.ms_excl_idx, np.int32)
+        _lib.check(self._L.gmm_set_receptor(h, r.n_atoms, _np_ptr(rk[0]), _np_ptr(rk[1]), _np_ptr(rk[2]),
+                                            _np_ptr(rk[3]), _np_ptr(rk[4]) if len(rk[4]) else None,
+                                            _np_ptr(ms_ptr), _np_ptr(ms_idx), _np_ptr(rk[5])))
+        self.centre = np.array(r.centre, dtype=np.float64)
+
+    # -- plumbing ----------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._L.gmm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.torch_device).cuda_stream)
+
+    def _dev(self, a, dtype):
+        if a is None:
+            return None
+        if isinstance(a, torch.Tensor):
+            return a.to(device=self.torch_device, dtype=dtype).contiguous()
+        return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(self.torch_device)
+
+    def reserve(self, max_pop):
+        _lib.check(self._L.gmm_reserve(self._h, int(max_pop)))
+
+    # -- hot path ----------------------------------------------------------------------
+    def express(self, torsions=None, xforms=None, rot_alleles=None, out=None):
+        """(P, M, 3) float32 device-frame coordinates (add ``self.centre`` for world frame)."""
+        t = self._dev(torsions, torch.float64)
+        x = self._dev(xforms, torch.float64)
+        r = self._dev(rot_alleles, torch.float64)
+        P = int((t if t is not None else (x if x is not None else r)).shape[0])
+        if out is None:
+            out = torch.empty((P, self.mobile.n_atoms, 3), dtype=torch.float32, device=self.torch_device)
+        _lib.check(self._L.gmm_express(self._h, P, _dev_ptr(t), _dev_ptr(x), _dev_ptr(r), _dev_ptr(out),
+                                       self._stream()))
+        return out
+
+    def contacts(self, xyz, counts=True):
+        xyz = self._dev(xyz, torch.float32)
+        P = int(xyz.shape[0])
+        scores = torch.empty((P, 2), dtype=torch.float64, device=self.torch_device)
+        cnt = torch.empty((P, 2), dtype=torch.int32, device=self.torch_device) if counts else None
+        _lib.check(self._L.gmm_contacts(self._h, P, _dev_ptr(xyz), _dev_ptr(scores), _dev_ptr(cnt),
+                                        self._stream()))
+        return scores, cnt
+
+    def evaluate(self, torsions=None, xforms=None, rot_alleles=None, want_xyz=False, counts=True,
+                 scores_out=None, counts_out=None, xyz_out=None):
+        """Device-resident batched ``Environment.evaluate``: returns (scores, counts, xyz)."""
+        t = self._dev(torsions, torch.float64)
+        x = self._dev(xforms, torch.float64)
+        r = self._dev(rot_alleles, torch.float64)
+        P = int((t if t is not None else (x if x is not None else r)).shape[0])
+        scores = scores_out if scores_out is not None else torch.empty(
+            (P, 2), dtype=torch.float64, device=self.torch_device)
+        cnt = counts_out
+        if cnt is None and counts:
+            cnt = torch.empty((P, 2), dtype=torch.int32, device=self.torch_device)
+        xyz = xyz_out
+        if xyz is None and want_xyz:
+            xyz = torch.empty((P, self.mobile.n_atoms, 3), dtype=torch.float32, device=self.torch_device)
+        _lib.check(self._L.gmm_evaluate(self._h, P, _dev_ptr(t), _dev_ptr(x), _dev_ptr(r), _dev_ptr(xyz),
+                                        _dev_ptr(scores), _dev_ptr(cnt), self._stream()))
+        return scores, cnt, xyz
+
+    def evaluate_host(self, torsions=None, xforms=None, rot_alleles=None, want_xyz=False):
+        """Host buffers in, host buffers out (H2D + kernels + D2H inside the call)."""
+        t = None if torsions is None else np.ascontiguousarray(torsions, np.float64)
+        x = None if xforms is None else np.ascontiguousarray(xforms, np.float64)
+        r = None if rot_alleles is None else np.ascontiguousarray(rot_alleles, np.float64)
+        P = int((t if t is not None else (x if x is not None else r)).shape[0])
+        scores = np.empty((P, 2), np.float64)
+        cnt = np.empty((P, 2), np.int32)
+        xyz = np.empty((P, self.mobile.n_atoms, 3), np.float32) if want_xyz else None
+        _lib.check(self._L.gmm_evaluate_host(self._h, P, _np_ptr(t), _np_ptr(x), _np_ptr(r), _np_ptr(xyz),
+                                             _np_ptr(scores), _np_ptr(cnt), self._stream()))
+        return scores, cnt, xyz
+
+    def rmsd_matrix(self, xyz, row0=0, row1=None, threshold=2.5, values=True, bits=True):
+        """Rows [row0, row1) of the all-pairs RMSD matrix of (N, A, 3) conformers.
+        Returns (rmsd float32 (rows, N) or None, similar uint32 bitmask (rows, ceil(N/32)) or None)."""
+        xyz = self._dev(xyz, torch.float32)
+        n, a = int(xyz.shape[0]), int(xyz.shape[1])
+        row1 = n if row1 is None else int(row1)
+        rows = row1 - row0
+        out = torch.empty((rows, n), dtype=torch.float32, device=self.torch_device) if values else None
+        # int32 storage for the uint32 words (torch has no general uint32 support)
+        bm = torch.empty((rows, (n + 31) // 32), dtype=torch.int32, device=self.torch_device) if bits else None
+        _lib.check(self._L.gmm_rmsd_matrix(self._h, n, a, _dev_ptr(xyz), int(row0), row1, _dev_ptr(out),
+                                           _dev_ptr(bm), float(threshold), self._stream()))
+        return out, bm
+
+    # -- parity / measurement helpers --------------------------------------------------
+    def contact_pairs(self, xyz_one, max_pairs=1 << 16):
+        """Pairs behind the Contacts score of one individual: list of
+        (atom_a, atom_b, kind, overlap, value); static atoms are numbered M + index."""
+        xyz = self._dev(xyz_one, torch.float32).reshape(self.mobile.n_atoms, 3)
+        pairs = np.empty((max_pairs, 2), np.int32)
+        kind = np.empty(max_pairs, np.int32)
+        ov = np.empty(max_pairs, np.float64)
+        val = np.empty(max_pairs, np.float64)
+        n = C.c_int(0)
+        _lib.check(self._L.gmm_contacts_pairs(self._h, _dev_ptr(xyz), max_pairs, _np_ptr(pairs), _np_ptr(kind),
+                                              _np_ptr(ov), _np_ptr(val), C.byref(n), self._stream()))
+        k = min(n.value, max_pairs)
+        return [(int(pairs[i, 0]), int(pairs[i, 1]), int(kind[i]), float(ov[i]), float(val[i])) for i in range(k)]
+
+    def last_pair_tests(self):
+        n = C.c_ulonglong(0)
+        _lib.check(self._L.gmm_last_pair_tests(self._h, C.byref(n)))
+        return int(n.value)
+
+
+def measure_fp32_peak(device=0):
+    """Measured dependent-free FFMA throughput in TFLOP/s (FP32 roofline denominator)."""
+    v = C.c_double(0.0)
+    _lib.check(_lib.lib().gmm_measure_fp32_peak(int(device), C.byref(v)))
+    return float(v.value)
+
+
+def launch_count():
+    return int(_lib.lib().gmm_launch_count())
+
+
+def bits_to_bool(bits, n):
+    """(rows, ceil(n/32)) int32/uint32 words -> (rows, n) bool numpy array."""
+    w = np.ascontiguousarray(bits.detach().cpu().numpy() if isinstance(bits, torch.Tensor) else bits)
+    w = w.view(np.uint32)
+    b = np.unpackbits(w.view(np.uint8).reshape(w.shape[0], -1), axis=1, bitorder="little")
+    return b[:, :n].astype(bool)

@@ -1,0 +1,276 @@
+"""
+Static model of a GaudiMM job as the CUDA path consumes it.
+
+The reference keeps topology inside live ``chimera.Molecule`` objects and rediscovers it
+on every evaluation (``BondRot`` objects at gaudi/genes/torsion.py:245-307, 4-level bond
+BFS inside ``DetectClash`` at gaudi/objectives/contacts.py:142-145).  Here everything that
+does not depend on the alleles is flattened once, on the host, into plain arrays:
+
+* ``MobileModel``   – atoms whose coordinates depend on the genome (the Search/Torsion
+  target ligand and, with a Rotamers gene, the flexible side chains);
+* ``ReceptorModel`` – every other atom of every Molecule gene (fixed coordinates);
+* ``ContactParams`` – the Contacts objective's settings (contacts.py:101-121).
+
+These arrays are exactly what ``include/gaudimm_b200.h`` takes.  This is input
+preparation (topology walks, run once per job); no scoring arithmetic happens here.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+# per-atom flag bits (uint8) ----------------------------------------------------------
+F_HYDROPHOBIC = 1   # element in Contacts.hydrophobic_elements (contacts.py:103)
+F_DONOR = 2         # H-bond donor   (DetectClash hbondAllowance, contacts.py:144)
+F_ACCEPTOR = 4      # H-bond acceptor
+F_SEED = 8          # zone seed: atom of a `probes` molecule or CB of a Rotamers residue
+F_XFORM = 16        # mobile atom that the Search gene's xform applies to
+
+
+def adjacency(n_atoms, bonds):
+    adj = [[] for _ in range(n_atoms)]
+    for a, b in np.asarray(bonds, dtype=np.int64).reshape(-1, 2):
+        adj[int(a)].append(int(b))
+        adj[int(b)].append(int(a))
+    return adj
+
+
+def within_bonds(adj, src, depth):
+    """Atoms reachable from ``src`` in at most ``depth`` bonds (``src`` included)."""
+    seen = {src}
+    frontier = [src]
+    for _ in range(depth):
+        nxt = []
+        for a in frontier:
+            for b in adj[a]:
+                if b not in seen:
+                    seen.add(b)
+                    nxt.append(b)
+        frontier = nxt
+        if not frontier:
+            break
+    return seen
+
+
+def side_of_bond(adj, fixed, moving):
+    """Atoms on the ``moving`` side of the bond fixed-moving (``moving`` included).
+    Raises ValueError if the bond is in a cycle (``chimera.BondRot`` refuses those,
+    torsion.py:299-304)."""
+    seen = {moving}
+    stack = [moving]
+    while stack:
+        a = stack.pop()
+        for b in adj[a]:
+            if a == moving and b == fixed:
+                continue
+            if b == fixed:
+                raise ValueError("bond %d-%d is in a cycle" % (fixed, moving))
+            if b not in seen:
+                seen.add(b)
+                stack.append(b)
+    return seen
+
+
+def graph_distances(adj, src):
+    dist = {src: 0}
+    frontier = [src]
+    while frontier:
+        nxt = []
+        for a in frontier:
+            for b in adj[a]:
+                if b not in dist:
+                    dist[b] = dist[a] + 1
+                    nxt.append(b)
+        frontier = nxt
+    return dist
+
+
+def bitmask(indices, n_atoms):
+    words = (n_atoms + 63) // 64
+    out = np.zeros(words, dtype=np.uint64)
+    for i in indices:
+        out[i >> 6] |= np.uint64(1) << np.uint64(i & 63)
+    return out
+
+
+@dataclass
+class ContactParams:
+    """gaudi/objectives/contacts.py:101-121 plus DetectClash's fixed options (:142-145)."""
+    radius: float = 5.0
+    clash_threshold: float = 0.6
+    hydrophobic_threshold: float = -0.4
+    hbond_allowance: float = 0.2
+    assumed_max_vdw: float = 2.1
+    cutoff: float = 0.0
+    weight: float = 1.0
+    bond_separation: int = 4
+    only_internal: bool = False
+    cull: bool = True       # B200 path only: skip receptor tiles out of reach of a pose
+
+
+@dataclass
+class MobileModel:
+    xyz0: np.ndarray            # (M, 3) f64 template coordinates (input-file frame)
+    radius: np.ndarray          # (M,)  f64
+    flags: np.ndarray           # (M,)  u8
+    bonds: np.ndarray           # (nb, 2) i32 bonds among mobile atoms
+    tors_fixed: np.ndarray      # (T,) i32   anchor-side atom of each rotatable bond
+    tors_moving: np.ndarray     # (T,) i32   moving-side atom
+    tors_mask: np.ndarray       # (T, W) u64 moving-side atom sets, W = ceil(M / 64)
+    tors_snap: np.ndarray       # (T,) u8    both atoms C2/N2 -> 0/180 only (torsion.py:159)
+    tors_src: np.ndarray        # (T,) i32   >= 0: column of the torsion allele;
+                                #            < 0: rotamer driven, -(1 + 4 * residue + chi)
+    excl_mask: np.ndarray       # (M, W) u64 atoms within <= bond_separation bonds (self incl.)
+    origin_atom: int = 0        # Search target atom (search.py:186-188)
+    torsion_before_search: bool = True
+    rot_ptr: np.ndarray = field(default_factory=lambda: np.zeros(1, dtype=np.int32))
+    rot_delta: np.ndarray = field(default_factory=lambda: np.zeros((0, 4), dtype=np.float64))
+
+    @property
+    def n_atoms(self):
+        return int(self.xyz0.shape[0])
+
+    @property
+    def n_torsions(self):
+        return int(self.tors_fixed.shape[0])
+
+    @property
+    def n_allele_torsions(self):
+        return int((self.tors_src >= 0).sum())
+
+    @property
+    def n_rotamer_residues(self):
+        return int(self.rot_ptr.shape[0] - 1)
+
+    def moving_indices(self, t):
+        m = self.tors_mask[t]
+        return np.array([i for i in range(self.n_atoms)
+                         if (int(m[i >> 6]) >> (i & 63)) & 1], dtype=np.int64)
+
+
+@dataclass
+class ReceptorModel:
+    xyz: np.ndarray             # (R, 3) f64 world coordinates
+    radius: np.ndarray          # (R,)  f64
+    flags: np.ndarray           # (R,)  u8 (F_SEED marks CB atoms of Rotamers residues)
+    bonds: np.ndarray           # (nb, 2) i32 bonds among static atoms
+    rr_ptr: np.ndarray          # (R + 1,) i32 CSR over static atoms a ...
+    rr_idx: np.ndarray          # (nnz,)  i32 ... partners b > a, > bond_separation bonds apart
+                                #          and close enough to ever be reported by DetectClash
+    centre: np.ndarray          # (3,) f64 re-centring origin of the fp32 device frame
+    ms_excl_ptr: np.ndarray = field(default_factory=lambda: np.zeros(1, dtype=np.int32))
+    ms_excl_idx: np.ndarray = field(default_factory=lambda: np.zeros(0, dtype=np.int32))
+    # ^ CSR over *mobile* atoms: static atoms within <= bond_separation bonds (Rotamers only)
+
+    @property
+    def n_atoms(self):
+        return int(self.xyz.shape[0])
+
+
+def build_mobile(xyz0, radius, flags, bonds, rotatable, origin_atom=0,
+                 torsion_before_search=True, snap=None, bond_separation=4,
+                 tors_src=None, rot_ptr=None, rot_delta=None):
+    """Flatten a mobile molecule.
+
+    ``rotatable`` is a list of ``(fixed, moving)`` atom-index pairs in the reference's bond
+    order (sorted by min serial, torsion.py:246-248); ``fixed`` is the atom on the anchor
+    side (``box.find_nearest(anchor, bond.atoms)``, torsion.py:305).
+    """
+    xyz0 = np.ascontiguousarray(xyz0, dtype=np.float64)
+    m = xyz0.shape[0]
+    bonds = np.asarray(bonds, dtype=np.int32).reshape(-1, 2)
+    adj = adjacency(m, bonds)
+    words = (m + 63) // 64
+    t = len(rotatable)
+    tors_mask = np.zeros((t, words), dtype=np.uint64)
+    for k, (fx, mv) in enumerate(rotatable):
+        tors_mask[k] = bitmask(side_of_bond(adj, int(fx), int(mv)), m)
+    excl = np.zeros((m, words), dtype=np.uint64)
+    for a in range(m):
+        excl[a] = bitmask(within_bonds(adj, a, bond_separation), m)
+    rot = np.asarray(rotatable, dtype=np.int32).reshape(-1, 2)
+    return MobileModel(
+        xyz0=xyz0,
+        radius=np.ascontiguousarray(radius, dtype=np.float64),
+        flags=np.ascontiguousarray(flags, dtype=np.uint8),
+        bonds=bonds,
+        tors_fixed=np.ascontiguousarray(rot[:, 0]),
+        tors_moving=np.ascontiguousarray(rot[:, 1]),
+        tors_mask=tors_mask,
+        tors_snap=(np.zeros(t, dtype=np.uint8) if snap is None
+                   else np.ascontiguousarray(snap, dtype=np.uint8)),
+        tors_src=(np.arange(t, dtype=np.int32) if tors_src is None
+                  else np.ascontiguousarray(tors_src, dtype=np.int32)),
+        excl_mask=excl,
+        origin_atom=int(origin_atom),
+        torsion_before_search=bool(torsion_before_search),
+        rot_ptr=(np.zeros(1, dtype=np.int32) if rot_ptr is None
+                 else np.ascontiguousarray(rot_ptr, dtype=np.int32)),
+        rot_delta=(np.zeros((0, 4), dtype=np.float64) if rot_delta is None
+                   else np.ascontiguousarray(rot_delta, dtype=np.float64).reshape(-1, 4)),
+    )
+
+
+def static_pair_candidates(xyz, radius, bonds, params, max_mobile_radius=0.0):
+    """CSR of static-static pairs that DetectClash could ever report: more than
+    ``bond_separation`` bonds apart and within the loosest geometric bound
+    ``d <= r_a + r_b - min(thresholds)``.  Their *values* are computed on the device
+    (``gmm_set_receptor``); this is only the neighbour/topology search."""
+    from scipy.spatial import cKDTree
+    r = xyz.shape[0]
+    ptr = np.zeros(r + 1, dtype=np.int32)
+    if r < 2:
+        return ptr, np.zeros(0, dtype=np.int32)
+    thr = min(params.hydrophobic_threshold, params.clash_threshold)
+    rmax = float(np.max(radius))
+    tree = cKDTree(xyz)
+    pairs = tree.query_pairs(2.0 * rmax - thr + 1e-6, output_type='ndarray')
+    if len(pairs) == 0:
+        return ptr, np.zeros(0, dtype=np.int32)
+    a = np.minimum(pairs[:, 0], pairs[:, 1])
+    b = np.maximum(pairs[:, 0], pairs[:, 1])
+    d = np.sqrt(((xyz[a] - xyz[b]) ** 2).sum(axis=1))
+    keep = d <= radius[a] + radius[b] - thr + 1e-6
+    a, b = a[keep], b[keep]
+    # drop pairs within <= bond_separation bonds
+    adj = adjacency(r, bonds)
+    cache = {}
+    ok = np.ones(len(a), dtype=bool)
+    for k in range(len(a)):
+        ai = int(a[k])
+        if not adj[ai]:
+            continue
+        nb = cache.get(ai)
+        if nb is None:
+            nb = cache[ai] = within_bonds(adj, ai, params.bond_separation)
+        if int(b[k]) in nb:
+            ok[k] = False
+    a, b = a[ok], b[ok]
+    order = np.lexsort((b, a))
+    a, b = a[order], b[order]
+    counts = np.bincount(a, minlength=r)
+    ptr[1:] = np.cumsum(counts)
+    return ptr, b.astype(np.int32)
+
+
+def build_receptor(xyz, radius, flags, bonds, params, centre=None):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+    radius = np.ascontiguousarray(radius, dtype=np.float64)
+    bonds = np.asarray(bonds, dtype=np.int32).reshape(-1, 2)
+    if params.only_internal:
+        ptr, idx = np.zeros(xyz.shape[0] + 1, dtype=np.int32), np.zeros(0, dtype=np.int32)
+    else:
+        ptr, idx = static_pair_candidates(xyz, radius, bonds, params)
+    if centre is None:
+        centre = xyz.mean(axis=0) if len(xyz) else np.zeros(3)
+    return ReceptorModel(xyz=xyz, radius=radius,
+                         flags=np.ascontiguousarray(flags, dtype=np.uint8),
+                         bonds=bonds, rr_ptr=ptr, rr_idx=idx,
+                         centre=np.ascontiguousarray(centre, dtype=np.float64))
+
+
+def empty_receptor(centre=(0.0, 0.0, 0.0)):
+    return ReceptorModel(xyz=np.zeros((0, 3)), radius=np.zeros(0), flags=np.zeros(0, np.uint8),
+                         bonds=np.zeros((0, 2), np.int32), rr_ptr=np.zeros(1, np.int32),
+                         rr_idx=np.zeros(0, np.int32), centre=np.asarray(centre, np.float64))

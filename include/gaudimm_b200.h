@@ -1,0 +1,179 @@
+/*
+ * gaudimm_b200.h — C ABI of libgaudimm_b200.so
+ *
+ * Batched (population-wide) replacement for the data-parallel hot path of GaudiMM
+ * (insilichem/gaudi): genome expression (Torsion, Rotamers, Search genes) -> Contacts
+ * objective -> pairwise similarity.rmsd.  The reference evaluates one individual at a
+ * time through UCSF Chimera; this library evaluates a whole population tensor per call on
+ * one B200.  Reference citations are paths relative to the reference repository root.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative GMM_E* code on failure; the
+ *     message is available from gmm_last_error() (thread local).  Nothing throws.
+ *   - pointers suffixed _h are HOST pointers, read during the call and not retained;
+ *     pointers suffixed _d are DEVICE pointers on the context's device (for a torch
+ *     tensor: tensor.data_ptr() of a contiguous CUDA tensor).  The library never frees or
+ *     reallocates caller memory.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Work is
+ *     enqueued on it; the batched calls do not synchronise, except that the first call
+ *     with a larger population than any before it grows the context's scratch buffer
+ *     (one cudaMalloc); call gmm_reserve() up front to avoid that.
+ *   - device coordinates are float32 in a frame re-centred at `centre` given to
+ *     gmm_set_receptor(): x_dev = (float)(x_world - centre).
+ *   - one context serves one (mobile model, receptor, parameter set); contexts are
+ *     independent.  Calls on one context must not overlap in time unless they are on the
+ *     same stream (they share the scratch buffer).
+ */
+#ifndef GAUDIMM_B200_H
+#define GAUDIMM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GMM_OK            0
+#define GMM_EINVAL       (-1)   /* bad argument */
+#define GMM_ECUDA        (-2)   /* CUDA runtime error (see gmm_last_error) */
+#define GMM_ESTATE       (-3)   /* call order: model/receptor/params not set */
+#define GMM_ELIMIT       (-4)   /* size beyond a documented limit */
+
+/* per-atom flag bits (uint8) */
+#define GMM_F_HYDROPHOBIC  1    /* element in Contacts.hydrophobic_elements (contacts.py:103) */
+#define GMM_F_DONOR        2    /* H-bond donor   (DetectClash hbondAllowance, contacts.py:144) */
+#define GMM_F_ACCEPTOR     4    /* H-bond acceptor */
+#define GMM_F_SEED         8    /* zone seed: probe atom / CB of a Rotamers residue (contacts.py:195-207) */
+#define GMM_F_XFORM       16    /* mobile atom moved by the Search xform (search.py:201-214) */
+
+/* gmm_set_params option bits */
+#define GMM_OPT_ONLY_INTERNAL  1  /* Contacts(only_internal=True), contacts.py:199 */
+#define GMM_OPT_NO_CULL        2  /* score every receptor tile (dense), no bounding-box culling */
+
+#define GMM_MAX_MOBILE_ATOMS   1024
+#define GMM_MAX_TORSIONS       1024
+
+typedef struct gmm_ctx gmm_ctx;
+
+/* Library / context -------------------------------------------------------------- */
+int         gmm_create(gmm_ctx** out, int device);
+int         gmm_destroy(gmm_ctx* ctx);
+const char* gmm_last_error(void);
+int         gmm_version(void);
+/* Pre-size the context's scratch for populations up to max_pop (optional). */
+int         gmm_reserve(gmm_ctx* ctx, int max_pop);
+
+/* Static model (host pointers, uploaded once) ------------------------------------ */
+
+/* The atoms whose coordinates depend on the genome.  Replaces the live chimera.Molecule
+ * plus the BondRot list of gaudi/genes/torsion.py:215-307 and the per-residue chi BondRots
+ * of gaudi/genes/rotamers.py:186-210.
+ *   xyz0_h      [M,3]  template coordinates (input-file frame), fp64
+ *   tors_*      T rotatable bonds in the reference's bond order (torsion.py:246-248);
+ *               fixed = atom on the anchor side (torsion.py:305), moving = the other atom
+ *   tors_mask_h [T, ceil(M/64)]  atoms on the moving side (bit i of word i/64)
+ *   tors_snap_h [T]    1 = both atoms C2/N2: allele <= 0 -> 0 deg else 180 (torsion.py:159-160)
+ *   tors_src_h  [T]    >= 0: column of torsion_deg_d driving this bond;
+ *                      <  0: rotamer driven, residue r and chi k with -(1 + 4 r + k)
+ *   excl_mask_h [M, ceil(M/64)]  atoms within <= bond_separation bonds (DetectClash exclusion)
+ *   origin_atom        Search target atom (search.py:186-188)
+ *   torsion_before_search  1 if Torsion is listed before Search in the YAML (base.py:157-168)
+ */
+int gmm_set_mobile(gmm_ctx* ctx, int M,
+                   const double* xyz0_h, const float* radius_h, const uint8_t* flags_h,
+                   int T, const int32_t* tors_fixed_h, const int32_t* tors_moving_h,
+                   const uint64_t* tors_mask_h, const uint8_t* tors_snap_h,
+                   const int32_t* tors_src_h, const uint64_t* excl_mask_h,
+                   int origin_atom, int torsion_before_search);
+
+/* Rotamer chi tables (gaudi/genes/rotamers.py:141-152,165-189): residue r owns rows
+ * rot_ptr_h[r] .. rot_ptr_h[r+1] of rot_delta_h [rows,4] = (chi - chi0) in degrees, sorted
+ * as the reference sorts its library.  Allele a in [0,1) selects row int(a * n_rows). */
+int gmm_set_rotamers(gmm_ctx* ctx, int n_res, const int32_t* rot_ptr_h, const double* rot_delta_h);
+
+/* Every atom with fixed coordinates (all other atoms of all Molecule genes).  Replaces the
+ * chimera.specifier.zone / DetectClash spatial searches of contacts.py:140-146,190-213.
+ *   rr_ptr_h/rr_idx_h  CSR over static atoms a of partners b > a that are more than
+ *                      bond_separation bonds apart and close enough to ever be reported;
+ *                      their score contributions are computed on the device.
+ *   ms_ptr_h/ms_idx_h  CSR over MOBILE atoms of static atoms within <= bond_separation
+ *                      bonds (only with flexible side chains; may be NULL).
+ *   centre_h[3]        origin of the fp32 device frame (e.g. the Search centre).
+ * Requires gmm_set_params() first (the static pair values depend on the thresholds). */
+int gmm_set_receptor(gmm_ctx* ctx, int R,
+                     const double* xyz_h, const float* radius_h, const uint8_t* flags_h,
+                     const int32_t* rr_ptr_h, const int32_t* rr_idx_h,
+                     const int32_t* ms_ptr_h, const int32_t* ms_idx_h,
+                     const double* centre_h);
+
+/* Contacts objective settings (contacts.py:101-121) and DetectClash's fixed options
+ * (contacts.py:142-145).  `cutoff`/`weight`: evaluate_clashes' penalty (contacts.py:132-133). */
+int gmm_set_params(gmm_ctx* ctx, double zone_radius, double clash_threshold,
+                   double hydrophobic_threshold, double hbond_allowance,
+                   double assumed_max_vdw, double cutoff, double weight, int options);
+
+/* Batched hot path (device pointers) --------------------------------------------- */
+
+/* Individual.express() for P individuals at once: Rotamers.express (rotamers.py:141-152),
+ * Torsion.express (torsion.py:153-164), Search.express (search.py:201-214) and the
+ * coordinate read-back of MolecularIndividual.post_express (base.py:301-303).
+ *   torsion_deg_d [P, n_allele_torsions] fp64 degrees (may be NULL if none)
+ *   xform_d       [P, 12] fp64 row-major 3x4 product T.R of the Search allele (NULL = identity)
+ *   rot_allele_d  [P, n_res] fp64 in [0,1) (NULL if no rotamers)
+ *   out_xyz_d     [P, M, 3] fp32, device frame */
+int gmm_express(gmm_ctx* ctx, int P, const double* torsion_deg_d, const double* xform_d,
+                const double* rot_allele_d, float* out_xyz_d, void* stream);
+
+/* Contacts.evaluate_clashes and Contacts.evaluate_hydrophobic (contacts.py:129-138) for P
+ * expressed individuals.
+ *   xyz_d        [P, M, 3] fp32 device-frame coordinates of the mobile atoms
+ *   out_scores_d [P, 2] fp64 = (clashes, hydrophobic), before the caller's round()
+ *   out_counts_d [P, 2] int32 = unique (clash, hydrophobic) pairs counted, or NULL */
+int gmm_contacts(gmm_ctx* ctx, int P, const float* xyz_d, double* out_scores_d,
+                 int32_t* out_counts_d, void* stream);
+
+/* Environment.evaluate (base.py:353-364) for the whole population: express + Contacts.
+ * out_xyz_d may be NULL (coordinates then live only in the context's scratch). */
+int gmm_evaluate(gmm_ctx* ctx, int P, const double* torsion_deg_d, const double* xform_d,
+                 const double* rot_allele_d, float* out_xyz_d, double* out_scores_d,
+                 int32_t* out_counts_d, void* stream);
+
+/* Same as gmm_evaluate with HOST buffers: copies alleles in, runs, copies scores (and
+ * coordinates if out_xyz_h != NULL) back, and synchronises the stream before returning.
+ * This is what toolbox.map(toolbox.evaluate, population) (algorithms.py:99-102) binds to. */
+int gmm_evaluate_host(gmm_ctx* ctx, int P, const double* torsion_deg_h, const double* xform_h,
+                      const double* rot_allele_h, float* out_xyz_h, double* out_scores_h,
+                      int32_t* out_counts_h, void* stream);
+
+/* gaudi.similarity.rmsd / _rmsd_squared (similarity.py:36-75) for rows [row0,row1) of the
+ * all-pairs matrix of N conformers x A atoms (no superposition).
+ *   xyz_d            [N, A, 3] fp32 (same frame for all conformers)
+ *   out_rmsd_d       [row1-row0, N] fp32 RMSD values, or NULL
+ *   out_similar_d    [row1-row0, ceil(N/32)] uint32 bitmask of NOT(rmsd^2 > thr^2), or NULL */
+int gmm_rmsd_matrix(gmm_ctx* ctx, int N, int A, const float* xyz_d, int row0, int row1,
+                    float* out_rmsd_d, uint32_t* out_similar_d, double threshold, void* stream);
+
+/* Parity / debugging: the pair lists the Contacts score of ONE individual is made of
+ * (what Contacts.find_interactions returns, contacts.py:140-146).  Atom ids: mobile atoms
+ * 0..M-1, static atoms M..M+R-1 (caller's receptor order).  kind: 0 = clash (volume),
+ * 1 = hydrophobic (LJ).  Synchronises.  Returns the number of pairs via n_out_h (may exceed
+ * max_pairs; only max_pairs are written). */
+int gmm_contacts_pairs(gmm_ctx* ctx, const float* xyz_one_d, int max_pairs,
+                       int32_t* out_pairs_h /*[max,2]*/, int32_t* out_kind_h /*[max]*/,
+                       double* out_overlap_h /*[max]*/, double* out_value_h /*[max]*/,
+                       int* n_out_h, void* stream);
+
+/* Measurement helpers ------------------------------------------------------------ */
+/* Dependent-free FFMA loop; returns achieved FP32 TFLOP/s (the roofline denominator that
+ * MEASURED_PEAKS.json does not carry).  Synchronises. */
+int gmm_measure_fp32_peak(int device, double* tflops_out);
+/* Pair tests executed by the last gmm_contacts/gmm_evaluate on this context (receptor
+ * tiles that survived culling x mobile atoms + intra-mobile pairs).  Synchronises. */
+int gmm_last_pair_tests(gmm_ctx* ctx, unsigned long long* n_out);
+/* Kernel launches issued by this library since load (for bench.py's gpu_launches). */
+unsigned long long gmm_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAUDIMM_B200_H */

