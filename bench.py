@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""Benchmark of the GaudiMM hot path on B200: individuals scored / s for
+express (Torsion + Search) + Contacts (clashes and hydrophobic), plus RMSD pairs / s.
+
+    python bench.py --gpus N --steps K --warmup W              # the B200 path (this repo)
+    python bench.py --impl reference --gpus N --steps K ...    # the reference's CPU path
+
+One "step" = one batched evaluate of the whole population (BASELINE.json configs[2]:
+65,536 poses of a 40-atom / 10-torsion ligand against a 20,000-atom receptor box; with N
+GPUs the population is sharded by individual and the fitness vectors are all-gathered).
+Prints ONE JSON line on rank 0.  See DESIGN.md section "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (population, ligand atoms, torsions, receptor atoms)
+    "c3": (65536, 40, 10, 20000),   # BASELINE.json configs[2] -- the headline
+    "c2": (4096, 40, 10, 5000),     # BASELINE.json configs[1]
+}
+RMSD_N, RMSD_A = 16384, 60          # BASELINE.json configs[3]
+FLOPS_PER_PAIR_TEST = 10
+FLOPS_PER_RMSD_PAIR = 9 * RMSD_A    # 3A FADD + 3A FFMA
+
+
+def build_system(name):
+    from gaudi_b200 import model as M, synth
+    pop, L, T, R = WORKLOADS[name]
+    params = M.ContactParams()
+    lig = synth.make_ligand(L, T, seed=1)
+    rec = synth.make_receptor(R, seed=2, params=params)
+    tors, xf = synth.make_alleles(pop, T, seed=3)
+    return params, lig, rec, tors, xf
+
+
+# ------------------------------------------------------------------------------------
+# CPU baseline: the oracle (a numpy/scipy port of the reference's CPU path) on host cores
+# ------------------------------------------------------------------------------------
+_W = {}
+
+
+def _cpu_init(name):
+    import oracle_adapter as OA
+    params, lig, rec, tors, xf = build_system(name)
+    _W.update(OA=OA, params=params, lig=lig, rec=rec, tors=tors, xf=xf)
+
+
+def _cpu_eval(rng):
+    OA, lig = _W["OA"], _W["lig"]
+    out = []
+    for p in range(rng[0], rng[1]):
+        x = OA.express(lig, _W["tors"][p], _W["xf"][p])
+        r = OA.contacts(lig, _W["rec"], _W["params"], x, with_slack=False)
+        out.append((r.clash, r.hydro))
+    return out
+
+
+class CpuPool(object):
+    def __init__(self, name, cores):
+        import multiprocessing as mp
+        self.cores = cores
+        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ.setdefault(var, "1")      # one process per core, no nested BLAS threads
+        # spawn: the parent may hold a CUDA context, which must not be forked
+        self.pool = mp.get_context("spawn").Pool(cores, initializer=_cpu_init, initargs=(name,))
+        self.pool.map(_cpu_eval, [(0, 1)] * cores)       # warm every worker
+
+    def run(self, start, count):
+        per = max(1, count // (self.cores * 4))
+        chunks = [(a, min(a + per, start + count)) for a in range(start, start + count, per)]
+        t0 = time.perf_counter()
+        res = self.pool.map(_cpu_eval, chunks)
+        dt = time.perf_counter() - t0
+        return dt, [s for c in res for s in c]
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+# ------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        threading.Thread.__init__(self, daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._halt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        while not self._halt.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, nm in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from gaudi_b200 import model as M
+    from gaudi_b200.engine import Engine, measure_fp32_peak, launch_count
+    from gaudi_b200 import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    name = args.workload
+    pop, L, T, R = WORKLOADS[name]
+    params, lig, rec, tors, xf = build_system(name)
+    # shard by individual: contiguous blocks, the last ranks may hold one fewer
+    bounds = [(pop * r) // world for r in range(world + 1)]
+    lo, hi = bounds[rank], bounds[rank + 1]
+    shard = hi - lo
+    max_shard = max(bounds[r + 1] - bounds[r] for r in range(world))
+
+    eng = Engine(lig, rec, params, device=local)
+    eng.reserve(max_shard)
+    eng.set_profiling(True)
+    t_d = torch.as_tensor(tors[lo:hi]).to(dev)
+    x_d = torch.as_tensor(xf[lo:hi]).to(dev)
+    scores = torch.empty((max_shard, 2), dtype=torch.float64, device=dev)
+    counts = torch.empty((max_shard, 2), dtype=torch.int32, device=dev)
+    gathered = torch.empty((world * max_shard, 2), dtype=torch.float64, device=dev) if world > 1 else None
+    flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step():
+        eng.evaluate(t_d, x_d, counts=True, scores_out=scores[:shard], counts_out=counts[:shard])
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, scores)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    peak32 = measure_fp32_peak(local)          # FP32 roofline denominator, measured here
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sweep_ms, expr_ms, fin_ms = [], [], []
+    barrier()
+    for k in range(args.steps):
+        flush.fill_(k & 0xff)                  # evict L2 between timed iterations
+        ev[k][0].record()
+        step()
+        ev[k][1].record()
+        kt = eng.kernel_times()                # synchronises; outside the event pair
+        sweep_ms.append(kt["sweep"]); expr_ms.append(kt["express"]); fin_ms.append(kt["finalize"])
+    barrier()
+    launches = launch_count() - launches0 - 0
+    clocks = sampler.stop()
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = pop / (ms_per_step * 1e-3)
+
+    # roofline of the dominant kernel (contacts sweep), executed pair tests
+    tests = eng.last_pair_tests()
+    sweep = float(np.mean(sweep_ms))
+    achieved = tests * FLOPS_PER_PAIR_TEST / (sweep * 1e-3) / 1e12
+    dense_flops_per_ind = FLOPS_PER_PAIR_TEST * (L * R + L * (L - 1) // 2)
+
+    # e2e: host buffers through the C ABI (H2D alleles, kernels, D2H scores) per step
+    th, xh = np.ascontiguousarray(tors[lo:hi]), np.ascontiguousarray(xf[lo:hi])
+    eng.evaluate_host(th, xh)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_e2e = max(3, min(args.steps, 10))
+    e0.record()
+    for _ in range(n_e2e):
+        s_h, c_h, _ = eng.evaluate_host(th, xh)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, scores)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / n_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+    h2d = int(th.nbytes + xh.nbytes)
+    d2h = int(s_h.nbytes + c_h.nbytes)
+
+    extra = {}
+    if rank == 0 and world == 1 and not args.quick:
+        extra = side_measurements(eng, torch, dev, peak32)
+
+    out = None
+    if rank == 0:
+        out = {
+            "metric": "individuals scored/sec (expr + Contacts)", "value": value, "unit": "individuals/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "configs[2]: pop %d x (%d-atom, %d-torsion ligand) vs %d-atom receptor box, "
+                                   "Torsion+Search express + Contacts(clashes, hydrophobic)" % (pop, L, T, R),
+                       "sharding": "by individual, %d per GPU, NCCL all_gather of fitness" % max_shard if world > 1
+                       else "single GPU",
+                       "l2": "192 MiB buffer written between timed iterations",
+                       "culling": "receptor tiles out of reach of a pose are skipped (results bit-identical to dense)"},
+            "roofline": {"bound": "fp32", "kernel": "contacts_sweep_kernel", "achieved": achieved, "peak": peak32,
+                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None, "traffic": None,
+                         "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
+                         "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
+                         "kernel_ms": sweep, "express_ms": float(np.mean(expr_ms)), "finalize_ms": float(np.mean(fin_ms)),
+                         "dense_flops_per_individual": dense_flops_per_ind,
+                         "executed_fraction_of_dense": tests * FLOPS_PER_PAIR_TEST / (dense_flops_per_ind * shard)},
+            "e2e": {"value": pop / (e2e_ms * 1e-3), "unit": "individuals/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        out.update(extra)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(name, args.cpu_sample)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+def side_measurements(eng, torch, dev, peak32):
+    """Dense (no culling) figure on the same workload, configs[1], and the RMSD matrix of
+    configs[3]; reported next to the headline, same timing rules."""
+    from gaudi_b200 import model as M, synth
+    from gaudi_b200.engine import Engine
+    res = {}
+
+    def timed(fn, reps):
+        fn(); fn(); fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    # dense on the headline workload
+    pop, L, T, R = WORKLOADS["c3"]
+    dense = Engine(eng.mobile, eng.receptor, M.ContactParams(cull=False), device=eng.device)
+    dense.set_profiling(True)
+    tors, xf = synth.make_alleles(pop, T, seed=3)
+    t_d, x_d = torch.as_tensor(tors).to(dev), torch.as_tensor(xf).to(dev)
+    ms = timed(lambda: dense.evaluate(t_d, x_d), 3)
+    kt = dense.kernel_times()
+    tests = dense.last_pair_tests()
+    ach = tests * FLOPS_PER_PAIR_TEST / (kt["sweep"] * 1e-3) / 1e12
+    res["dense"] = {"value": pop / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms,
+                    "roofline": {"achieved": ach, "peak": peak32, "frac": ach / peak32, "unit": "TFLOP/s",
+                                 "kernel_ms": kt["sweep"], "pair_tests_per_launch": tests}}
+    dense.close()
+    # configs[1]
+    params, lig, rec, tors, xf = build_system("c2")
+    e2 = Engine(lig, rec, params, device=eng.device)
+    t_d, x_d = torch.as_tensor(tors).to(dev), torch.as_tensor(xf).to(dev)
+    ms = timed(lambda: e2.evaluate(t_d, x_d), 20)
+    res["configs1_pop4096_rec5k"] = {"value": tors.shape[0] / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms}
+    e2.close()
+    # configs[3]: RMSD matrix, bitmask output (what niching consumes)
+    conf = torch.as_tensor(synth.make_conformers(RMSD_N, RMSD_A, seed=4), dtype=torch.float32).to(dev)
+    bits = torch.empty((RMSD_N, RMSD_N // 32), dtype=torch.int32, device=dev)
+    from gaudi_b200 import _lib
+    import ctypes as C
+
+    def rm():
+        _lib.check(eng._L.gmm_rmsd_matrix(eng._h, RMSD_N, RMSD_A, C.c_void_p(conf.data_ptr()), 0, RMSD_N, None,
+                                          C.c_void_p(bits.data_ptr()), 2.5, eng._stream()))
+    ms = timed(rm, 5)
+    ordered = RMSD_N * RMSD_N
+    ach = ordered * FLOPS_PER_RMSD_PAIR / (ms * 1e-3) / 1e12
+    res["rmsd"] = {"metric": "RMSD pairs/s", "value": (RMSD_N * (RMSD_N - 1) // 2) / (ms * 1e-3),
+                   "unit": "unique pairs/s", "ms": ms, "n_conformers": RMSD_N, "atoms": RMSD_A,
+                   "note": "full N x N matrix computed (every unordered pair twice); value counts unique pairs",
+                   "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "frac": ach / peak32,
+                                "unit": "TFLOP/s", "flops_per_pair": FLOPS_PER_RMSD_PAIR}}
+    return res
+
+
+def cpu_baseline(name, sample):
+    cores = os.cpu_count() or 1
+    pool = CpuPool(name, cores)
+    dt, _ = pool.run(0, sample)
+    pool.close()
+    return {"value": sample / dt, "unit": "individuals/s", "cores": cores, "kind": "port",
+            "sample": "first %d individuals of the same population, numpy/scipy fp64 oracle "
+                      "(express + zone + DetectClash rule + scoring), %d processes, %.1f s" % (sample, cores, dt)}
+
+
+# ------------------------------------------------------------------------------------
+# reference arm: the reference's CPU path (oracle port; Chimera itself cannot run here)
+# ------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    name = args.workload
+    pop, L, T, R = WORKLOADS[name]
+    cores = os.cpu_count() or 1
+    pool = CpuPool(name, cores)
+    per_step = max(cores * 8, min(args.cpu_sample, 4096) // max(1, args.steps))
+    for w in range(min(args.warmup, 1)):
+        pool.run(0, per_step)
+    total = 0.0
+    for k in range(args.steps):
+        dt, _ = pool.run((k * per_step) % (pop - per_step), per_step)
+        total += dt
+    pool.close()
+    value = per_step * args.steps / total
+    sample = ("each step = %d individuals of the %d-individual population; numpy/scipy fp64 port of the "
+              "reference's Chimera-based CPU path (the reference itself needs UCSF Chimera + Python 2 and "
+              "cannot run on this box), %d processes" % (per_step, pop, cores))
+    out = {"impl": "reference", "metric": "individuals scored/sec (expr + Contacts)", "value": value,
+           "unit": "individuals/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": "configs[2]: pop %d x (%d-atom, %d-torsion ligand) vs %d-atom receptor box, "
+                                  "Torsion+Search express + Contacts(clashes, hydrophobic)" % (pop, L, T, R)},
+           "cpu_baseline": {"value": value, "unit": "individuals/s", "cores": cores, "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": "individuals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-sample", type=int, default=2048, help="individuals in the CPU baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--quick", action="store_true", help="skip the dense / configs[1] / RMSD side measurements")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

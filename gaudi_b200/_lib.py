@@ -36,6 +36,8 @@ SIGNATURES = {
     "gmm_contacts_pairs": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, C.POINTER(_i), _vp]),
     "gmm_measure_fp32_peak": (_i, [_i, C.POINTER(_d)]),
     "gmm_last_pair_tests": (_i, [_vp, C.POINTER(C.c_ulonglong)]),
+    "gmm_set_profiling": (_i, [_vp, _i]),
+    "gmm_kernel_times": (_i, [_vp, C.POINTER(C.c_float)]),
     "gmm_launch_count": (C.c_ulonglong, []),
 }
 

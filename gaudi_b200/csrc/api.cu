@@ -112,6 +112,7 @@ int gmm_destroy(gmm_ctx* c) {
     if (c->d_scratch) cudaFree(c->d_scratch);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->h_pin) cudaFreeHost(c->h_pin);
+    for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     delete c;
     return GMM_OK;
 }
@@ -456,6 +457,28 @@ int gmm_contacts_pairs(gmm_ctx* c, const float* xyz_one_d, int max_pairs, int32_
     REQUIRE(max_pairs == 0 || (out_pairs_h && out_kind_h && out_overlap_h && out_value_h), GMM_EINVAL, "gmm_contacts_pairs: NULL output");
     DeviceGuard g(c->device);
     return launch_pairs_dump(c, xyz_one_d, max_pairs, out_pairs_h, out_kind_h, out_overlap_h, out_value_h, n_out_h, (cudaStream_t)stream);
+}
+
+int gmm_set_profiling(gmm_ctx* c, int on) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_profiling: ctx is NULL");
+    DeviceGuard g(c->device);
+    if (on && !c->ev[0])
+        for (int k = 0; k < 6; ++k) GMM_CUDA(cudaEventCreate(&c->ev[k]));
+    c->prof = on != 0;
+    for (int k = 0; k < 3; ++k) c->ev_used[k] = false;
+    return GMM_OK;
+}
+
+int gmm_kernel_times(gmm_ctx* c, float* ms_out) {
+    REQUIRE(c && ms_out, GMM_EINVAL, "gmm_kernel_times: NULL argument");
+    REQUIRE(c->ev[0], GMM_ESTATE, "gmm_kernel_times: profiling was never enabled");
+    DeviceGuard g(c->device);
+    GMM_CUDA(cudaDeviceSynchronize());
+    for (int k = 0; k < 3; ++k) {
+        ms_out[k] = 0.f;
+        if (c->ev_used[k]) GMM_CUDA(cudaEventElapsedTime(&ms_out[k], c->ev[2 * k], c->ev[2 * k + 1]));
+    }
+    return GMM_OK;
 }
 
 int gmm_last_pair_tests(gmm_ctx* c, unsigned long long* n_out) {

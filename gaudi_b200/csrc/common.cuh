@@ -164,6 +164,10 @@ struct gmm_ctx {
     // scratch (grown on demand)
     void* d_scratch = nullptr; size_t scratch_bytes = 0;
     unsigned long long* d_counters = nullptr;   // [4] pair tests, ...
+    // optional per-kernel timing (gmm_set_profiling): events around express / sweep / finalize
+    bool prof = false;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool ev_used[3] = {false, false, false};
     // pinned staging for gmm_evaluate_host
     void* h_pin = nullptr; size_t pin_bytes = 0;
     void* d_stage = nullptr; size_t stage_bytes = 0;

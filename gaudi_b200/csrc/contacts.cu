@@ -584,8 +584,10 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
             attr = true;
         }
         dim3 grid(a.n_chunks, (P + kGroup - 1) / kGroup);
+        if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
         contacts_sweep_kernel<<<grid, kSweepWarps * 32, smem, s>>>(a);
         GMM_LAUNCH_CHECK("contacts_sweep_kernel");
+        if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[3], s)); c->ev_used[1] = true; }
     }
     FinArgs f;
     f.s = a; f.mm_pairs = c->d_mm_pairs; f.n_mm = c->n_mm;
@@ -598,8 +600,10 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
         GMM_CUDA(cudaFuncSetAttribute(contacts_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         fattr = true;
     }
+    if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[4], s));
     contacts_finalize_kernel<<<(P + kFinWarps - 1) / kFinWarps, kFinWarps * 32, fsmem, s>>>(f);
     GMM_LAUNCH_CHECK("contacts_finalize_kernel");
+    if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[5], s)); c->ev_used[2] = true; }
     return GMM_OK;
 }
 

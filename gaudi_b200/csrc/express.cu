@@ -135,8 +135,10 @@ int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, c
     int blocks = (P + kExprWarps - 1) / kExprWarps;
     const int cap = 148 * 16;
     if (blocks > cap) blocks = cap;
+    if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[0], s));
     express_kernel<<<blocks, kExprWarps * 32, smem, s>>>(a);
     GMM_LAUNCH_CHECK("express_kernel");
+    if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[1], s)); c->ev_used[0] = true; }
     return GMM_OK;
 }
 

@@ -183,6 +183,15 @@ class Engine(object):
         k = min(n.value, max_pairs)
         return [(int(pairs[i, 0]), int(pairs[i, 1]), int(kind[i]), float(ov[i]), float(val[i])) for i in range(k)]
 
+    def set_profiling(self, on=True):
+        _lib.check(self._L.gmm_set_profiling(self._h, int(bool(on))))
+
+    def kernel_times(self):
+        """Durations in ms of the last express / sweep / finalize kernels (profiling on)."""
+        ms = (C.c_float * 3)()
+        _lib.check(self._L.gmm_kernel_times(self._h, ms))
+        return {"express": ms[0], "sweep": ms[1], "finalize": ms[2]}
+
     def last_pair_tests(self):
         n = C.c_ulonglong(0)
         _lib.check(self._L.gmm_last_pair_tests(self._h, C.byref(n)))

@@ -270,6 +270,92 @@ def build_receptor(xyz, radius, flags, bonds, params, centre=None):
                          centre=np.ascontiguousarray(centre, dtype=np.float64))
 
 
+def split_molecule(xyz, radius, flags, bonds, mobile_idx, params, rotatable=(), origin_atom=None,
+                   centre=None, **mobile_kw):
+    """Split one bonded system into a mobile part (atoms ``mobile_idx``, in that order) and
+    a static part (everything else), keeping DetectClash's bond-separation exclusions across
+    the cut (``ms_excl``).  This is how flexible side chains of a Rotamers gene sit next to
+    the rest of their protein.  ``rotatable`` uses indices of the *whole* system.
+    Returns ``(MobileModel, ReceptorModel, static_idx)``."""
+    xyz = np.asarray(xyz, dtype=np.float64)
+    n = xyz.shape[0]
+    bonds = np.asarray(bonds, dtype=np.int64).reshape(-1, 2)
+    mobile_idx = np.asarray(mobile_idx, dtype=np.int64)
+    is_mobile = np.zeros(n, dtype=bool)
+    is_mobile[mobile_idx] = True
+    static_idx = np.flatnonzero(~is_mobile)
+    to_m = -np.ones(n, dtype=np.int64)
+    to_m[mobile_idx] = np.arange(len(mobile_idx))
+    to_s = -np.ones(n, dtype=np.int64)
+    to_s[static_idx] = np.arange(len(static_idx))
+    mm = bonds[is_mobile[bonds[:, 0]] & is_mobile[bonds[:, 1]]]
+    ss = bonds[~is_mobile[bonds[:, 0]] & ~is_mobile[bonds[:, 1]]]
+    cross = bonds[is_mobile[bonds[:, 0]] != is_mobile[bonds[:, 1]]]
+    # rotatable bonds may have their fixed atom in the static part: the moving side is then
+    # computed on the full graph and must lie entirely in the mobile part
+    adj = adjacency(n, bonds)
+    m = len(mobile_idx)
+    words = (m + 63) // 64
+    mob = build_mobile(xyz[mobile_idx], np.asarray(radius)[mobile_idx], np.asarray(flags)[mobile_idx],
+                       np.stack([to_m[mm[:, 0]], to_m[mm[:, 1]]], axis=1) if len(mm) else np.zeros((0, 2), np.int32),
+                       [], origin_atom=0 if origin_atom is None else int(to_m[origin_atom]),
+                       bond_separation=params.bond_separation, **mobile_kw)
+    if len(rotatable):
+        fixed, moving, masks = [], [], []
+        for fx, mv in rotatable:
+            side = side_of_bond(adj, int(fx), int(mv))
+            if not all(is_mobile[a] for a in side):
+                raise ValueError("moving side of bond %d-%d leaves the mobile part" % (fx, mv))
+            if to_m[fx] < 0:
+                raise ValueError("fixed atom %d of a rotatable bond must be in the mobile part "
+                                 "(add it to mobile_idx; it never moves)" % fx)
+            fixed.append(int(to_m[fx])); moving.append(int(to_m[mv]))
+            masks.append(bitmask([int(to_m[a]) for a in side], m))
+        mob.tors_fixed = np.asarray(fixed, np.int32)
+        mob.tors_moving = np.asarray(moving, np.int32)
+        mob.tors_mask = np.asarray(masks, np.uint64).reshape(len(fixed), words)
+        mob.tors_snap = np.zeros(len(fixed), np.uint8)
+        if "tors_src" not in mobile_kw or mobile_kw["tors_src"] is None:
+            mob.tors_src = np.arange(len(fixed), dtype=np.int32)
+    # exclusions across the cut, on the full graph
+    excl = np.zeros((m, words), dtype=np.uint64)
+    ms_ptr = np.zeros(m + 1, dtype=np.int32)
+    ms_idx = []
+    for k, a in enumerate(mobile_idx):
+        near = within_bonds(adj, int(a), params.bond_separation)
+        excl[k] = bitmask([int(to_m[b]) for b in near if is_mobile[b]], m)
+        ms_idx.extend(sorted(int(to_s[b]) for b in near if not is_mobile[b]))
+        ms_ptr[k + 1] = len(ms_idx)
+    mob.excl_mask = excl
+    rec = build_receptor(xyz[static_idx], np.asarray(radius)[static_idx], np.asarray(flags)[static_idx],
+                         np.stack([to_s[ss[:, 0]], to_s[ss[:, 1]]], axis=1) if len(ss) else np.zeros((0, 2), np.int32),
+                         params, centre=xyz.mean(axis=0) if centre is None else centre)
+    # static-static exclusions must also see paths that run through mobile atoms
+    if len(cross) and len(rec.rr_idx):
+        keep = np.ones(len(rec.rr_idx), dtype=bool)
+        touched = {int(to_s[b]) for a in mobile_idx for b in within_bonds(adj, int(a), params.bond_separation)
+                   if not is_mobile[b]}
+        for sa in touched:
+            near = within_bonds(adj, int(static_idx[sa]), params.bond_separation)
+            for e in range(rec.rr_ptr[sa], rec.rr_ptr[sa + 1]):
+                if int(static_idx[rec.rr_idx[e]]) in near:
+                    keep[e] = False
+        for sb in touched:          # rows a < b where b is the touched atom
+            near = within_bonds(adj, int(static_idx[sb]), params.bond_separation)
+            for sa in {int(to_s[x]) for x in near if not is_mobile[x]}:
+                for e in range(rec.rr_ptr[sa], rec.rr_ptr[sa + 1]):
+                    if rec.rr_idx[e] == sb:
+                        keep[e] = False
+        counts = np.array([keep[rec.rr_ptr[a]:rec.rr_ptr[a + 1]].sum() for a in range(rec.n_atoms)])
+        rec.rr_idx = rec.rr_idx[keep]
+        rec.rr_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    rec.ms_excl_ptr = ms_ptr
+    rec.ms_excl_idx = np.asarray(ms_idx, dtype=np.int32)
+    rec.ms_bonds = np.array([(to_m[a], to_s[b]) if is_mobile[a] else (to_m[b], to_s[a]) for a, b in cross],
+                            dtype=np.int32).reshape(-1, 2)
+    return mob, rec, static_idx
+
+
 def empty_receptor(centre=(0.0, 0.0, 0.0)):
     return ReceptorModel(xyz=np.zeros((0, 3)), radius=np.zeros(0), flags=np.zeros(0, np.uint8),
                          bonds=np.zeros((0, 2), np.int32), rr_ptr=np.zeros(1, np.int32),

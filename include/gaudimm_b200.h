@@ -170,6 +170,11 @@ int gmm_measure_fp32_peak(int device, double* tflops_out);
 /* Pair tests executed by the last gmm_contacts/gmm_evaluate on this context (receptor
  * tiles that survived culling x mobile atoms + intra-mobile pairs).  Synchronises. */
 int gmm_last_pair_tests(gmm_ctx* ctx, unsigned long long* n_out);
+/* Per-kernel timing for roofline reports: when on, CUDA events are recorded around the
+ * express, Contacts-sweep and Contacts-finalize kernels on the caller's stream;
+ * gmm_kernel_times() synchronises and returns the durations (ms) of the LAST call of each. */
+int gmm_set_profiling(gmm_ctx* ctx, int on);
+int gmm_kernel_times(gmm_ctx* ctx, float* ms_out /*[3] express, sweep, finalize*/);
 /* Kernel launches issued by this library since load (for bench.py's gpu_launches). */
 unsigned long long gmm_launch_count(void);
 
