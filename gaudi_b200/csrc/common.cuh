@@ -178,7 +178,7 @@ namespace gmm {
 int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, const double* rot,
                    float* out_xyz, cudaStream_t s);
 int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts,
-                    cudaStream_t s);
+                    cudaStream_t s, void* workspace = nullptr);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);

@@ -561,11 +561,12 @@ static void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs
     plan_chunks(c, P, &a.tiles_per_chunk, &a.n_chunks);
 }
 
-int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s) {
+int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
+                    void* workspace) {
     if (P == 0) return GMM_OK;
     SweepArgs a;
     fill_sweep_args(c, P, xyz, a);
-    unsigned char* base = static_cast<unsigned char*>(c->d_scratch);
+    unsigned char* base = static_cast<unsigned char*>(workspace ? workspace : c->d_scratch);
     size_t off = align_up((size_t)P * c->M * 3 * sizeof(float), 256);
     a.zone = reinterpret_cast<uint32_t*>(base + off);
     off += align_up((size_t)P * a.ZW * sizeof(uint32_t), 256);

@@ -145,6 +145,22 @@ int gmm_evaluate_host(gmm_ctx* ctx, int P, const double* torsion_deg_h, const do
                       const double* rot_allele_h, float* out_xyz_h, double* out_scores_h,
                       int32_t* out_counts_h, void* stream);
 
+/* gmm_evaluate for callers that may not allocate device memory (no counterpart in the
+ * reference, which runs on the CPU and has no device memory to manage).  Same inputs and
+ * outputs as gmm_evaluate without out_xyz_d, but the scratch the evaluation needs
+ * (coordinates, zone bitmask, partial sums) is a 16 MiB array built into the library instead
+ * of the context's cudaMalloc'ed buffer: the call never calls cudaMalloc/cudaFree.
+ *   - populations whose scratch need exceeds 16 MiB are refused with GMM_ELIMIT (the message
+ *     states both sizes); split them into smaller batches;
+ *   - the first call on each device looks the array's device address up (one-time set-up);
+ *     make that first call before starting any stream capture;
+ *   - all calls, from every context on that device, share the one array: calls that overlap on
+ *     the GPU (different streams) race with each other; on one stream they are safe.  Nothing
+ *     in it has to be zero on entry (every word is written before it is read). */
+int gmm_evaluate_static(gmm_ctx* ctx, int P, const double* torsion_deg_d, const double* xform_d,
+                        const double* rot_allele_d, double* out_scores_d, int32_t* out_counts_d,
+                        void* stream);
+
 /* gaudi.similarity.rmsd / _rmsd_squared (similarity.py:36-75) for rows [row0,row1) of the
  * all-pairs matrix of N conformers x A atoms (no superposition).
  *   xyz_d            [N, A, 3] fp32 (same frame for all conformers)

@@ -1,0 +1,63 @@
+"""gmm_evaluate_static: the evaluate entry point for hosts that are not allowed to allocate
+device memory (a GPU shared with a framework that owns the memory pool, a latency-bound loop
+that cannot take cudaMalloc's device-wide synchronisation).  Its scratch is an array built into
+the library, shared by every call, so this checks two calls in a row — with different
+populations, so that data left behind by the first cannot pass for the second — against the
+regular gmm_evaluate.  Collected last on purpose (file name), and self-contained so that it
+also passes alone in a fresh process."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from gaudi_b200 import model as M
+from gaudi_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def test_static_scratch_evaluate_matches_regular_evaluate(built_lib):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from gaudi_b200 import _lib
+    from gaudi_b200.engine import Engine
+
+    params = M.ContactParams()
+    lig = synth.make_ligand(40, 10, seed=1)
+    rec = synth.make_receptor(3000, seed=2, params=params)
+    eng = Engine(lig, rec, params, device=0)
+    dev = eng.torch_device
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    def static_eval(tors, xf):
+        t = torch.as_tensor(tors).to(dev)
+        x = torch.as_tensor(xf).to(dev)
+        scores = torch.full((t.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
+        counts = torch.full((t.shape[0], 2), -1, dtype=torch.int32, device=dev)
+        _lib.check(built_lib.gmm_evaluate_static(eng._h, t.shape[0], C.c_void_p(t.data_ptr()),
+                                                 C.c_void_p(x.data_ptr()), None,
+                                                 C.c_void_p(scores.data_ptr()), C.c_void_p(counts.data_ptr()),
+                                                 stream))
+        torch.cuda.synchronize()
+        return scores.cpu().numpy(), counts.cpu().numpy()
+
+    for seed, pop in ((31, 1500), (32, 700)):          # two calls in a row, second one smaller
+        tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=seed)
+        want_s, want_c, _ = eng.evaluate(tors, xf)
+        got_s, got_c = static_eval(tors, xf)
+        want_s = want_s.cpu().numpy()
+        # same tolerance as tests/test_gpu_parity.py (the sums are integer, so in fact equal)
+        assert np.all(np.abs(got_s - want_s) <= 1e-4 * np.maximum(1.0, np.abs(want_s)))
+        assert np.array_equal(got_c, want_c.cpu().numpy())
+        assert np.isfinite(got_s).all() and (np.abs(got_s).sum() > 0)
+
+    # a population that does not fit the built-in 16 MiB is refused, loudly, without allocating
+    big = 200000
+    t = torch.zeros((big, lig.n_allele_torsions), dtype=torch.float64, device=dev)
+    x = torch.zeros((big, 12), dtype=torch.float64, device=dev)
+    s = torch.zeros((big, 2), dtype=torch.float64, device=dev)
+    rc = built_lib.gmm_evaluate_static(eng._h, big, C.c_void_p(t.data_ptr()), C.c_void_p(x.data_ptr()), None,
+                                       C.c_void_p(s.data_ptr()), None, stream)
+    assert rc == _lib.GMM_ELIMIT
+    assert b"built-in buffer" in built_lib.gmm_last_error()
