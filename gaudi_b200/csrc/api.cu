@@ -107,6 +107,7 @@ int gmm_destroy(gmm_ctx* c) {
     release(c->d_rot_ptr); release(c->d_rot_delta);
     release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
+    release(c->d_edge); release(c->d_sub_box);
     release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx);
     release(c->d_counters);
     if (c->d_scratch) cudaFree(c->d_scratch);
@@ -222,7 +223,7 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     REQUIRE(c, GMM_EINVAL, "gmm_set_receptor: ctx is NULL");
     REQUIRE(c->has_params, GMM_ESTATE, "gmm_set_receptor: call gmm_set_params first");
     REQUIRE(c->has_mobile, GMM_ESTATE, "gmm_set_receptor: call gmm_set_mobile first");
-    REQUIRE(R >= 0 && R < (1 << 24), GMM_ELIMIT, "gmm_set_receptor: R=%d outside [0,2^24)", R);
+    REQUIRE(R >= 0 && R < (1 << 22), GMM_ELIMIT, "gmm_set_receptor: R=%d outside [0,2^22)", R);
     REQUIRE(centre_h, GMM_EINVAL, "gmm_set_receptor: centre is NULL");
     REQUIRE(R == 0 || (xyz_h && radius_h && flags_h), GMM_EINVAL, "gmm_set_receptor: NULL array");
     DeviceGuard g(c->device);
@@ -231,35 +232,46 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     c->n_tiles = (R + kTileAtoms - 1) / kTileAtoms;
     c->Rpad = c->n_tiles * kTileAtoms;
 
-    // Morton order of the device-frame coordinates -> spatially compact 128-atom tiles
+    // Spatial order: recursive median bisection along the longest axis down to leaves of exactly
+    // 32 atoms ("sub-tiles", one atom per lane); four consecutive leaves form a 128-atom tile.
+    // Compact leaves are what makes the per-pose culling effective.
     std::vector<float> fx((size_t)R * 3);
-    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
     for (int i = 0; i < R; ++i)
-        for (int k = 0; k < 3; ++k) {
-            const float v = (float)(xyz_h[(size_t)i * 3 + k] - centre_h[k]);
-            fx[(size_t)i * 3 + k] = v;
-            lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v);
-        }
-    float span = 1e-6f;
-    for (int k = 0; k < 3; ++k) span = std::max(span, hi[k] - lo[k]);
-    std::vector<uint32_t> code(R);
-    for (int i = 0; i < R; ++i) {
-        uint32_t q[3];
-        for (int k = 0; k < 3; ++k) {
-            float t = (fx[(size_t)i * 3 + k] - lo[k]) / span * 1023.f;
-            q[k] = (uint32_t)std::min(1023.f, std::max(0.f, t));
-        }
-        code[i] = spread10(q[0]) | (spread10(q[1]) << 1) | (spread10(q[2]) << 2);
-    }
+        for (int k = 0; k < 3; ++k) fx[(size_t)i * 3 + k] = (float)(xyz_h[(size_t)i * 3 + k] - centre_h[k]);
     std::vector<int32_t> s2o(R);
     std::iota(s2o.begin(), s2o.end(), 0);
-    std::stable_sort(s2o.begin(), s2o.end(), [&](int a, int b) { return code[a] < code[b]; });
+    {
+        std::vector<std::pair<int, int>> stack;
+        stack.emplace_back(0, R);
+        while (!stack.empty()) {
+            const int lo_i = stack.back().first, hi_i = stack.back().second;
+            stack.pop_back();
+            const int n = hi_i - lo_i;
+            if (n <= kSubTile) continue;
+            float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+            for (int i = lo_i; i < hi_i; ++i)
+                for (int k = 0; k < 3; ++k) {
+                    const float v = fx[(size_t)s2o[i] * 3 + k];
+                    lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v);
+                }
+            int ax = 0;
+            for (int k = 1; k < 3; ++k) if (hi[k] - lo[k] > hi[ax] - lo[ax]) ax = k;
+            const int leaves = (n + kSubTile - 1) / kSubTile;
+            const int mid = lo_i + (leaves / 2) * kSubTile;
+            std::nth_element(s2o.begin() + lo_i, s2o.begin() + mid, s2o.begin() + hi_i, [&](int a, int b) {
+                const float va = fx[(size_t)a * 3 + ax], vb = fx[(size_t)b * 3 + ax];
+                return va < vb || (va == vb && a < b);
+            });
+            stack.emplace_back(lo_i, mid);
+            stack.emplace_back(mid, hi_i);
+        }
+    }
     std::vector<int32_t> o2s(R);
     for (int s = 0; s < R; ++s) o2s[s2o[s]] = s;
     c->h_sorted2orig = s2o;
 
-    std::vector<float4> rec(c->Rpad, make_float4(kFar, kFar, kFar, 0.f));
-    std::vector<uint8_t> rfl(c->Rpad, 0);
+    std::vector<float4> rec(c->Rpad + kSubTile, make_float4(kFar, kFar, kFar, 0.f));   // + one dummy sub-tile
+    std::vector<uint8_t> rfl(c->Rpad + kSubTile, 0);
     std::vector<float> box((size_t)c->n_tiles * 8, 0.f);
     std::vector<float4> sseed;
     float rmax = 0.f;
@@ -281,18 +293,35 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
             b[6] = std::max(b[6], rec[s].w);
         }
     }
+    // sub-tile (32-atom leaf) boxes; entry n_sub is the dummy far-away leaf used as padding
+    const int n_sub = c->Rpad / kSubTile;
+    std::vector<float> sbox((size_t)(n_sub + 1) * 8, 0.f);
+    for (int t = 0; t <= n_sub; ++t) {
+        float* b = &sbox[(size_t)t * 8];
+        b[0] = b[1] = b[2] = kFar; b[3] = b[4] = b[5] = kFar; b[6] = 0.f; b[7] = 0.f;
+        bool first = true;
+        for (int s = t * kSubTile; s < std::min(R, (t + 1) * kSubTile); ++s) {
+            if (first) { b[0] = b[3] = rec[s].x; b[1] = b[4] = rec[s].y; b[2] = b[5] = rec[s].z; first = false; }
+            b[0] = std::min(b[0], rec[s].x); b[3] = std::max(b[3], rec[s].x);
+            b[1] = std::min(b[1], rec[s].y); b[4] = std::max(b[4], rec[s].y);
+            b[2] = std::min(b[2], rec[s].z); b[5] = std::max(b[5], rec[s].z);
+            b[6] = std::max(b[6], rec[s].w);
+        }
+    }
     int rc;
+    if ((rc = upload(&c->d_sub_box, sbox.data(), sbox.size()))) return rc;
     if ((rc = upload(&c->d_rec4, rec.data(), rec.size()))) return rc;
     if ((rc = upload(&c->d_rflags, rfl.data(), rfl.size()))) return rc;
     if ((rc = upload(&c->d_tile_box, box.data(), box.size()))) return rc;
     c->n_sseed = (int)sseed.size();
     if ((rc = upload(&c->d_sseed, sseed.data(), sseed.size()))) return rc;
     release(c->d_always);
-    if (c->Rpad) GMM_CUDA(cudaMalloc((void**)&c->d_always, sizeof(uint32_t) * c->n_tiles * 4));
+    GMM_CUDA(cudaMalloc((void**)&c->d_always, sizeof(uint32_t) * (c->n_tiles * 4 + 1)));
+    GMM_CUDA(cudaMemset(c->d_always, 0, sizeof(uint32_t) * (c->n_tiles * 4 + 1)));
 
     // static-static candidate pairs -> sorted index space, row = smaller sorted index
     c->rr_nnz = 0;
-    release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
+    release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind); release(c->d_edge);
     if (R > 0 && rr_ptr_h && rr_idx_h && rr_ptr_h[R] > 0) {
         const int nnz = rr_ptr_h[R];
         std::vector<std::pair<int32_t, int32_t>> pr;
@@ -306,15 +335,17 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
             }
         std::sort(pr.begin(), pr.end());
         pr.erase(std::unique(pr.begin(), pr.end()), pr.end());
-        std::vector<int32_t> ptr(R + 1, 0), idx(pr.size());
+        // rows exist for the padding atoms too (empty), so that row sub*32 is always valid
+        std::vector<int32_t> ptr(c->Rpad + kSubTile + 1, 0), idx(pr.size());
         for (auto& p : pr) ptr[p.first + 1]++;
-        for (int a = 0; a < R; ++a) ptr[a + 1] += ptr[a];
+        for (int a = 0; a < c->Rpad + kSubTile; ++a) ptr[a + 1] += ptr[a];
         for (size_t e = 0; e < pr.size(); ++e) idx[e] = pr[e].second;
         c->rr_nnz = (int)pr.size();
         if ((rc = upload(&c->d_rr_ptr, ptr.data(), ptr.size()))) return rc;
         if ((rc = upload(&c->d_rr_idx, idx.data(), idx.size()))) return rc;
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_val, sizeof(long long) * 2 * pr.size()));
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_kind, pr.size()));
+        GMM_CUDA(cudaMalloc((void**)&c->d_edge, sizeof(uint32_t) * pr.size()));
     }
     // mobile-static exclusions (flexible side chains bonded to the static backbone)
     c->ms_nnz = 0;

@@ -35,6 +35,7 @@ extern unsigned long long g_launches;
 
 // ---- tunables ---------------------------------------------------------------------
 constexpr int kTileAtoms = 128;      // receptor atoms per tile (4 per lane)
+constexpr int kSubTile = 32;         // receptor atoms per sub-tile (k-d leaf), one per lane
 constexpr int kSweepWarps = 4;       // warps per sweep CTA
 constexpr int kGroup = 8;            // individuals per sweep CTA
 constexpr int kCandQ = 256;          // per-warp candidate queue entries
@@ -153,6 +154,8 @@ struct gmm_ctx {
     int32_t* d_rr_ptr = nullptr; int32_t* d_rr_idx = nullptr;   // sorted index space
     long long* d_rr_val = nullptr;   // [nnz,2] clash_fx, hydro_fx
     uint8_t* d_rr_kind = nullptr;    // [nnz]
+    uint32_t* d_edge = nullptr;      // [nnz]   b | a_local << 24 | kind << 29 (fused kernel)
+    float* d_sub_box = nullptr;      // [Rpad/32 + 1, 8] sub-tile boxes (last = dummy leaf)
     int rr_nnz = 0;
     float4* d_sseed = nullptr; int n_sseed = 0;                  // static zone seeds (CB atoms)
     int32_t* d_ms_ptr = nullptr; int32_t* d_ms_idx = nullptr;   // CSR over slots -> sorted static idx
@@ -179,6 +182,8 @@ int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, c
                    float* out_xyz, cudaStream_t s);
 int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts,
                     cudaStream_t s, void* workspace = nullptr);
+int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
+                          int* handled);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);

@@ -27,86 +27,9 @@
 //
 // Receptor tiles are Morton-sorted; a tile is skipped for an individual when its bounding
 // box is out of reach of the pose's bounding sphere (GMM_OPT_NO_CULL disables this).
-#include "common.cuh"
+#include "contacts_common.cuh"
 
 namespace gmm {
-
-struct SweepArgs {
-    int P, M, Mp, MW, n_seed, n_tiles, tiles_per_chunk, n_chunks, ZW, n_sseed, cull, all_seed;
-    const float* xyz;
-    const int32_t* slot2atom; const float* mrad; const uint8_t* mflags;
-    const float4* rec4; const uint8_t* rflags; const float* tile_box; const uint32_t* always;
-    const float4* sseed;
-    const int32_t* ms_ptr; const int32_t* ms_idx;
-    uint32_t* zone; long long* partial; unsigned long long* counters;
-    Params prm;
-    float rad2, thr_min, rmax_mobile, reach_extra;
-};
-
-__device__ __forceinline__ float dist2f(float ax, float ay, float az, float bx, float by, float bz) {
-    const float dx = ax - bx, dy = ay - by, dz = az - bz;
-    return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-}
-
-// fp32 pre-filter cutoff, slightly widened so that the fp64 decision in score_pair is the
-// only one that matters.
-__device__ __forceinline__ float loose_c2(float ri, float rj, float thr_min) {
-    const float c = ri + rj - thr_min;
-    return c * c * 1.000004f + 1e-6f;
-}
-
-__device__ __forceinline__ bool ms_excluded(const int32_t* ms_ptr, const int32_t* ms_idx, int slot, int j) {
-    if (ms_ptr == nullptr) return false;
-    for (int e = ms_ptr[slot]; e < ms_ptr[slot + 1]; ++e)
-        if (ms_idx[e] == j) return true;
-    return false;
-}
-
-// Shared-memory carve-up used by sweep, finalize and dump.
-struct LigSmem {
-    float4* lig;      // [G][Mp]
-    uint32_t* zm;     // [G][MW]  mobile atoms in zone
-};
-
-// Load G individuals' mobile atoms into slot order and decide which mobile atoms are in the zone.
-template <int THREADS>
-__device__ __forceinline__ void load_ligands(const SweepArgs& a, int p0, int Gn, float4* lig, uint32_t* zm) {
-    for (int idx = threadIdx.x; idx < Gn * a.Mp; idx += THREADS) {
-        const int g = idx / a.Mp, s = idx - g * a.Mp;
-        const int atom = a.slot2atom[s];
-        float4 v = make_float4(kFar, kFar, kFar, 0.f);
-        if (atom >= 0) {
-            const float* src = a.xyz + ((size_t)(p0 + g) * a.M + atom) * 3;
-            v = make_float4(src[0], src[1], src[2], a.mrad[s]);
-        }
-        lig[idx] = v;
-    }
-    __syncthreads();
-    // zone membership of mobile atoms: seeds always; others iff within radius of a seed
-    for (int idx = threadIdx.x; idx < Gn * a.MW; idx += THREADS) {
-        const int g = idx / a.MW, w = idx - g * a.MW;
-        uint32_t bits = 0;
-        for (int b = 0; b < 32; ++b) {
-            const int s = w * 32 + b;
-            if (s >= a.M) break;
-            bool in = s < a.n_seed;
-            if (!in && !(a.prm.options & GMM_OPT_ONLY_INTERNAL)) {
-                const float4 q = lig[g * a.Mp + s];
-                for (int k = 0; k < a.n_seed && !in; ++k) {
-                    const float4 t = lig[g * a.Mp + k];
-                    in = dist2f(t.x, t.y, t.z, q.x, q.y, q.z) <= a.rad2;
-                }
-                for (int k = 0; k < a.n_sseed && !in; ++k) {
-                    const float4 t = a.sseed[k];
-                    in = dist2f(t.x, t.y, t.z, q.x, q.y, q.z) <= a.rad2;
-                }
-            }
-            if (in) bits |= 1u << b;
-        }
-        zm[idx] = bits;
-    }
-    __syncthreads();
-}
 
 // ---------------------------------------------------------------------------------------
 // sweep + expand + score
@@ -392,7 +315,7 @@ contacts_finalize_kernel(const FinArgs f) {
 // static-static pair values and always-in-zone atoms (run once per gmm_set_receptor)
 // ---------------------------------------------------------------------------------------
 __global__ void rr_values_kernel(int R, const int32_t* rr_ptr, const int32_t* rr_idx, const float4* rec4,
-                                 const uint8_t* rflags, Params prm, long long* val, uint8_t* kind) {
+                                 const uint8_t* rflags, Params prm, long long* val, uint8_t* kind, uint32_t* edge) {
     const int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia >= R) return;
     const float4 A = rec4[ia];
@@ -404,6 +327,7 @@ __global__ void rr_values_kernel(int R, const int32_t* rr_ptr, const int32_t* rr
         val[2 * (size_t)e] = ps.clash_fx;
         val[2 * (size_t)e + 1] = ps.hydro_fx;
         kind[e] = (uint8_t)ps.kind;
+        edge[e] = (uint32_t)ib | ((uint32_t)(ia & 31) << 24) | ((uint32_t)ps.kind << 29);
     }
 }
 
@@ -543,7 +467,7 @@ size_t contacts_scratch_bytes(const gmm_ctx* c, int P) {
     return b + 256;
 }
 
-static void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a) {
+void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a) {
     a.P = P; a.M = c->M; a.Mp = c->Mp; a.MW = (c->Mp + 31) / 32; a.n_seed = c->n_seed;
     a.n_tiles = c->n_tiles; a.ZW = c->n_tiles * 4;
     a.n_sseed = c->n_sseed; a.sseed = c->d_sseed;
@@ -564,6 +488,11 @@ static void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs
 int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
                     void* workspace) {
     if (P == 0) return GMM_OK;
+    if (!(c->prm.options & GMM_OPT_TILED)) {
+        int handled = 0;
+        const int rc = launch_contacts_fused(c, P, xyz, scores, counts, s, &handled);
+        if (rc != GMM_OK || handled) return rc;
+    }
     SweepArgs a;
     fill_sweep_args(c, P, xyz, a);
     unsigned char* base = static_cast<unsigned char*>(workspace ? workspace : c->d_scratch);
@@ -620,7 +549,7 @@ int launch_rr_values(gmm_ctx* c, cudaStream_t s) {
     }
     if (c->rr_nnz > 0) {
         rr_values_kernel<<<(c->R + 127) / 128, 128, 0, s>>>(c->R, c->d_rr_ptr, c->d_rr_idx, c->d_rec4,
-                                                           c->d_rflags, c->prm, c->d_rr_val, c->d_rr_kind);
+                                                           c->d_rflags, c->prm, c->d_rr_val, c->d_rr_kind, c->d_edge);
         GMM_LAUNCH_CHECK("rr_values_kernel");
     }
     return GMM_OK;

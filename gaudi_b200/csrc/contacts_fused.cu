@@ -1,0 +1,408 @@
+// Contacts objective, one-kernel path (gaudi/objectives/contacts.py:129-268; Chimera's
+// specifier.zone at :210-212 and DetectClash.detectClash at :145): a team of S warps (S = 1 for
+// large populations, S = 4 = one CTA for small ones) owns one individual from its expressed
+// coordinates to its two scores, so nothing but the scores leaves the SM.
+//
+//   0  stage    the pose's mobile atoms go to shared memory twice: exact (x, y, z, radius) and
+//               re-centred on the pose's own centre c (x-c, y-c, z-c, |.|^2);
+//   1  cull     lanes test the boxes of 32-atom receptor leaves against the pose in parallel
+//               and ballot-compact the survivors into a list (all leaves when culling is off);
+//   2  sweep    four leaves at a time, one atom of each per lane.  With a = -2 (r - c) and
+//               n = |r - c|^2 kept in registers, d^2 = n + min_i (a . m_i + |m_i|^2): THREE FFMA
+//               and one FMNMX per pair test, branch-free.  Working relative to the pose centre
+//               keeps every magnitude small, so this expanded form is accurate to ~1e-4 A^2;
+//               receptor atoms whose min d^2 lands within a margin of radius^2 get their zone
+//               membership re-decided with exact differences (rare), so zone bits are identical
+//               to the direct-difference definition.  Candidates (atoms that can have a contact
+//               at all) are expanded against the mobile atoms with exact differences and the
+//               surviving pairs scored in fp64 (score_pair), as in contacts.cu;
+//   3  static   static-static pairs are stored as per-leaf edge lists; leaves with a non-empty
+//               zone word walk their edges with coalesced loads and test both zone bits in
+//               shared memory;
+//   4  intra    pairs inside the mobile set (exclusions pre-removed);
+//   5  finish   fixed-point sums -> doubles, x2 (contacts.py:176-177), cutoff penalty
+//               (contacts.py:132-133).
+#include "contacts_common.cuh"
+
+namespace gmm {
+
+struct FusedArgs {
+    SweepArgs s;
+    int NST, R;
+    const float* sub_box;
+    const int32_t* rr_ptr; const uint32_t* edge; const long long* rr_val;
+    const uint32_t* mm_pairs; int n_mm;
+    double* scores; int32_t* counts;
+    int ind_bytes;
+};
+
+struct Acc { long long cfx, hfx; int nc, nh; };
+
+template <int S>
+__device__ __forceinline__ void team_sync() {
+    if (S == 1) __syncwarp(); else __syncthreads();
+}
+
+__device__ __forceinline__ void fused_drain_pairs(const SweepArgs& a, uint32_t* pq, int& npq, const float4* ligx,
+                                                  Acc& acc, int lane) {
+    for (int base = 0; base < npq; base += 32) {
+        const int e = base + lane;
+        if (e < npq) {
+            const uint32_t pr = pq[e];
+            const int s = pr >> 22, j = pr & 0x3fffff;
+            if (!ms_excluded(a.ms_ptr, a.ms_idx, s, j)) {
+                const float4 m = ligx[s];
+                const float4 r = a.rec4[j];
+                const PairScore ps = score_pair(m.x, m.y, m.z, m.w, a.mflags[s], r.x, r.y, r.z, r.w, a.rflags[j], a.prm);
+                if (ps.kind & 1) { acc.cfx += ps.clash_fx; ++acc.nc; }
+                if (ps.kind & 2) { acc.hfx += ps.hydro_fx; ++acc.nh; }
+            }
+        }
+    }
+    __syncwarp();
+    npq = 0;
+}
+
+__device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint32_t* cq, int& ncq, uint32_t* pq,
+                                                       int& npq, const float4* ligx, const uint32_t* zm, Acc& acc,
+                                                       int lane) {
+    for (int base = 0; base < ncq; base += 32) {
+        const int e = base + lane;
+        const bool valid = e < ncq;
+        int j = 0;
+        float4 r = make_float4(kFar, kFar, kFar, 0.f);
+        if (valid) { j = (int)cq[e]; r = a.rec4[j]; }
+        for (int s = 0; s < a.M; ++s) {
+            const float4 m = ligx[s];
+            const float d2 = dist2f(r.x, r.y, r.z, m.x, m.y, m.z);
+            const bool hit = valid && d2 <= loose_c2(m.w, r.w, a.thr_min) && ((zm[s >> 5] >> (s & 31)) & 1u);
+            const unsigned mask = __ballot_sync(0xffffffffu, hit);
+            if (mask) {
+                if (hit) pq[npq + __popc(mask & ((1u << lane) - 1u))] = ((uint32_t)s << 22) | (uint32_t)j;
+                npq += __popc(mask);
+                __syncwarp();
+                if (npq > kPairQ - 32) fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+            }
+        }
+    }
+    __syncwarp();
+    ncq = 0;
+    fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+}
+
+template <int S>
+__global__ void __launch_bounds__(128, 8)
+contacts_fused_kernel(const FusedArgs f) {
+    const SweepArgs& a = f.s;
+    constexpr int IPC = 4 / S;            // individuals per CTA
+    constexpr int TL = 32 * S;            // lanes per team
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int team = warp / S, wt = warp % S, tlane = wt * 32 + lane;
+    const int p = blockIdx.x * IPC + team;
+    if (S == 1 && p >= a.P) return;       // whole warp leaves; S == 4 has one individual per CTA
+
+    unsigned char* ib = smem_raw + (size_t)team * f.ind_bytes;
+    float4* ligx = reinterpret_cast<float4*>(ib);                 // [Mp] exact x, y, z, radius
+    float4* ligc = ligx + a.Mp;                                   // [Mp] centred x, y, z, |.|^2
+    float4* misc = ligc + a.Mp;                                   // [0] sphere, [1] box lo, [2] box hi
+    long long* accs = reinterpret_cast<long long*>(misc + 3);     // [4]
+    int* nlist_p = reinterpret_cast<int*>(accs + 4);              // [4] (16 bytes)
+    uint32_t* list = reinterpret_cast<uint32_t*>(nlist_p + 4);    // [NST + 4], 16-byte aligned
+    uint32_t* zone = list + (f.NST + 4);                          // [NST + 1]
+    uint32_t* zm = zone + (f.NST + 1);                            // [MW]
+    uint32_t* cq = reinterpret_cast<uint32_t*>(smem_raw + (size_t)IPC * f.ind_bytes) + warp * (kCandQ + kPairQ);
+    uint32_t* pq = cq + kCandQ;
+
+    // ---- 0. stage the pose --------------------------------------------------------------
+    for (int s = tlane; s < a.Mp; s += TL) {
+        const int atom = a.slot2atom[s];
+        float4 v = make_float4(kFar, kFar, kFar, 0.f);
+        if (atom >= 0) {
+            const float* src = a.xyz + ((size_t)p * a.M + atom) * 3;
+            v = make_float4(src[0], src[1], src[2], a.mrad[s]);
+        }
+        ligx[s] = v;
+    }
+    if (tlane < 4) accs[tlane] = 0;
+    if (tlane == 0) nlist_p[0] = 0;
+    team_sync<S>();
+    const bool internal = a.prm.options & GMM_OPT_ONLY_INTERNAL;
+    for (int w = tlane; w < a.MW; w += TL) {          // mobile atoms in the zone
+        uint32_t bits = 0;
+        for (int b = 0; b < 32; ++b) {
+            const int s = w * 32 + b;
+            if (s >= a.M) break;
+            bool in = s < a.n_seed;
+            if (!in && !internal) {
+                const float4 q = ligx[s];
+                for (int k = 0; k < a.n_seed && !in; ++k)
+                    in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
+                for (int k = 0; k < a.n_sseed && !in; ++k)
+                    in = dist2f(a.sseed[k].x, a.sseed[k].y, a.sseed[k].z, q.x, q.y, q.z) <= a.rad2;
+            }
+            if (in) bits |= 1u << b;
+        }
+        zm[w] = bits;
+    }
+    if (wt == 0) {                                     // bounding box and sphere of the pose
+        float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+        for (int s = lane; s < a.M; s += 32) {
+            const float4 m = ligx[s];
+            lo[0] = fminf(lo[0], m.x); hi[0] = fmaxf(hi[0], m.x);
+            lo[1] = fminf(lo[1], m.y); hi[1] = fmaxf(hi[1], m.y);
+            lo[2] = fminf(lo[2], m.z); hi[2] = fmaxf(hi[2], m.z);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+                hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+            }
+        const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
+        float r2 = 0.f;
+        for (int s = lane; s < a.M; s += 32) r2 = fmaxf(r2, dist2f(ligx[s].x, ligx[s].y, ligx[s].z, cx, cy, cz));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, o));
+        if (lane == 0) {
+            misc[0] = make_float4(cx, cy, cz, r2);
+            misc[1] = make_float4(lo[0], lo[1], lo[2], 0.f);
+            misc[2] = make_float4(hi[0], hi[1], hi[2], 0.f);
+        }
+    }
+    team_sync<S>();
+    const float4 sph = misc[0];
+    const float wmax = sph.w;
+    for (int s = tlane; s < a.Mp; s += TL) {
+        const float4 m = ligx[s];
+        const float x = m.x - sph.x, y = m.y - sph.y, z = m.z - sph.z;
+        ligc[s] = make_float4(x, y, z, fmaf(z, z, fmaf(y, y, x * x)));
+    }
+    for (int st = tlane; st <= f.NST; st += TL) zone[st] = a.always[st];
+
+    Acc acc; acc.cfx = 0; acc.hfx = 0; acc.nc = 0; acc.nh = 0;
+    unsigned long long tests = 0;
+    const bool have_sweep = !internal && f.R > 0;
+
+    if (have_sweep) {
+        // ---- 1. surviving leaves ----------------------------------------------------------
+        const float4 blo = misc[1], bhi = misc[2];
+        const float prad = sqrtf(sph.w) * 1.00001f + 1e-4f;
+        int nl = 0;
+        for (int base = 0; base < f.NST; base += TL) {
+            const int st = base + tlane;
+            bool keep = false;
+            if (st < f.NST && st * kSubTile < f.R) {
+                if (!a.cull || a.always[st] != 0u) {
+                    keep = true;
+                } else {
+                    const float* bx = f.sub_box + (size_t)st * 8;
+                    const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
+                    const float ex = fmaxf(fmaxf(bx[0] - sph.x, sph.x - bx[3]), 0.f);
+                    const float ey = fmaxf(fmaxf(bx[1] - sph.y, sph.y - bx[4]), 0.f);
+                    const float ez = fmaxf(fmaxf(bx[2] - sph.z, sph.z - bx[5]), 0.f);
+                    const float lim = prad + reach;
+                    keep = ex * ex + ey * ey + ez * ez <= lim * lim &&
+                           bx[0] <= bhi.x + reach && bx[3] >= blo.x - reach &&
+                           bx[1] <= bhi.y + reach && bx[4] >= blo.y - reach &&
+                           bx[2] <= bhi.z + reach && bx[5] >= blo.z - reach;
+                }
+            }
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            int pos;
+            if (S == 1) {
+                pos = nl;
+                nl += __popc(mask);
+            } else {
+                int b0 = 0;
+                if (lane == 0 && mask) b0 = atomicAdd(nlist_p, __popc(mask));
+                pos = __shfl_sync(0xffffffffu, b0, 0);
+            }
+            if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint32_t)st;
+        }
+        if (S == 1) { if (lane == 0) nlist_p[0] = nl; }
+        team_sync<S>();
+        const int nlist = nlist_p[0];
+        const int ngroups = (nlist + 3) >> 2;
+        if (tlane < 4 && nlist + tlane < ngroups * 4) list[nlist + tlane] = (uint32_t)f.NST;   // dummy far leaf
+        team_sync<S>();
+
+        // ---- 2. sweep -----------------------------------------------------------------------
+        int ncq = 0, npq = 0;
+        for (int gi = wt; gi < ngroups; gi += S) {
+            const uint4 st4 = *reinterpret_cast<const uint4*>(list + 4 * gi);
+            const uint32_t stv[4] = {st4.x, st4.y, st4.z, st4.w};
+            float ax[4], ay[4], az[4], nr[4], rw[4], ms[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float4 r = a.rec4[stv[k] * kSubTile + lane];
+                const float x = r.x - sph.x, y = r.y - sph.y, z = r.z - sph.z;
+                ax[k] = -2.f * x; ay[k] = -2.f * y; az[k] = -2.f * z;
+                nr[k] = fmaf(z, z, fmaf(y, y, x * x));
+                rw[k] = r.w;
+                ms[k] = 3e38f;
+                tests += (stv[k] < (uint32_t)f.NST) ? (unsigned long long)kSubTile * a.M : 0ull;
+            }
+#pragma unroll 4
+            for (int s = 0; s < a.n_seed; ++s) {
+                const float4 m = ligc[s];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ms[k] = fminf(ms[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
+            }
+            float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
+            for (int s = a.n_seed; s < a.M; ++s) {
+                const float4 m = ligc[s];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ma[k] = fminf(ma[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float margin = 2e-4f + 1e-6f * (nr[k] + wmax);
+                const float dz = ms[k] + nr[k];
+                bool in = ((zone[stv[k]] >> lane) & 1u) || dz <= a.rad2 - margin;
+                const bool band = !in && dz <= a.rad2 + margin;
+                if (__any_sync(0xffffffffu, band)) {
+                    if (band) {     // re-decide with exact differences (same arithmetic as the dump kernel)
+                        const float4 r = a.rec4[stv[k] * kSubTile + lane];
+                        float e = 3e38f;
+                        for (int s = 0; s < a.n_seed; ++s)
+                            e = fminf(e, dist2f(r.x, r.y, r.z, ligx[s].x, ligx[s].y, ligx[s].z));
+                        in = e <= a.rad2;
+                    }
+                }
+                const float c = rw[k] + a.rmax_mobile - a.thr_min;
+                const bool cand = in && (ma[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin);
+                const unsigned zb = __ballot_sync(0xffffffffu, in);
+                const unsigned cb = __ballot_sync(0xffffffffu, cand);
+                __syncwarp();
+                if (lane == 0 && stv[k] < (uint32_t)f.NST) zone[stv[k]] = zb;
+                if (cb) {
+                    if (cand) cq[ncq + __popc(cb & ((1u << lane) - 1u))] = stv[k] * kSubTile + lane;
+                    ncq += __popc(cb);
+                }
+            }
+            __syncwarp();
+            if (ncq > kCandQ - 128) fused_drain_candidates(a, cq, ncq, pq, npq, ligx, zm, acc, lane);
+        }
+        fused_drain_candidates(a, cq, ncq, pq, npq, ligx, zm, acc, lane);
+        team_sync<S>();
+
+        // ---- 3. static-static pairs with both atoms in the zone ------------------------------
+        // Only swept leaves can have a non-empty zone word (leaves holding always-in-zone atoms are
+        // never culled).  Lanes fetch the edge ranges of 32 leaves at once, then the warp
+        // walks each non-empty leaf's edges with coalesced loads.
+        if (f.rr_ptr != nullptr) {
+            for (int base = wt * 32; base < nlist; base += TL) {
+                const int i = base + lane;
+                uint32_t my_z = 0;
+                int my_e0 = 0, my_e1 = 0;
+                if (i < nlist) {
+                    const uint32_t my_st = list[i];
+                    my_z = zone[my_st];
+                    if (my_z) { my_e0 = f.rr_ptr[my_st * kSubTile]; my_e1 = f.rr_ptr[my_st * kSubTile + kSubTile]; }
+                }
+                unsigned todo = __ballot_sync(0xffffffffu, my_z != 0u && my_e1 > my_e0);
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const uint32_t z = __shfl_sync(0xffffffffu, my_z, src);
+                    const int e0 = __shfl_sync(0xffffffffu, my_e0, src), e1 = __shfl_sync(0xffffffffu, my_e1, src);
+                    for (int e = e0 + lane; e < e1; e += 32) {
+                        const uint32_t en = f.edge[e];
+                        const uint32_t kind = en >> 29, al = (en >> 24) & 31u, b = en & 0x3fffffu;
+                        if (kind && ((z >> al) & 1u) && ((zone[b >> 5] >> (b & 31u)) & 1u)) {
+                            if (kind & 1) { acc.cfx += f.rr_val[2 * (size_t)e]; ++acc.nc; }
+                            if (kind & 2) { acc.hfx += f.rr_val[2 * (size_t)e + 1]; ++acc.nh; }
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- 4. pairs inside the mobile set ------------------------------------------------------
+    for (int e = tlane; e < f.n_mm; e += TL) {
+        const uint32_t pr = f.mm_pairs[e];
+        const int sa = pr & 0xffff, sb = pr >> 16;
+        if (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u)) continue;
+        const float4 A = ligx[sa], B = ligx[sb];
+        if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > loose_c2(A.w, B.w, a.thr_min)) continue;
+        const PairScore ps = score_pair(A.x, A.y, A.z, A.w, a.mflags[sa], B.x, B.y, B.z, B.w, a.mflags[sb], a.prm);
+        if (ps.kind & 1) { acc.cfx += ps.clash_fx; ++acc.nc; }
+        if (ps.kind & 2) { acc.hfx += ps.hydro_fx; ++acc.nh; }
+    }
+
+    // ---- 5. finish ---------------------------------------------------------------------------
+    long long cfx = acc.cfx, hfx = acc.hfx, nc = acc.nc, nh = acc.nh;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cfx += __shfl_xor_sync(0xffffffffu, cfx, o); hfx += __shfl_xor_sync(0xffffffffu, hfx, o);
+        nc += __shfl_xor_sync(0xffffffffu, nc, o); nh += __shfl_xor_sync(0xffffffffu, nh, o);
+    }
+    if (S > 1) {
+        if (lane == 0) {
+            atomicAdd((unsigned long long*)&accs[0], (unsigned long long)cfx);
+            atomicAdd((unsigned long long*)&accs[1], (unsigned long long)hfx);
+            atomicAdd((unsigned long long*)&accs[2], (unsigned long long)nc);
+            atomicAdd((unsigned long long*)&accs[3], (unsigned long long)nh);
+        }
+        team_sync<S>();
+        cfx = accs[0]; hfx = accs[1]; nc = accs[2]; nh = accs[3];
+    }
+    if (lane == 0 && tests) atomicAdd(a.counters, tests);
+    if (tlane == 0) {
+        if (f.n_mm) atomicAdd(a.counters, (unsigned long long)f.n_mm);
+        double clash = 2.0 * ((double)cfx / kFxScale);          // contacts.py:176-177
+        const double hydro = 2.0 * ((double)hfx / kFxScale);
+        if (a.prm.cutoff != 0.0 && clash > a.prm.cutoff) clash = -1000.0 * a.prm.weight;   // contacts.py:132-133
+        f.scores[2 * (size_t)p] = clash;
+        f.scores[2 * (size_t)p + 1] = hydro;
+        if (f.counts) { f.counts[2 * (size_t)p] = (int32_t)nc; f.counts[2 * (size_t)p + 1] = (int32_t)nh; }
+    }
+}
+
+void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a);
+
+// Returns GMM_OK and sets *handled = 1 when the fused kernel ran; *handled = 0 when the model
+// does not fit its shared-memory plan (the caller then uses the tiled kernels of contacts.cu).
+int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
+                          int* handled) {
+    *handled = 0;
+    FusedArgs f;
+    fill_sweep_args(c, P, xyz, f.s);
+    f.NST = c->Rpad / kSubTile; f.R = c->R;
+    f.sub_box = c->d_sub_box;
+    f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge; f.rr_val = c->d_rr_val;
+    f.mm_pairs = c->d_mm_pairs; f.n_mm = c->n_mm;
+    f.scores = scores; f.counts = counts;
+    size_t ind = (size_t)2 * f.s.Mp * sizeof(float4) + 3 * sizeof(float4) + 4 * sizeof(long long) + 4 * sizeof(int) +
+                 (size_t)(f.NST + 4) * 4 + (size_t)(f.NST + 1) * 4 + (size_t)f.s.MW * 4;
+    ind = (ind + 15) / 16 * 16;
+    f.ind_bytes = (int)ind;
+    const size_t queues = (size_t)4 * (kCandQ + kPairQ) * sizeof(uint32_t);
+    const size_t limit = 200 * 1024;
+    int S = (P >= 148 * 8) ? 1 : 4;
+    if (S == 1 && 4 * ind + queues > limit) S = 4;
+    if (ind + queues > limit) return GMM_OK;    // not handled
+    const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
+    GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));
+    static bool attr1 = false, attr4 = false;
+    if (S == 1) {
+        if (!attr1) { GMM_CUDA(cudaFuncSetAttribute(contacts_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit)); attr1 = true; }
+        if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
+        contacts_fused_kernel<1><<<(P + 3) / 4, 128, smem, s>>>(f);
+    } else {
+        if (!attr4) { GMM_CUDA(cudaFuncSetAttribute(contacts_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit)); attr4 = true; }
+        if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
+        contacts_fused_kernel<4><<<P, 128, smem, s>>>(f);
+    }
+    GMM_LAUNCH_CHECK("contacts_fused_kernel");
+    if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[3], s)); c->ev_used[1] = true; c->ev_used[2] = false; }
+    *handled = 1;
+    return GMM_OK;
+}
+
+}  // namespace gmm

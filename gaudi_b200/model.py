@@ -107,6 +107,7 @@ class ContactParams:
     bond_separation: int = 4
     only_internal: bool = False
     cull: bool = True       # B200 path only: skip receptor tiles out of reach of a pose
+    tiled: bool = False     # B200 path only: two-kernel tiled Contacts path instead of the fused one
 
 
 @dataclass

@@ -49,6 +49,7 @@ extern "C" {
 /* gmm_set_params option bits */
 #define GMM_OPT_ONLY_INTERNAL  1  /* Contacts(only_internal=True), contacts.py:199 */
 #define GMM_OPT_NO_CULL        2  /* score every receptor tile (dense), no bounding-box culling */
+#define GMM_OPT_TILED          4  /* use the two-kernel tiled Contacts path instead of the fused one */
 
 #define GMM_MAX_MOBILE_ATOMS   1024
 #define GMM_MAX_TORSIONS       1024

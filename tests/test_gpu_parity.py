@@ -129,6 +129,22 @@ def test_contacts_invariances(small_system, torch_cuda):
     assert eng.last_pair_tests() < dense.last_pair_tests()
 
 
+@pytest.mark.parametrize("pop", [4096, 100, 1])
+def test_fused_equals_tiled(small_system, torch_cuda, pop):
+    """The one-kernel Contacts path (warp or CTA per individual, expanded-form sweep with exact
+    re-decision near the zone radius) and the two-kernel tiled path (direct differences) must
+    agree bit for bit: both sum the same per-pair fixed-point values."""
+    from gaudi_b200.engine import Engine
+    lig, rec, params, eng = small_system
+    tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=17)
+    s1, c1, x1 = eng.evaluate(tors, xf, want_xyz=True)
+    for kw in (dict(tiled=True), dict(tiled=True, cull=False), dict(cull=False)):
+        other = Engine(lig, rec, M.ContactParams(**kw), device=0)
+        s2, c2 = other.contacts(x1)
+        assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2), kw
+        other.close()
+
+
 def test_evaluate_host_equals_device(small_system):
     lig, rec, params, eng = small_system
     tors, xf = synth.make_alleles(777, lig.n_allele_torsions, seed=9)
