@@ -321,6 +321,7 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
 
     // static-static candidate pairs -> sorted index space, row = smaller sorted index
     c->rr_nnz = 0;
+    std::vector<int32_t> rr_ptr_s, rr_idx_s;      // sorted-index CSR kept for the pruning pass below
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind); release(c->d_edge);
     if (R > 0 && rr_ptr_h && rr_idx_h && rr_ptr_h[R] > 0) {
         const int nnz = rr_ptr_h[R];
@@ -346,6 +347,7 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_val, sizeof(long long) * 2 * pr.size()));
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_kind, pr.size()));
         GMM_CUDA(cudaMalloc((void**)&c->d_edge, sizeof(uint32_t) * pr.size()));
+        rr_ptr_s.swap(ptr); rr_idx_s.swap(idx);
     }
     // mobile-static exclusions (flexible side chains bonded to the static backbone)
     c->ms_nnz = 0;
@@ -367,6 +369,27 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     }
     if ((rc = launch_rr_values(c, 0))) return rc;
     GMM_CUDA(cudaDeviceSynchronize());
+    if (c->rr_nnz > 0) {
+        // Drop the candidate pairs that contribute to neither score under these parameters (two
+        // thirds of them on protein-like input); the per-individual walk only sees the rest.
+        std::vector<uint8_t> kind(c->rr_nnz);
+        GMM_CUDA(cudaMemcpy(kind.data(), c->d_rr_kind, kind.size(), cudaMemcpyDeviceToHost));
+        std::vector<int32_t> ptr(rr_ptr_s.size(), 0), idx;
+        idx.reserve(c->rr_nnz);
+        const int rows = (int)rr_ptr_s.size() - 1;
+        for (int a = 0; a < rows; ++a) {
+            for (int e = rr_ptr_s[a]; e < rr_ptr_s[a + 1]; ++e)
+                if (kind[e]) idx.push_back(rr_idx_s[e]);
+            ptr[a + 1] = (int32_t)idx.size();
+        }
+        c->rr_nnz = (int)idx.size();
+        if ((rc = upload(&c->d_rr_ptr, ptr.data(), ptr.size()))) return rc;
+        if ((rc = upload(&c->d_rr_idx, idx.data(), idx.size()))) return rc;
+        if (c->rr_nnz > 0) {
+            if ((rc = launch_rr_values(c, 0))) return rc;     // same values, compacted order
+            GMM_CUDA(cudaDeviceSynchronize());
+        }
+    }
     c->has_receptor = true;
     return GMM_OK;
 }

@@ -310,12 +310,19 @@ contacts_fused_kernel(const FusedArgs f) {
                     todo &= todo - 1;
                     const uint32_t z = __shfl_sync(0xffffffffu, my_z, src);
                     const int e0 = __shfl_sync(0xffffffffu, my_e0, src), e1 = __shfl_sync(0xffffffffu, my_e1, src);
-                    for (int e = e0 + lane; e < e1; e += 32) {
+                    for (int e = e0 + lane; e < e1; e += 64) {      // two independent edges in flight
+                        const int e2 = e + 32;
                         const uint32_t en = f.edge[e];
+                        const uint32_t en2 = e2 < e1 ? f.edge[e2] : 0u;
                         const uint32_t kind = en >> 29, al = (en >> 24) & 31u, b = en & 0x3fffffu;
+                        const uint32_t kind2 = en2 >> 29, al2 = (en2 >> 24) & 31u, b2 = en2 & 0x3fffffu;
                         if (kind && ((z >> al) & 1u) && ((zone[b >> 5] >> (b & 31u)) & 1u)) {
                             if (kind & 1) { acc.cfx += f.rr_val[2 * (size_t)e]; ++acc.nc; }
                             if (kind & 2) { acc.hfx += f.rr_val[2 * (size_t)e + 1]; ++acc.nh; }
+                        }
+                        if (kind2 && ((z >> al2) & 1u) && ((zone[b2 >> 5] >> (b2 & 31u)) & 1u)) {
+                            if (kind2 & 1) { acc.cfx += f.rr_val[2 * (size_t)e2]; ++acc.nc; }
+                            if (kind2 & 2) { acc.hfx += f.rr_val[2 * (size_t)e2 + 1]; ++acc.nh; }
                         }
                     }
                 }
