@@ -1,0 +1,120 @@
+"""The (mu + lambda) loop of gaudi/algorithms.py:54-202 with the two seams of the B200 path
+filled in: ``toolbox.map`` is a batched evaluate (one GPU call per generation instead of a
+serial Python ``map``), and the O((mu+lambda)^2) ``toolbox.similarity`` calls of the niching
+pass (algorithms.py:139-155) read a bitmask computed by one ``gmm_rmsd_matrix`` call.  The
+greedy, order-dependent niching pass itself, hall of fame and NSGA-II selection run on the host
+exactly as in the reference."""
+from __future__ import annotations
+
+import logging
+import random
+from time import time
+
+from . import deaplite
+
+logger = logging.getLogger(__name__)
+
+
+class BatchedMap(object):
+    """Drop-in for ``toolbox.map``: ``map(toolbox.evaluate, individuals)`` becomes one batched
+    GPU evaluation.  Any other mapped function falls back to the builtin."""
+
+    def __init__(self, environment, evaluate_alias=None):
+        self.environment = environment
+        self.evaluate_alias = evaluate_alias
+
+    def __call__(self, fn, individuals):
+        individuals = list(individuals)
+        if self.evaluate_alias is None or fn is self.evaluate_alias:
+            return self.environment.evaluate_population(individuals)
+        return list(map(fn, individuals))
+
+
+def niching(candidates, similar):
+    """gaudi/algorithms.py:139-155 verbatim in behaviour: visit in order; drop a candidate at the
+    first similar kept individual that is at least as fit, otherwise evict the similar, worse ones."""
+    new_population = []
+    for i in candidates:
+        to_delete = []
+        for n_i in new_population:
+            if similar(i, n_i):
+                if i.fitness <= n_i.fitness:
+                    break
+                else:
+                    to_delete.append(new_population.index(n_i))
+        else:
+            if to_delete:
+                new_population = [k for j, k in enumerate(new_population) if j not in to_delete]
+            new_population.append(i)
+    return new_population
+
+
+def ea_mu_plus_lambda(population, toolbox, mu, lambda_, cxpb, mutpb, ngen, cfg=None, stats=None,
+                      halloffame=None, verbose=True, environment=None):
+    """Returns ``(population, logbook)``; ``logbook`` is a list of dicts with the reference's
+    columns ``gen, nevals, speed`` (ev/s defined as in algorithms.py:168-171)."""
+    logbook = []
+    t0 = time()
+    invalid = [ind for ind in population if not ind.fitness.valid]
+    for ind, fit in zip(invalid, toolbox.map(toolbox.evaluate, invalid)):
+        ind.fitness.values = fit
+    population = toolbox.select(population, len(population))
+    if halloffame is not None:
+        halloffame.update(population)
+    nevals = len(invalid)
+    logbook.append({"gen": 0, "nevals": nevals, "speed": nevals / max(time() - t0, 1e-9)})
+    batch = environment.batch if environment is not None else None
+    sim_args = cfg.similarity.args if cfg is not None else None
+    for gen in range(1, ngen + 1):
+        offspring = deaplite.var_or(population, toolbox, lambda_, cxpb, mutpb)
+        t1 = time()
+        invalid = [ind for ind in offspring if not ind.fitness.valid]
+        for ind, fit in zip(invalid, toolbox.map(toolbox.evaluate, invalid)):
+            ind.fitness.values = fit
+        candidates = population + offspring
+        if batch is not None and sim_args is not None:
+            batch.similarity_matrix(candidates, sim_args[0], sim_args[1])   # one GPU call per generation
+        new_population = niching(candidates, toolbox.similarity)
+        while len(new_population) < mu:
+            new_population.append(random.choice(candidates))
+        if halloffame is not None:
+            halloffame.clear()
+            halloffame.update(new_population)
+        population[:] = toolbox.select(new_population, mu)
+        nevals = len(invalid)
+        t2 = time()
+        logbook.append({"gen": gen, "nevals": nevals, "speed": nevals / max(t2 - t1, 1e-9)})
+        if verbose:
+            logger.log(100, "gen %d  nevals %d  %.2f ev/s", gen, nevals, logbook[-1]["speed"])
+    return population, logbook
+
+
+def launch(cfg, device=0, seed=None):
+    """gaudi/cli/gaudi_run.py:69-134 for the B200 path: build population and environment,
+    register the DEAP-style aliases plus the batched ``map``, run the loop."""
+    from . import base, plugin
+    if seed is not None:
+        random.seed(seed)
+    plugin.import_plugins(*cfg.genes)
+    plugin.import_plugins(*cfg.objectives)
+    toolbox = deaplite.Toolbox()
+    population = [base.MolecularIndividual(cfg) for _ in range(cfg.ga.population)]
+    environment = base.Environment(cfg, device=device)
+    cfg._environment = environment
+    environment.attach(population[0])
+    toolbox.register("evaluate", environment.evaluate)
+    toolbox.register("mate", lambda a, b: a.mate(b))
+    toolbox.register("mutate", lambda ind, indpb: ind.mutate(indpb), indpb=cfg.ga.mut_indpb)
+    toolbox.register("similarity", lambda a, b: a.similar(b))
+    toolbox.register("select", deaplite.sel_nsga2)
+    toolbox.register("map", BatchedMap(environment, toolbox.evaluate))
+    if cfg.output.pareto:
+        elite = deaplite.ParetoFront(toolbox.similarity)
+    else:
+        elite = deaplite.HallOfFame(int(cfg.ga.population * cfg.ga.mu), similar=toolbox.similarity)
+    mu = int(cfg.ga.mu * cfg.ga.population)
+    lambda_ = int(cfg.ga.lambda_ * cfg.ga.population)
+    population, log = ea_mu_plus_lambda(population, toolbox, mu=mu, lambda_=lambda_, cxpb=cfg.ga.cx_pb,
+                                        mutpb=cfg.ga.mut_pb, ngen=cfg.ga.generations, cfg=cfg,
+                                        halloffame=elite, verbose=cfg.output.verbose, environment=environment)
+    return population, log, elite

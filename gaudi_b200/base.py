@@ -1,0 +1,371 @@
+"""Individual / Environment of the B200 path.
+
+Mirrors gaudi/base.py: ``MolecularIndividual`` is an ordered container of gene plugins
+(base.py:104-119,275-316), ``Environment`` an ordered container of objective plugins whose
+``evaluate(individual)`` returns the rounded score list (base.py:342-364).  What is new is
+``BatchEvaluator``: it flattens the genes of one template individual and the Contacts
+objectives into the static model of ``gaudi_b200.model``, owns the GPU context(s), and scores a
+whole list of individuals with one ``gmm_evaluate`` call — the body of the batched
+``toolbox.map`` (gaudi/algorithms.py:99-102)."""
+from __future__ import annotations
+
+import sys
+from collections import OrderedDict
+from contextlib import contextmanager
+from copy import deepcopy
+
+import numpy as np
+
+from . import model as M
+from . import molio, plugin
+from .deaplite import Fitness
+
+
+class MolecularIndividual(object):
+    _CACHE = {}
+
+    def __init__(self, cfg=None, **kwargs):
+        self.cfg = cfg
+        self.genes = OrderedDict()
+        self._molecules = OrderedDict()
+        self.fitness = None
+        self.expressed = False
+        self.__ready__()
+        self.__expression_hooks__()
+
+    def __ready__(self):
+        if self.cfg is not None:
+            plugin.load_plugins(self.cfg.genes, container=self.genes, parent=self,
+                                cx_eta=self.cfg.ga.cx_eta, mut_eta=self.cfg.ga.mut_eta,
+                                mut_indpb=self.cfg.ga.mut_indpb)
+            self.fitness = Fitness(self.cfg.weights)
+            mod, fn = self.cfg.similarity.module.rsplit(".", 1)
+            if mod not in sys.modules:
+                __import__(mod)
+            self._similarity = getattr(sys.modules[mod], fn)
+        for name, gene in self.genes.items():
+            if gene.__class__.__name__ == "Molecule":
+                self._molecules[name] = gene
+        for name, gene in self.genes.items():
+            gene.__ready__()
+
+    def __expression_hooks__(self):
+        with expressed(self):
+            for gene in self.genes.values():
+                gene.__expression_hooks__()
+
+    def __deepcopy__(self, memo):
+        # gaudi/base.py:289-299 re-initialises and re-expresses every clone; here a clone is
+        # a copy of the alleles (the "row copy" of SURVEY.md section 3.4).
+        new = self.__class__.__new__(self.__class__)
+        new.cfg = self.cfg
+        new.genes = OrderedDict()
+        new._molecules = OrderedDict()
+        for name, gene in self.genes.items():
+            if gene.__class__.__name__ == "Molecule":
+                g = deepcopy(gene, memo)
+            else:
+                g = gene.__class__.__new__(gene.__class__)
+                g.__dict__.update(gene.__dict__)
+                g.allele = deepcopy(gene.allele)
+            g.parent = new
+            new.genes[name] = g
+            if g.__class__.__name__ == "Molecule":
+                new._molecules[name] = g
+        new.fitness = deepcopy(self.fitness, memo)
+        new._similarity = getattr(self, "_similarity", None)
+        new.expressed = self.expressed
+        return new
+
+    def express(self):
+        for gene in self.genes.values():
+            gene.express()
+        self.expressed = True
+
+    def unexpress(self):
+        for gene in reversed(list(self.genes.values())):
+            gene.unexpress()
+        self.expressed = False
+
+    def mate(self, other):
+        for a, b in zip(self.genes.values(), other.genes.values()):
+            a.mate(b)
+        return self, other
+
+    def mutate(self, indpb):
+        for gene in self.genes.values():
+            gene.mutate(indpb)
+        return self,
+
+    def similar(self, other):
+        return self._similarity(self, other, *self.cfg.similarity.args, **self.cfg.similarity.kwargs)
+
+    def find_molecule(self, name):
+        try:
+            return self._molecules[name]
+        except KeyError:
+            raise KeyError("Molecule {} not found. Try with {}".format(name, sorted(self._molecules)))
+
+    def xyz(self, gene=None):
+        try:
+            return self._molecules[gene]._expressed_coordinates
+        except KeyError:
+            return {name: mol._expressed_coordinates for name, mol in self._molecules.items()}
+
+    def clear_cache(self):
+        self._CACHE.clear()
+        for gene in self.genes.values():
+            gene.clear_cache()
+
+
+@contextmanager
+def expressed(*individuals):
+    try:
+        for individual in individuals:
+            individual.express()
+        yield individuals
+    finally:
+        for individual in individuals:
+            individual.unexpress()
+
+
+class Environment(object):
+    def __init__(self, cfg=None, device=0, **kwargs):
+        self.objectives = OrderedDict()
+        self.cfg = cfg
+        self.device = device
+        self.batch = None
+        if cfg is not None:
+            self.weights = cfg.weights
+            plugin.load_plugins(cfg.objectives, container=self.objectives, zone=None, environment=self,
+                                precision=cfg.output.precision)
+
+    def attach(self, template):
+        """Build the GPU model from one (template) individual; called once per job."""
+        self.batch = BatchEvaluator(template, self, device=self.device)
+        return self.batch
+
+    def evaluate(self, individual):
+        """gaudi/base.py:353-364 for one individual (a population of one on the GPU)."""
+        return self.evaluate_population([individual])[0]
+
+    def evaluate_population(self, individuals):
+        if self.batch is None:
+            self.attach(individuals[0])
+        return self.batch.evaluate(individuals)
+
+    def clear_cache(self):
+        for obj in self.objectives.values():
+            obj.clear_cache()
+
+
+class BatchEvaluator(object):
+    """Static model + GPU context(s) for one job, and the batched evaluate."""
+
+    def __init__(self, template, environment, device=0):
+        from .engine import Engine
+        self.environment = environment
+        self.device = device
+        genes = template.genes
+        self.torsion_name = next((n for n, g in genes.items() if g.__class__.__name__ == "Torsion"), None)
+        self.search_name = next((n for n, g in genes.items() if g.__class__.__name__ == "Search"), None)
+        self.rotamer_name = next((n for n, g in genes.items() if g.__class__.__name__ == "Rotamers"), None)
+        names = list(genes.keys())
+        tors, search, rot = (genes.get(self.torsion_name), genes.get(self.search_name),
+                             genes.get(self.rotamer_name))
+        if sum(g.__class__.__name__ == "Torsion" for g in genes.values()) > 1 or \
+           sum(g.__class__.__name__ == "Search" for g in genes.values()) > 1:
+            raise NotImplementedError("one Torsion and one Search gene per individual on the B200 path")
+        self.ligand_name = tors.target if tors is not None else (search.target[0] if search is not None else None)
+        if tors is not None and search is not None and tors.target != search.target[0]:
+            raise NotImplementedError("Torsion and Search must target the same molecule on the B200 path")
+        mol_names = list(template._molecules.keys())
+        if self.ligand_name is None:
+            self.ligand_name = mol_names[0]
+        self.mol_names = mol_names
+
+        # ---- one bonded system over every Molecule gene -------------------------------
+        offsets, xyz, elements, bonds = {}, [], [], []
+        radius, hb = [], []
+        n = 0
+        for name in mol_names:
+            g = template._molecules[name]
+            offsets[name] = n
+            xyz.append(g.mol.xyz); elements += list(g.mol.element)
+            bonds.append(np.asarray(g.mol.bonds, np.int64).reshape(-1, 2) + n)
+            radius.append(g.radii()); hb.append(molio.hbond_flags(g.mol))
+            n += g.mol.n_atoms
+        self.offsets = offsets
+        xyz = np.concatenate(xyz); radius = np.concatenate(radius); hb = np.concatenate(hb)
+        bonds = np.concatenate(bonds) if bonds else np.zeros((0, 2), np.int64)
+        lig = template._molecules[self.ligand_name]
+        lo = offsets[self.ligand_name]
+        lig_idx = np.arange(lo, lo + lig.mol.n_atoms)
+
+        # rotatable bonds: ligand torsions first (allele columns), then rotamer chis
+        rotatable, snap, tors_src = [], [], []
+        if tors is not None:
+            for k, (fx, mv, sn) in enumerate(tors.rotatable_bonds):
+                rotatable.append((fx + lo, mv + lo)); snap.append(sn); tors_src.append(k)
+        self.n_torsions = len(rotatable)
+        flex_idx, cb_idx = [], []
+        rot_ptr, rot_delta = [0], []
+        if rot is not None:
+            for r, (molname, pos, atoms, quads, chi0, table) in enumerate(rot.residues):
+                ro = offsets[molname]
+                g = template._molecules[molname]
+                cb_idx += [a + ro for a in atoms if g.mol.name[a] == "CB"]
+                rows = table if table else [list(chi0) if chi0 else [0.0]]
+                for row in rows:
+                    d = [(row[k] - chi0[k]) if (table and k < len(row) and k < len(chi0)) else 0.0 for k in range(4)]
+                    rot_delta.append(d)
+                rot_ptr.append(len(rot_delta))
+                if not table:
+                    continue
+                adj = g.mol.adjacency()
+                for k, q in enumerate(quads):
+                    fx, mv = q[1], q[2]            # chi k turns about atoms 2-3, CA side fixed
+                    side = M.side_of_bond(adj, fx, mv)
+                    rotatable.append((fx + ro, mv + ro)); snap.append(0); tors_src.append(-(1 + 4 * r + k))
+                    flex_idx += [a + ro for a in side] + [fx + ro]
+        self.n_rot_res = len(rot_ptr) - 1 if rot is not None else 0
+        mobile_idx = np.concatenate([lig_idx, np.array(sorted(set(flex_idx) - set(lig_idx.tolist())), np.int64)])
+        self.mobile_idx = mobile_idx
+        self.lig_slice = slice(0, lig.mol.n_atoms)
+
+        origin = (search.origin_atom + lo) if search is not None else int(lig_idx[0])
+        centre = np.asarray(search.center if search is not None else lig.mol.xyz.mean(axis=0), np.float64)
+        t_before_s = True
+        if tors is not None and search is not None:
+            t_before_s = names.index(self.torsion_name) < names.index(self.search_name)
+
+        # ---- one context per distinct Contacts parameter set ---------------------------
+        self.groups = []            # [(engine, [(objective index, column)])]
+        contacts = [(i, o) for i, o in enumerate(environment.objectives.values())
+                    if o.__class__.__name__ == "Contacts"]
+        others = [o for o in environment.objectives.values() if o.__class__.__name__ != "Contacts"]
+        if others:
+            raise NotImplementedError("only Contacts objectives run on the B200 path: %s"
+                                      % [o.name for o in others])
+        grouped = OrderedDict()
+        for i, o in contacts:
+            placed = False
+            for key, g in grouped.items():
+                if key[0] == o.model_key() and (g["penalty"] is None or o.penalty_key() in (None, g["penalty"])):
+                    g["members"].append((i, o))
+                    g["penalty"] = g["penalty"] or o.penalty_key()
+                    placed = True
+                    break
+            if not placed:
+                grouped[(o.model_key(), len(grouped))] = {"members": [(i, o)], "penalty": o.penalty_key()}
+        self.engines = []
+        for key, g in grouped.items():
+            o = g["members"][0][1]
+            params = o.params()
+            if g["penalty"]:
+                params.cutoff, params.weight = g["penalty"]
+            else:
+                params.cutoff = 0.0
+            hyd = {e.upper() for e in o.hydrophobic_elements}
+            flags = hb.copy()
+            for a, e in enumerate(elements):
+                if e in hyd:
+                    flags[a] |= M.F_HYDROPHOBIC
+            for pname in o._probes:
+                po = offsets[pname]
+                flags[po:po + template._molecules[pname].mol.n_atoms] |= M.F_SEED
+            if not o.only_internal:
+                flags[np.asarray(cb_idx, np.int64)] |= M.F_SEED
+            if search is not None:
+                flags[lig_idx] |= M.F_XFORM
+            mob, rec, _ = M.split_molecule(xyz, radius, flags, bonds, mobile_idx, params, rotatable=rotatable,
+                                           origin_atom=origin, centre=centre,
+                                           torsion_before_search=t_before_s)
+            mob.tors_snap = np.asarray(snap, np.uint8)
+            mob.tors_src = np.asarray(tors_src, np.int32)
+            if rot is not None:
+                mob.rot_ptr = np.asarray(rot_ptr, np.int32)
+                mob.rot_delta = np.asarray(rot_delta, np.float64).reshape(-1, 4)
+            eng = Engine(mob, rec, params, device=device)
+            self.engines.append((eng, [(i, m.column) for i, m in g["members"]]))
+        self.mobile, self.receptor = (self.engines[0][0].mobile, self.engines[0][0].receptor) if self.engines else (None, None)
+        self._scores = {}           # id(individual) -> list of raw scores
+        self._coords = {}           # id(individual) -> (A, 3) float32 device-frame ligand coordinates
+        self.centre = centre
+        self._sim = None
+
+    # ---- allele packing ------------------------------------------------------------------
+    def pack(self, individuals):
+        P = len(individuals)
+        tors = np.zeros((P, self.n_torsions))
+        xf = np.zeros((P, 12)) if self.search_name else None
+        rot = np.zeros((P, self.n_rot_res)) if self.n_rot_res else None
+        for p, ind in enumerate(individuals):
+            if self.torsion_name:
+                a = ind.genes[self.torsion_name].allele
+                tors[p, :min(len(a), self.n_torsions)] = a[:self.n_torsions]
+            if self.search_name:
+                xf[p] = ind.genes[self.search_name].device_allele()
+            if rot is not None:
+                rot[p] = ind.genes[self.rotamer_name].allele
+        return tors, xf, rot
+
+    def evaluate(self, individuals):
+        """Batched ``Environment.evaluate``: list of rounded score lists, in objective order
+        (``round(score, obj.precision)``, gaudi/base.py:361)."""
+        if not individuals:
+            return []
+        tors, xf, rot = self.pack(individuals)
+        objectives = list(self.environment.objectives.values())
+        out = [[None] * len(objectives) for _ in individuals]
+        xyz = None
+        for eng, members in self.engines:
+            scores, _, coords = eng.evaluate_host(tors if self.n_torsions else np.zeros((len(individuals), 0)),
+                                                  xf, rot, want_xyz=xyz is None)
+            if coords is not None:
+                xyz = coords
+            for p in range(len(individuals)):
+                for i, col in members:
+                    out[p][i] = round(float(scores[p, col]), objectives[i].precision)
+        for p, ind in enumerate(individuals):
+            lig = xyz[p, self.lig_slice]
+            self._coords[id(ind)] = lig
+            # post_express (gaudi/base.py:301-303): cache world-frame coordinates for similarity
+            ind._molecules[self.ligand_name]._expressed_coordinates = lig.astype(np.float64) + self.centre
+            self._scores[id(ind)] = out[p]
+        return out
+
+    def score_of(self, individual, objective):
+        idx = list(self.environment.objectives.values()).index(objective)
+        return self.evaluate([individual])[0][idx]
+
+    # ---- batched similarity -----------------------------------------------------------------
+    def similarity_matrix(self, individuals, subjects, threshold):
+        """One ``gmm_rmsd_matrix`` call for every pair among ``individuals``; afterwards
+        ``gaudi_b200.similarity.rmsd`` answers from the bitmask."""
+        from .engine import bits_to_bool
+        conf = np.stack([np.asarray(ind._molecules[subjects[0]]._expressed_coordinates - self.centre, np.float32)
+                         for ind in individuals])
+        eng = self.engines[0][0]
+        _, bits = eng.rmsd_matrix(conf, threshold=threshold, values=False)
+        sim = bits_to_bool(bits, len(individuals))
+        for s in subjects[1:]:
+            conf = np.stack([np.asarray(ind._molecules[s]._expressed_coordinates - self.centre, np.float32)
+                             for ind in individuals])
+            _, bits = eng.rmsd_matrix(conf, threshold=threshold, values=False)
+            sim &= bits_to_bool(bits, len(individuals))
+        self._sim = ({id(ind): k for k, ind in enumerate(individuals)}, sim, tuple(subjects), float(threshold))
+        return sim
+
+    def lookup_similarity(self, ind1, ind2, subjects, threshold):
+        if self._sim is None:
+            return None
+        index, sim, subj, thr = self._sim
+        a, b = index.get(id(ind1)), index.get(id(ind2))
+        if a is None or b is None or subj != tuple(subjects) or thr != float(threshold):
+            return None
+        return bool(sim[a, b])
+
+    def close(self):
+        for eng, _ in self.engines:
+            eng.close()

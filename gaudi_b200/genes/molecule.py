@@ -19,7 +19,7 @@ def enable(**kwargs):
 
 class Molecule(GeneProvider):
     _validate = {"path": "required", "symmetry": None, "hydrogens": None, "pdbfix": None, "vdw_radii": None,
-                 "types_from": None}
+                 "types_from": None, "mol": None}
     _CATALOG = {}
 
     def __init__(self, path=None, vdw_radii=None, types_from=None, mol=None, **kwargs):

@@ -1,0 +1,146 @@
+"""The reference-facing plugin path on the GPU: gene / objective plugins loaded by dotted module
+path, batched ``toolbox.map``, the (mu + lambda) loop with GPU-computed similarity, flexible
+side chains (Rotamers) — each checked against the CPU oracle.  BASELINE.json configs[0]
+(tests/data ligand + receptor, Torsion + Search, Contacts, pop 100 x 10 generations) runs here
+from the committed fixtures."""
+import random
+
+import numpy as np
+import pytest
+
+import golden_util as G
+import oracle_adapter as OA
+from gaudi_b200 import parse
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cuda(built_lib):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch
+
+
+def job(population=100, generations=10, rotamers=None):
+    genes = [
+        {"name": "Protein", "module": "gaudi_b200.genes.molecule", "path": "5er1_protein.mol2",
+         "mol": G.load("5er1_protein_mol2")},
+        {"name": "Ligand", "module": "gaudi_b200.genes.molecule", "path": "5er1_ligand.mol2",
+         "mol": G.load("5er1_ligand_mol2")},
+    ]
+    if rotamers:
+        genes.append({"name": "Rotamers", "module": "gaudi_b200.genes.rotamers", "residues": rotamers[0],
+                      "library": rotamers[1], "with_original": True})
+    genes += [
+        {"name": "Torsion", "module": "gaudi_b200.genes.torsion", "target": "Ligand", "flexibility": 360},
+        {"name": "Search", "module": "gaudi_b200.genes.search", "target": "Ligand/1", "radius": 3.0, "rotate": True},
+    ]
+    return parse.Settings({
+        "output": {"verbose": False, "precision": 3},
+        "ga": {"population": population, "generations": generations, "mu": 1.0, "lambda_": 1.0},
+        "genes": genes,
+        "objectives": [
+            {"name": "Clashes", "module": "gaudi_b200.objectives.contacts", "which": "clashes",
+             "probes": ["Ligand"], "radius": 5.0, "weight": -1.0},
+            {"name": "Contacts", "module": "gaudi_b200.objectives.contacts", "which": "hydrophobic",
+             "probes": ["Ligand"], "radius": 5.0, "weight": -1.0}],
+        "similarity": {"module": "gaudi_b200.similarity.rmsd", "args": [["Ligand"], 2.5], "kwargs": {}},
+    })
+
+
+def oracle_scores(batch, ind):
+    tors, xf, rot = batch.pack([ind])
+    eng = batch.engines[0][0]
+    xyz = OA.express(eng.mobile, tors[0], xf[0], None if rot is None else rot[0])
+    res = OA.contacts(eng.mobile, eng.receptor, eng.params, xyz)
+    return res, xyz
+
+
+def test_configs0_ga_run_matches_oracle(cuda):
+    from gaudi_b200 import algorithms
+    cfg = job(100, 10)
+    pop, log, elite = algorithms.launch(cfg, seed=2026)
+    assert len(pop) == 100 and len(log) == 11 and len(elite) >= 1
+    assert all(ind.fitness.valid for ind in pop)
+    batch = cfg._environment.batch
+    assert len(batch.engines) == 1            # both Contacts objectives share one GPU context
+    # the evolved population's fitness is what the oracle computes for the same alleles
+    for ind in pop[::13]:
+        res, xyz = oracle_scores(batch, ind)
+        got = ind.fitness.values
+        assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash)
+        assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro)
+        lig = ind.find_molecule("Ligand")._expressed_coordinates
+        assert np.abs(lig - xyz[batch.lig_slice]).max() < 1e-4
+    # the GA did its job: the best clash score did not get worse than the random start
+    random.seed(2026)
+    first = [deep for deep in algorithms.launch(job(100, 0), seed=2026)[0]]
+    assert min(i.fitness.values[0] for i in pop) <= min(i.fitness.values[0] for i in first)
+
+
+def test_single_evaluate_and_similarity(cuda):
+    from gaudi_b200 import algorithms, base, similarity
+    cfg = job(12, 0)
+    pop, _, _ = algorithms.launch(cfg, seed=5)
+    env = cfg._environment
+    batched = env.evaluate_population(pop)
+    for ind, want in zip(pop[:4], batched):
+        assert env.evaluate(ind) == want                      # population of one == row of the batch
+        assert env.objectives["Clashes"].evaluate(ind) == want[0]
+    sim = env.batch.similarity_matrix(pop, ["Ligand"], 2.5)
+    ref = OA.rmsd_matrix(np.stack([i.find_molecule("Ligand")._expressed_coordinates for i in pop]))
+    clear = np.abs(ref - 2.5) > 1e-4
+    assert np.array_equal(sim[clear], (ref <= 2.5)[clear])
+    assert pop[0].similar(pop[0]) and sim[0, 0]
+    env.batch._sim = None                                     # no batch bitmask: pairwise GPU call
+    for a, b in ((0, 1), (2, 7)):
+        if clear[a, b]:
+            assert similarity.rmsd(pop[a], pop[b], ["Ligand"], 2.5) == bool(ref[a, b] <= 2.5)
+
+
+def test_rotamers_flexible_side_chains(cuda):
+    """configs[4] in miniature: Rotamers gene on residues around the site + Torsion + Search."""
+    from gaudi_b200 import base
+    rng = np.random.default_rng(11)
+    prot = G.load("5er1_protein_mol2")
+    lig = G.load("5er1_ligand_mol2")
+    # residues with side chains closest to the ligand
+    d = np.linalg.norm(prot.xyz[:, None, :] - lig.xyz[None, ::4, :], axis=2).min(axis=1)
+    near = []
+    for a in np.argsort(d):
+        r, nm = int(prot.resseq[a]), prot.resname[a][:3].upper()
+        if nm not in ("ALA", "GLY", "PRO") and r not in near:
+            near.append(r)
+        if len(near) == 6:
+            break
+    library = {nm: rng.uniform(-180, 180, size=(int(rng.integers(3, 9)), 4)).tolist()
+               for nm in set(prot.resname[a][:3].upper() for a in range(prot.n_atoms))}
+    cfg = job(48, 0, rotamers=([("Protein", str(r)) for r in near], library))
+    random.seed(3)
+    pop = [base.MolecularIndividual(cfg) for _ in range(48)]
+    env = base.Environment(cfg)
+    cfg._environment = env
+    scores = env.evaluate_population(pop)
+    batch = env.batch
+    assert batch.n_rot_res == 6 and batch.mobile.n_atoms > lig.n_atoms
+    assert len(batch.receptor.ms_excl_idx) > 0        # side chains are bonded to the static backbone
+    checked = 0
+    for ind, got in list(zip(pop, scores))[::5]:
+        res, _ = oracle_scores(batch, ind)
+        assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash), (got, res.clash)
+        assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro), (got, res.hydro)
+        checked += 1
+    assert checked >= 9
+    # express parity incl. the rotamer-driven torsions, and CA atoms never move (test_genes_rotamers.py:62-85)
+    tors, xf, rot = batch.pack(pop[:8])
+    eng = batch.engines[0][0]
+    xyz = eng.express(tors, xf, rot).cpu().numpy().astype(np.float64) + eng.centre
+    for p in range(8):
+        assert np.abs(xyz[p] - OA.express(eng.mobile, tors[p], xf[p], rot[p])).max() < 1e-4
+    fixed = np.unique(eng.mobile.tors_fixed[eng.mobile.tors_src < 0])
+    ca_like = [int(a) for a in fixed
+               if not any((int(m[int(a) >> 6]) >> (int(a) & 63)) & 1 for m in eng.mobile.tors_mask)]
+    assert len(ca_like) >= 1
+    assert np.abs(xyz[:, ca_like] - eng.mobile.xyz0[ca_like]).max() < 1e-5

@@ -1,0 +1,139 @@
+"""Host-side logic that needs no GPU: NSGA-II bookkeeping, the greedy niching pass against the
+oracle's restatement, allele plumbing of the gene plugins, sharding arithmetic, and the N > 1
+gather path over gloo (world size 2) with the CPU oracle standing in for the per-shard compute."""
+import os
+import random
+import sys
+
+import numpy as np
+import pytest
+
+import oracle_adapter as OA
+from gaudi_b200 import deaplite, parallel
+from gaudi_b200.algorithms import BatchedMap, niching
+
+O = OA.oracle()
+
+
+class _Ind(object):
+    def __init__(self, values, weights=(-1.0, -1.0)):
+        self.fitness = deaplite.Fitness(weights)
+        self.fitness.values = values
+
+
+def test_fitness_and_nsga2():
+    a, b, c = _Ind((1.0, 1.0)), _Ind((2.0, 2.0)), _Ind((0.5, 3.0))
+    assert a.fitness.dominates(b.fitness) and not b.fitness.dominates(a.fitness)
+    assert not a.fitness.dominates(c.fitness) and not c.fitness.dominates(a.fitness)
+    chosen = deaplite.sel_nsga2([a, b, c], 2)
+    assert set(map(id, chosen)) == {id(a), id(c)}
+    fronts = deaplite.sort_nondominated([a, b, c], 3)
+    assert [len(f) for f in fronts] == [2, 1]
+    pf = deaplite.ParetoFront(lambda x, y: False)
+    pf.update([a, b, c])
+    assert len(pf) == 2
+
+
+def test_niching_matches_oracle_restatement():
+    rng = random.Random(5)
+    inds = [_Ind((rng.random(), rng.random())) for _ in range(40)]
+    sim = {(i, j) for i in range(40) for j in range(40) if i != j and rng.random() < 0.15}
+    sim |= {(j, i) for i, j in sim}
+    index = {id(x): k for k, x in enumerate(inds)}
+    kept = niching(inds, lambda a, b: (index[id(a)], index[id(b)]) in sim)
+    want = O.greedy_niching(list(range(40)), lambda i, j: (i, j) in sim,
+                            lambda i, j: inds[i].fitness <= inds[j].fitness)
+    assert [index[id(x)] for x in kept] == want
+
+
+def test_variation_operators_respect_bounds():
+    random.seed(3)
+    a, b = [10.0, -170.0, 33.3], [-20.0, 160.0, 90.0]
+    deaplite.cx_simulated_binary_bounded(a, b, 5.0, -180.0, 180.0)
+    assert all(-180.0 <= v <= 180.0 for v in a + b)
+    m, = deaplite.mut_polynomial_bounded([0.0, 179.0, -179.0], 5.0, -180.0, 180.0, 1.0)
+    assert all(-180.0 <= v <= 180.0 for v in m)
+    x, y = deaplite.cx_two_point([1, 2, 3, 4], [5, 6, 7, 8])
+    assert sorted(x + y) == [1, 2, 3, 4, 5, 6, 7, 8]
+
+
+def test_batched_map_dispatch():
+    class Env(object):
+        def evaluate_population(self, inds):
+            return [[len(inds)]] * len(inds)
+
+    def evaluate(ind):
+        raise AssertionError("serial path must not run")
+    bm = BatchedMap(Env(), evaluate)
+    assert bm(evaluate, [1, 2, 3]) == [[3], [3], [3]]
+    assert bm(abs, [-1, 2]) == [1, 2]
+
+
+def test_search_allele_product():
+    from gaudi_b200.genes import search as S
+    random.seed(7)
+    t = S.random_translation((1.0, 2.0, 3.0), 4.0)
+    r = S.random_rotation()
+    prod = S.multiply_matrices(t, r)
+    assert np.allclose(prod[:, :3] @ prod[:, :3].T, np.eye(3), atol=1e-12)
+    assert np.allclose(prod[:, 3], [row[3] for row in t])
+    assert np.linalg.norm(prod[:, 3] - np.array([1.0, 2.0, 3.0])) <= 4.0
+    assert np.allclose(prod, O.multiply_3x4(t, r))
+    mid = S.interpolate_xforms(prod, (0, 0, 0), prod, 0.5)
+    assert np.allclose(mid, prod, atol=1e-12)
+
+
+def test_shard_bounds():
+    for n in (0, 1, 7, 65536, 65537):
+        for w in (1, 2, 3, 8):
+            b = parallel.shard_bounds(n, w)
+            assert b[0] == 0 and b[-1] == n and all(b[i] <= b[i + 1] for i in range(w))
+            assert max(b[i + 1] - b[i] for i in range(w)) - min(b[i + 1] - b[i] for i in range(w)) <= 1
+
+
+def _gloo_worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from gaudi_b200 import model as M, synth
+    params = M.ContactParams()
+    lig = synth.make_ligand(12, 3, seed=1)
+    rec = synth.make_receptor(300, seed=2, params=params)
+    tors, xf = synth.make_alleles(9, 3, seed=3)          # 9 individuals over 2 ranks: ragged
+
+    def shard(t, x):          # the CPU oracle stands in for the GPU on this rank's slice
+        res = []
+        for k in range(t.shape[0]):
+            r = OA.contacts(lig, rec, params, OA.express(lig, t[k], x[k]), with_slack=False)
+            res.append((r.clash, r.hydro))
+        return np.array(res).reshape(-1, 2)
+    full = parallel.sharded_evaluate(shard, (tors, xf))
+    conf = np.stack([OA.express(lig, tors[k], xf[k]) for k in range(9)]).astype(np.float32)
+    b = parallel.shard_bounds(9, world)
+
+    def rows(allc, r0, r1):
+        ref = OA.rmsd_matrix(allc.numpy().astype(np.float64), rows=range(r0, r1)) <= 2.5
+        words = np.packbits(np.pad(ref, ((0, 0), (0, 32 - ref.shape[1] % 32)))[:, :32 * ((ref.shape[1] + 31) // 32)],
+                            axis=1, bitorder="little").view(np.uint32).astype(np.int64)
+        return torch.as_tensor(words.astype(np.uint32).view(np.int32))
+    bits = parallel.sharded_rmsd_bits(rows, torch.as_tensor(conf[b[rank]:b[rank + 1]]))
+    if rank == 0:
+        want = shard(tors, xf)
+        ref = OA.rmsd_matrix(conf.astype(np.float64)) <= 2.5
+        from gaudi_b200.engine import bits_to_bool
+        np.save(out, np.array([float(np.abs(full.numpy() - want).max()),
+                               float((bits_to_bool(bits.numpy(), 9) != ref).sum())]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_gather_world2_gloo(tmp_path):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "res.npy")
+    port = 29500 + random.randint(0, 2000)
+    mp.spawn(_gloo_worker, args=(2, port, out), nprocs=2, join=True)
+    res = np.load(out)
+    assert res[0] == 0.0          # gathered fitness == single-process fitness, bit for bit
+    assert res[1] == 0.0          # row-block sharded similarity bitmask == full matrix
