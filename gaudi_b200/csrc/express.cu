@@ -39,44 +39,55 @@ express_kernel(const ExpressArgs a) {
             sx[i] = a.xyz0[3 * i]; sy[i] = a.xyz0[3 * i + 1]; sz[i] = a.xyz0[3 * i + 2];
         }
         __syncwarp();
-        for (int t = 0; t < a.T; ++t) {
-            const int src = a.tsrc[t];
-            double alpha;
-            if (src >= 0) {
-                alpha = a.tors[(size_t)p * a.n_allele_tors + src];
-                if (a.tsnap[t]) alpha = (alpha <= 0.0) ? 0.0 : 180.0;   // torsion.py:159-160
-            } else {
-                const int code = -(src + 1), res = code >> 2, chi = code & 3;
-                const int r0 = a.rot_ptr[res], n = a.rot_ptr[res + 1] - r0;
-                int k = (int)(a.rot[(size_t)p * a.n_res + res] * (double)n);  // rotamers.py:150
-                k = min(max(k, 0), n - 1);
-                alpha = a.rot_delta[(size_t)(r0 + k) * 4 + chi];
+        // The angle of every bond (allele column or rotamer table row) and its sine / cosine are
+        // evaluated 32 bonds at a time, one per lane, then broadcast bond by bond.
+        for (int t0 = 0; t0 < a.T; t0 += 32) {
+            const int tl = t0 + lane;
+            double my_alpha = 0.0, my_s = 0.0, my_c = 1.0;
+            if (tl < a.T) {
+                const int src = a.tsrc[tl];
+                if (src >= 0) {
+                    my_alpha = a.tors[(size_t)p * a.n_allele_tors + src];
+                    if (a.tsnap[tl]) my_alpha = (my_alpha <= 0.0) ? 0.0 : 180.0;   // torsion.py:159-160
+                } else {
+                    const int code = -(src + 1), res = code >> 2, chi = code & 3;
+                    const int r0 = a.rot_ptr[res], n = a.rot_ptr[res + 1] - r0;
+                    int k = (int)(a.rot[(size_t)p * a.n_res + res] * (double)n);  // rotamers.py:150
+                    k = min(max(k, 0), n - 1);
+                    my_alpha = a.rot_delta[(size_t)(r0 + k) * 4 + chi];
+                }
+                if (my_alpha != 0.0) sincos(my_alpha * (3.14159265358979323846 / 180.0), &my_s, &my_c);
             }
-            if (alpha != 0.0) {   // warp-uniform
-                const int f = a.tfixed[t], m = a.tmoving[t];
-                const double bx = sx[m], by = sy[m], bz = sz[m];
-                double ux = bx - sx[f], uy = by - sy[f], uz = bz - sz[f];
-                const double inv = 1.0 / sqrt(ux * ux + uy * uy + uz * uz);
-                ux *= inv; uy *= inv; uz *= inv;
-                double s, c;
-                sincos(alpha * (3.14159265358979323846 / 180.0), &s, &c);
-                const double omc = 1.0 - c;
-                __syncwarp();
-                const uint64_t* mask = a.tmask + (size_t)t * a.W;
-                for (int i = lane; i < a.M; i += 32) {
-                    if ((mask[i >> 6] >> (i & 63)) & 1ull) {
-                        const double vx = sx[i] - bx, vy = sy[i] - by, vz = sz[i] - bz;
-                        const double crx = uy * vz - uz * vy;
-                        const double cry = uz * vx - ux * vz;
-                        const double crz = ux * vy - uy * vx;
-                        const double dot = ux * vx + uy * vy + uz * vz;
-                        sx[i] = bx + vx * c + crx * s + ux * dot * omc;
-                        sy[i] = by + vy * c + cry * s + uy * dot * omc;
-                        sz[i] = bz + vz * c + crz * s + uz * dot * omc;
+            const int tn = min(32, a.T - t0);
+            for (int tt = 0; tt < tn; ++tt) {
+                const int t = t0 + tt;
+                const double alpha = __shfl_sync(0xffffffffu, my_alpha, tt);
+                if (alpha != 0.0) {   // warp-uniform
+                    const double s = __shfl_sync(0xffffffffu, my_s, tt);
+                    const double c = __shfl_sync(0xffffffffu, my_c, tt);
+                    const int f = a.tfixed[t], m = a.tmoving[t];
+                    const double bx = sx[m], by = sy[m], bz = sz[m];
+                    double ux = bx - sx[f], uy = by - sy[f], uz = bz - sz[f];
+                    const double inv = 1.0 / sqrt(ux * ux + uy * uy + uz * uz);
+                    ux *= inv; uy *= inv; uz *= inv;
+                    const double omc = 1.0 - c;
+                    __syncwarp();
+                    const uint64_t* mask = a.tmask + (size_t)t * a.W;
+                    for (int i = lane; i < a.M; i += 32) {
+                        if ((mask[i >> 6] >> (i & 63)) & 1ull) {
+                            const double vx = sx[i] - bx, vy = sy[i] - by, vz = sz[i] - bz;
+                            const double crx = uy * vz - uz * vy;
+                            const double cry = uz * vx - ux * vz;
+                            const double crz = ux * vy - uy * vx;
+                            const double dot = ux * vx + uy * vy + uz * vz;
+                            sx[i] = bx + vx * c + crx * s + ux * dot * omc;
+                            sy[i] = by + vy * c + cry * s + uy * dot * omc;
+                            sz[i] = bz + vz * c + crz * s + uz * dot * omc;
+                        }
                     }
                 }
+                __syncwarp();
             }
-            __syncwarp();
         }
         // Search: xform = T . R . to_zero(origin)  ->  x' = R (x - origin) + t
         double m[12];
