@@ -23,6 +23,8 @@ struct RmsdArgs {
     const float* xyz;
     float* out; uint32_t* bits; int words;
     float thr2, inv_a;
+    int sym, R0, R1;      // bitmask-only calls: tiles below the diagonal of the square part are
+                          // skipped and filled in by their mirror tile (the matrix is symmetric)
 };
 
 __device__ __forceinline__ void cp_async_4(float* smem_dst, const float* gmem_src) {
@@ -46,6 +48,10 @@ rmsd_tile_kernel(const RmsdArgs a) {
     const int r_base = a.row0 + blockIdx.y * kRT;   // first row (conformer index) of the tile
     const int c_base = blockIdx.x * kRT;            // first column
     const int n_chunks = (a.K + RK - 1) / RK;
+    const int rb = a.R0 + blockIdx.y, cbk = blockIdx.x;      // tile coordinates in units of kRT
+    const bool in_square = a.sym && cbk >= a.R0 && cbk < a.R1;
+    if (in_square && cbk < rb) return;                        // written by tile (cbk, rb)
+    const bool mirror = in_square && cbk > rb;
 
     // stage chunk `c` into buffer `buf`: flat element e -> (conformer r = e / RK, coordinate k = e % RK);
     // consecutive threads read consecutive coordinates of a conformer (coalesced), and scatter
@@ -94,7 +100,10 @@ rmsd_tile_kernel(const RmsdArgs a) {
         __syncthreads();
     }
 
-    // epilogue
+    // epilogue: values straight to global; similarity bits through a 128 x 128-bit tile in shared
+    // memory (the operand buffers are free now), written out coalesced and, for tiles above the
+    // diagonal of a bitmask-only call, once more transposed
+    uint32_t* Wn = reinterpret_cast<uint32_t*>(smem_f);       // [128 rows][4 words]
     const bool want_values = a.out != nullptr;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -117,9 +126,24 @@ rmsd_tile_kernel(const RmsdArgs a) {
                 word |= __shfl_xor_sync(0xffffffffu, word, 1);
                 word |= __shfl_xor_sync(0xffffffffu, word, 2);
                 word |= __shfl_xor_sync(0xffffffffu, word, 4);
-                const int w = (c_base + h * 64) / 32 + (tx >> 3);
-                if ((tx & 7) == 0 && row_ok && w < a.words)
-                    a.bits[(size_t)(row - a.row0) * a.words + w] = word;
+                if ((tx & 7) == 0) Wn[(i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)) * 4 + h * 2 + (tx >> 3)] = word;
+            }
+        }
+    }
+    if (a.bits != nullptr) {
+        __syncthreads();
+        for (int w = tid; w < kRT * 4; w += 256) {
+            const int r = w >> 2, q = w & 3, row = r_base + r, wc = c_base / 32 + q;
+            if (row < a.row1 && wc < a.words) a.bits[(size_t)(row - a.row0) * a.words + wc] = Wn[w];
+        }
+        if (mirror) {
+            for (int w = tid; w < kRT * 4; w += 256) {
+                const int cidx = w & 127, rw = w >> 7;
+                unsigned t = 0;
+#pragma unroll 8
+                for (int r = 0; r < 32; ++r) t |= ((Wn[(32 * rw + r) * 4 + (cidx >> 5)] >> (cidx & 31)) & 1u) << r;
+                const int mrow = c_base + cidx, wc = r_base / 32 + rw;
+                if (mrow < a.row1 && mrow < a.N && wc < a.words) a.bits[(size_t)(mrow - a.row0) * a.words + wc] = t;
             }
         }
     }
@@ -146,6 +170,8 @@ int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, 
     a.N = N; a.A = A; a.K = 3 * A; a.row0 = row0; a.row1 = row1;
     a.xyz = xyz; a.out = out_rmsd; a.bits = out_bits; a.words = (N + 31) / 32;
     a.thr2 = (float)(thr * thr); a.inv_a = 1.0f / (float)A;
+    a.sym = (out_rmsd == nullptr && out_bits != nullptr && row0 % kRT == 0) ? 1 : 0;
+    a.R0 = row0 / kRT; a.R1 = (row1 + kRT - 1) / kRT;
     dim3 grid((N + kRT - 1) / kRT, (row1 - row0 + kRT - 1) / kRT);
     if (a.K % 36 == 0) return launch_rmsd_rk<36>(a, grid, s);
     return launch_rmsd_rk<32>(a, grid, s);

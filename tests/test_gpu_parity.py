@@ -225,6 +225,16 @@ def test_rmsd_matrix(small_system, torch_cuda):
     # row block == the same rows of the full matrix (row-block sharding)
     out2, bits2 = eng.rmsd_matrix(conf, row0=100, row1=231, threshold=2.5)
     assert torch_cuda.equal(out2, out[100:231]) and torch_cuda.equal(bits2, bits[100:231])
+    # bitmask-only calls compute each off-diagonal tile once and mirror it: same words
+    _, b_only = eng.rmsd_matrix(conf, threshold=2.5, values=False)
+    assert torch_cuda.equal(b_only, bits)
+    big = synth.make_conformers(n=1500, n_atoms=60, seed=6)
+    _, b_full = eng.rmsd_matrix(big, threshold=2.5)                       # values + bits: no mirroring
+    _, b_sym = eng.rmsd_matrix(big, threshold=2.5, values=False)
+    assert torch_cuda.equal(b_sym, b_full)
+    for r0, r1 in ((128, 1500), (256, 777), (100, 900)):                  # row blocks (multi-GPU shards)
+        _, b_blk = eng.rmsd_matrix(big, row0=r0, row1=r1, threshold=2.5, values=False)
+        assert torch_cuda.equal(b_blk, b_full[r0:r1]), (r0, r1)
     # properties at full size: symmetric, zero diagonal
     big = synth.make_conformers(n=2048, n_atoms=60, seed=5)
     o, _ = eng.rmsd_matrix(big, threshold=2.5, bits=False)
