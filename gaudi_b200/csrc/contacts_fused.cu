@@ -221,6 +221,42 @@ contacts_fused_kernel(const FusedArgs f) {
             }
             if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint32_t)st;
         }
+        if (S == 1 && a.cull) {
+            // Refine: a leaf stays only if some mobile atom is within reach of its box (the
+            // sphere/box test above keeps ~40 leaves, this keeps ~27; the sweep of a leaf costs
+            // more than this test).  One leaf per lane, compacted in place.
+            __syncwarp();
+            int nout = 0;
+            for (int base = 0; base < nl; base += 32) {
+                const int i = base + lane;
+                uint32_t st = 0;
+                bool keep = false;
+                if (i < nl) {
+                    st = list[i];
+                    keep = a.always[st] != 0u;
+                    if (!keep) {
+                        const float* bx = f.sub_box + (size_t)st * 8;
+                        const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
+                        const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
+                        float mn = 3e38f;
+                        for (int s = 0; s < a.M; ++s) {
+                            const float4 m = ligx[s];
+                            const float ex = fmaxf(fmaxf(b0 - m.x, m.x - b3), 0.f);
+                            const float ey = fmaxf(fmaxf(b1 - m.y, m.y - b4), 0.f);
+                            const float ez = fmaxf(fmaxf(b2 - m.z, m.z - b5), 0.f);
+                            mn = fminf(mn, fmaf(ez, ez, fmaf(ey, ey, ex * ex)));
+                        }
+                        keep = mn <= reach * reach;
+                    }
+                }
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                __syncwarp();
+                if (keep) list[nout + __popc(mask & ((1u << lane) - 1u))] = st;
+                nout += __popc(mask);
+                __syncwarp();
+            }
+            nl = nout;
+        }
         if (S == 1) { if (lane == 0) nlist_p[0] = nl; }
         team_sync<S>();
         const int nlist = nlist_p[0];
@@ -244,15 +280,24 @@ contacts_fused_kernel(const FusedArgs f) {
                 ms[k] = 3e38f;
                 tests += (stv[k] < (uint32_t)f.NST) ? (unsigned long long)kSubTile * a.M : 0ull;
             }
-#pragma unroll 4
-            for (int s = 0; s < a.n_seed; ++s) {
+            // two mobile atoms per step: 6 FFMA + one 3-input FMNMX3 per receptor atom
+            int s = 0;
+#pragma unroll 2
+            for (; s + 1 < a.n_seed; s += 2) {
+                const float4 m = ligc[s], q = ligc[s + 1];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ms[k] = fminf(ms[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
+                                               fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
+            }
+            if (s < a.n_seed) {
                 const float4 m = ligc[s];
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     ms[k] = fminf(ms[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
             }
             float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
-            for (int s = a.n_seed; s < a.M; ++s) {
+            for (s = a.n_seed; s < a.M; ++s) {
                 const float4 m = ligc[s];
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
