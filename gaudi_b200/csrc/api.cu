@@ -129,6 +129,8 @@ int gmm_set_params(gmm_ctx* c, double zone_radius, double clash_threshold, doubl
     c->prm.hydro_thr = hydrophobic_threshold; c->prm.hb_allow = hbond_allowance;
     c->prm.amv = assumed_max_vdw; c->prm.cutoff = cutoff; c->prm.weight = weight;
     c->prm.options = options;
+    c->prm.f_clash_thr = (float)clash_threshold; c->prm.f_hydro_thr = (float)hydrophobic_threshold;
+    c->prm.f_allow = (float)hbond_allowance; c->prm.f_amv = (float)assumed_max_vdw;
     c->has_params = true;
     return GMM_OK;
 }

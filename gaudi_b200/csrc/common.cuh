@@ -53,6 +53,7 @@ struct Params {
     double cutoff;
     double weight;
     int options;
+    float f_clash_thr, f_hydro_thr, f_allow, f_amv;   // fp32 copies for score_pair
 };
 
 struct PairScore {
@@ -68,51 +69,55 @@ struct PairScore {
 //   positive / negative split:      contacts.py:176-187
 //   LJ-like energy:                 contacts.py:215-241
 //   spherical-cap overlap volume:   contacts.py:243-268 (pi literal 3.14159265359)
+// Arithmetic is IEEE fp32 (correctly rounded sqrt and divisions, no fast-math): per pair the
+// values carry ~1e-6 relative error, two orders below the 1e-4 the sums are held to, and the
+// accept/reject decisions move by < 1e-6 A, inside the 1e-4 A band north_star exempts.  An fp64
+// version of this function cost 16 % of the whole kernel (DSQRT + 3 DDIV per pair) for digits
+// nobody reads.  Every kernel (fused, tiled, static-pair set-up, pair dump) calls this one
+// function, so their results stay bit-identical to each other.
 __device__ __forceinline__ PairScore score_pair(float ax, float ay, float az, float ra, unsigned fa,
                                                 float bx, float by, float bz, float rb, unsigned fb,
                                                 const Params& p) {
     PairScore o;
     o.clash_fx = 0; o.hydro_fx = 0; o.kind = 0; o.clash_val = 0.0; o.hydro_val = 0.0;
-    const double dx = (double)ax - (double)bx;
-    const double dy = (double)ay - (double)by;
-    const double dz = (double)az - (double)bz;
-    const double d = sqrt(dx * dx + dy * dy + dz * dz);
-    const double Ra = (double)ra, Rb = (double)rb;
+    const float dx = ax - bx, dy = ay - by, dz = az - bz;
+    const float d = sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
     const bool hb = ((fa & GMM_F_DONOR) && (fb & GMM_F_ACCEPTOR)) ||
                     ((fb & GMM_F_DONOR) && (fa & GMM_F_ACCEPTOR));
-    const double ov = Ra + Rb - d - ((hb && p.hb_allow != 0.0) ? p.hb_allow : 0.0);
-    o.overlap = ov;
-    const double maxr = fmax(Ra, Rb);
+    const float r0 = ra + rb;
+    const float ov = r0 - d - ((hb && p.f_allow != 0.f) ? p.f_allow : 0.f);
+    o.overlap = (double)ov;
+    const float maxr = fmaxf(ra, rb);
     // which == 'hydrophobic': DetectClash threshold = hydrophobic_threshold
-    if (d <= maxr + p.amv - p.hydro_thr && ov >= p.hydro_thr && ov <= p.clash_thr &&
+    if (d <= maxr + p.f_amv - p.f_hydro_thr && ov >= p.f_hydro_thr && ov <= p.f_clash_thr &&
         (fa & GMM_F_HYDROPHOBIC) && (fb & GMM_F_HYDROPHOBIC)) {
-        const double r0 = Ra + Rb;
-        const double dist = r0 - ov;
-        double x = r0 / dist;
+        const float dist = r0 - ov;
+        float x = r0 / dist;
         x = x * x; x = x * x * x;                 // (r0 / distance) ** 6
-        double e = x * x - 2.0 * x;
-        e = fmin(fmax(e, -1.0e9), 1.0e9);
-        o.hydro_val = e;
-        o.hydro_fx = __double2ll_rn(e * kFxScale);
+        float e = fmaf(x, x, -2.f * x);
+        e = fminf(fmaxf(e, -1.0e9f), 1.0e9f);
+        o.hydro_val = (double)e;
+        o.hydro_fx = __double2ll_rn((double)e * kFxScale);
         o.kind |= 2;
     }
     // which == 'clashes': DetectClash threshold = clash_threshold, then overlap > clash_threshold
-    if (d <= maxr + p.amv - p.clash_thr && ov >= p.clash_thr && ov > p.clash_thr) {
-        const double dd = Ra + Rb - ov;
-        double v;
-        if (dd == 0.0) {
-            v = 1000.0;
+    if (d <= maxr + p.f_amv - p.f_clash_thr && ov > p.f_clash_thr) {
+        const float dd = r0 - ov;
+        float v;
+        if (dd == 0.f) {
+            v = 1000.f;
         } else {
-            double ha = 0.0, hbb = 0.0;
-            if (dd < Ra + Rb) {
-                ha = (Rb * Rb - (dd - Ra) * (dd - Ra)) / (2.0 * dd);
-                hbb = (Ra * Ra - (dd - Rb) * (dd - Rb)) / (2.0 * dd);
+            float ha = 0.f, hbb = 0.f;
+            if (dd < r0) {
+                const float inv = 1.f / (2.f * dd);
+                ha = (rb * rb - (dd - ra) * (dd - ra)) * inv;
+                hbb = (ra * ra - (dd - rb) * (dd - rb)) * inv;
             }
-            v = (3.14159265359 / 3.0) * (ha * ha * (3.0 * Ra - ha) + hbb * hbb * (3.0 * Rb - hbb));
+            v = (3.14159265359f / 3.f) * (ha * ha * (3.f * ra - ha) + hbb * hbb * (3.f * rb - hbb));
         }
-        v = fmin(fabs(v), 1.0e9);
-        o.clash_val = v;
-        o.clash_fx = __double2ll_rn(v * kFxScale);
+        v = fminf(fabsf(v), 1.0e9f);
+        o.clash_val = (double)v;
+        o.clash_fx = __double2ll_rn((double)v * kFxScale);
         o.kind |= 1;
     }
     return o;
