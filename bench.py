@@ -214,14 +214,17 @@ def run_b200(args):
     dense_flops_per_ind = FLOPS_PER_PAIR_TEST * (L * R + L * (L - 1) // 2)
 
     # e2e: host buffers through the C ABI (H2D alleles, kernels, D2H scores) per step
-    th, xh = np.ascontiguousarray(tors[lo:hi]), np.ascontiguousarray(xf[lo:hi])
-    eng.evaluate_host(th, xh)
+    th = torch.as_tensor(np.ascontiguousarray(tors[lo:hi])).pin_memory()      # pinned host inputs
+    xh = torch.as_tensor(np.ascontiguousarray(xf[lo:hi])).pin_memory()
+    s_pin = torch.empty((shard, 2), dtype=torch.float64).pin_memory()         # pinned host outputs
+    c_pin = torch.empty((shard, 2), dtype=torch.int32).pin_memory()
+    eng.evaluate_host(th, xh, scores_out=s_pin, counts_out=c_pin)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n_e2e = max(3, min(args.steps, 10))
     e0.record()
     for _ in range(n_e2e):
-        s_h, c_h, _ = eng.evaluate_host(th, xh)
+        s_h, c_h, _ = eng.evaluate_host(th, xh, scores_out=s_pin, counts_out=c_pin)
         if world > 1:
             dist.all_gather_into_tensor(gathered, scores)
     e1.record()
@@ -230,8 +233,9 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
-    h2d = int(th.nbytes + xh.nbytes)
-    d2h = int(s_h.nbytes + c_h.nbytes)
+    h2d = int(th.numel() * th.element_size() + xh.numel() * xh.element_size())
+    d2h = int(s_h.numel() * s_h.element_size() + c_h.numel() * c_h.element_size())
+    assert torch.equal(s_pin.to(dev), scores[:shard]), "e2e path disagrees with the device path"
 
     extra = {}
     if rank == 0 and world == 1 and not args.quick:
@@ -250,7 +254,7 @@ def run_b200(args):
                        else "single GPU",
                        "l2": "192 MiB buffer written between timed iterations",
                        "culling": "receptor tiles out of reach of a pose are skipped (results bit-identical to dense)"},
-            "roofline": {"bound": "fp32", "kernel": "contacts_sweep_kernel", "achieved": achieved, "peak": peak32,
+            "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": achieved, "peak": peak32,
                          "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None, "traffic": None,
                          "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
                          "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,

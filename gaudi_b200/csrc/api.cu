@@ -476,20 +476,40 @@ int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const doub
     }
     unsigned char* hp = static_cast<unsigned char*>(c->h_pin);
     unsigned char* dp = static_cast<unsigned char*>(c->d_stage);
-    if (nt) memcpy(hp + o_t, torsion_deg_h, nt);
-    if (nx) memcpy(hp + o_x, xform_h, nx);
-    if (nr) memcpy(hp + o_r, rot_allele_h, nr);
-    const size_t in_bytes = o_s;   // contiguous block of inputs
-    if (in_bytes) GMM_CUDA(cudaMemcpyAsync(dp, hp, in_bytes, cudaMemcpyHostToDevice, s));
+    // Buffers the caller already holds in page-locked memory (cudaHostAlloc / cudaHostRegister /
+    // torch pin_memory) are copied from and to directly; pageable ones go through the context's
+    // pinned staging area.
+    auto pinned = [](const void* ptr) {
+        if (!ptr) return false;
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+        return at.type == cudaMemoryTypeHost;
+    };
+    auto h2d = [&](size_t off, const void* src, size_t n) -> int {
+        if (!n) return GMM_OK;
+        if (pinned(src)) { GMM_CUDA(cudaMemcpyAsync(dp + off, src, n, cudaMemcpyHostToDevice, s)); return GMM_OK; }
+        memcpy(hp + off, src, n);
+        GMM_CUDA(cudaMemcpyAsync(dp + off, hp + off, n, cudaMemcpyHostToDevice, s));
+        return GMM_OK;
+    };
+    if ((rc = h2d(o_t, torsion_deg_h, nt))) return rc;
+    if ((rc = h2d(o_x, xform_h, nx))) return rc;
+    if ((rc = h2d(o_r, rot_allele_h, nr))) return rc;
     rc = gmm_evaluate(c, P, nt ? (const double*)(dp + o_t) : nullptr, nx ? (const double*)(dp + o_x) : nullptr,
                       nr ? (const double*)(dp + o_r) : nullptr, nxyz ? (float*)(dp + o_xyz) : nullptr,
                       (double*)(dp + o_s), (int32_t*)(dp + o_c), stream);
     if (rc) return rc;
-    GMM_CUDA(cudaMemcpyAsync(hp + o_s, dp + o_s, (o_xyz - o_s) + nxyz, cudaMemcpyDeviceToHost, s));
+    struct Out { void* dst; size_t off, n; bool direct; };
+    Out outs[3] = {{out_scores_h, o_s, ns, false}, {out_counts_h, o_c, out_counts_h ? nc : 0, false},
+                   {out_xyz_h, o_xyz, nxyz, false}};
+    for (auto& o : outs) {
+        if (!o.n) continue;
+        o.direct = pinned(o.dst);
+        GMM_CUDA(cudaMemcpyAsync(o.direct ? o.dst : (void*)(hp + o.off), dp + o.off, o.n, cudaMemcpyDeviceToHost, s));
+    }
     GMM_CUDA(cudaStreamSynchronize(s));
-    memcpy(out_scores_h, hp + o_s, ns);
-    if (out_counts_h) memcpy(out_counts_h, hp + o_c, nc);
-    if (nxyz) memcpy(out_xyz_h, hp + o_xyz, nxyz);
+    for (auto& o : outs)
+        if (o.n && !o.direct) memcpy(o.dst, hp + o.off, o.n);
     return GMM_OK;
 }
 

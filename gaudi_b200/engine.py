@@ -142,18 +142,34 @@ class Engine(object):
                                         _dev_ptr(scores), _dev_ptr(cnt), self._stream()))
         return scores, cnt, xyz
 
-    def evaluate_host(self, torsions=None, xforms=None, rot_alleles=None, want_xyz=False):
-        """Host buffers in, host buffers out (H2D + kernels + D2H inside the call)."""
-        t = None if torsions is None else np.ascontiguousarray(torsions, np.float64)
-        x = None if xforms is None else np.ascontiguousarray(xforms, np.float64)
-        r = None if rot_alleles is None else np.ascontiguousarray(rot_alleles, np.float64)
+    def evaluate_host(self, torsions=None, xforms=None, rot_alleles=None, want_xyz=False,
+                      scores_out=None, counts_out=None):
+        """Host buffers in, host buffers out (H2D + kernels + D2H inside the call).
+
+        Inputs may be numpy arrays or CPU torch tensors; page-locked ones
+        (``torch.empty(..., pin_memory=True)``) are copied from directly, pageable ones are
+        staged.  ``scores_out`` / ``counts_out``: optional preallocated (pinned) CPU tensors."""
+        def host(a):
+            if a is None:
+                return None, None
+            if isinstance(a, torch.Tensor):
+                a = a if (a.dtype == torch.float64 and a.is_contiguous()) else a.to(torch.float64).contiguous()
+                return a, C.c_void_p(a.data_ptr())
+            a = np.ascontiguousarray(a, np.float64)
+            return a, _np_ptr(a)
+        t, tp = host(torsions)
+        x, xp = host(xforms)
+        r, rp = host(rot_alleles)
         P = int((t if t is not None else (x if x is not None else r)).shape[0])
-        scores = np.empty((P, 2), np.float64)
-        cnt = np.empty((P, 2), np.int32)
+        if scores_out is None:
+            scores_out = np.empty((P, 2), np.float64)
+        if counts_out is None:
+            counts_out = np.empty((P, 2), np.int32)
+        sp = C.c_void_p(scores_out.data_ptr()) if isinstance(scores_out, torch.Tensor) else _np_ptr(scores_out)
+        cp = C.c_void_p(counts_out.data_ptr()) if isinstance(counts_out, torch.Tensor) else _np_ptr(counts_out)
         xyz = np.empty((P, self.mobile.n_atoms, 3), np.float32) if want_xyz else None
-        _lib.check(self._L.gmm_evaluate_host(self._h, P, _np_ptr(t), _np_ptr(x), _np_ptr(r), _np_ptr(xyz),
-                                             _np_ptr(scores), _np_ptr(cnt), self._stream()))
-        return scores, cnt, xyz
+        _lib.check(self._L.gmm_evaluate_host(self._h, P, tp, xp, rp, _np_ptr(xyz), sp, cp, self._stream()))
+        return scores_out, counts_out, xyz
 
     def rmsd_matrix(self, xyz, row0=0, row1=None, threshold=2.5, values=True, bits=True):
         """Rows [row0, row1) of the all-pairs RMSD matrix of (N, A, 3) conformers.
