@@ -189,6 +189,7 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
                     cudaStream_t s, void* workspace = nullptr);
 int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
                           int* handled);
+bool fused_applicable(const gmm_ctx* c);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);

@@ -457,10 +457,11 @@ static void plan_chunks(const gmm_ctx* c, int P, int* tiles_per_chunk, int* n_ch
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// scratch layout: [coords P*M*3 f32][zone P*ZW u32][partial P*n_chunks*4 i64]
+// scratch layout: [coords P*M*3 f32] and, for the tiled path only, [zone P*ZW u32][partial P*n_chunks*4 i64]
 size_t contacts_scratch_bytes(const gmm_ctx* c, int P) {
     const size_t ZW = (size_t)c->n_tiles * 4;
     size_t b = align_up((size_t)P * c->M * 3 * sizeof(float), 256);
+    if (fused_applicable(c)) return b + 256;      // the one-kernel path only parks coordinates here
     b += align_up((size_t)P * ZW * sizeof(uint32_t), 256);
     // P * n_chunks(P) <= kGroup * want_ctas + P for every P (see plan_chunks): monotone bound
     b += align_up(((size_t)kGroup * 148 * 12 + kGroup + (size_t)P) * 4 * sizeof(long long), 256);

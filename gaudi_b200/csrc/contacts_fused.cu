@@ -7,15 +7,16 @@
 //               re-centred on the pose's own centre c (x-c, y-c, z-c, |.|^2);
 //   1  cull     lanes test the boxes of 32-atom receptor leaves against the pose in parallel
 //               and ballot-compact the survivors into a list (all leaves when culling is off);
+//               a second pass keeps a leaf only if some mobile atom is within reach of its box;
 //   2  sweep    four leaves at a time, one atom of each per lane.  With a = -2 (r - c) and
 //               n = |r - c|^2 kept in registers, d^2 = n + min_i (a . m_i + |m_i|^2): THREE FFMA
-//               and one FMNMX per pair test, branch-free.  Working relative to the pose centre
+//               per pair test and one FMNMX3 per two, branch-free.  Working relative to the pose centre
 //               keeps every magnitude small, so this expanded form is accurate to ~1e-4 A^2;
 //               receptor atoms whose min d^2 lands within a margin of radius^2 get their zone
 //               membership re-decided with exact differences (rare), so zone bits are identical
 //               to the direct-difference definition.  Candidates (atoms that can have a contact
 //               at all) are expanded against the mobile atoms with exact differences and the
-//               surviving pairs scored in fp64 (score_pair), as in contacts.cu;
+//               surviving pairs scored with all lanes busy (score_pair), as in contacts.cu;
 //   3  static   static-static pairs are stored as per-leaf edge lists; leaves with a non-empty
 //               zone word walk their edges with coalesced loads and test both zone bits in
 //               shared memory;
@@ -418,6 +419,21 @@ contacts_fused_kernel(const FusedArgs f) {
 
 void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a);
 
+static size_t fused_ind_bytes(const gmm_ctx* c) {
+    const int NST = c->Rpad / kSubTile, MW = (c->Mp + 31) / 32;
+    size_t ind = (size_t)2 * c->Mp * sizeof(float4) + 3 * sizeof(float4) + 4 * sizeof(long long) + 4 * sizeof(int) +
+                 (size_t)(NST + 4) * 4 + (size_t)(NST + 1) * 4 + (size_t)MW * 4;
+    return (ind + 15) / 16 * 16;
+}
+static const size_t kFusedQueues = (size_t)4 * (kCandQ + kPairQ) * sizeof(uint32_t);
+static const size_t kFusedSmemLimit = 200 * 1024;
+
+// True when gmm_contacts / gmm_evaluate will run the one-kernel path for this context.
+bool fused_applicable(const gmm_ctx* c) {
+    if (c->prm.options & GMM_OPT_TILED) return false;
+    return fused_ind_bytes(c) + kFusedQueues <= kFusedSmemLimit;
+}
+
 // Returns GMM_OK and sets *handled = 1 when the fused kernel ran; *handled = 0 when the model
 // does not fit its shared-memory plan (the caller then uses the tiled kernels of contacts.cu).
 int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
@@ -430,12 +446,10 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge; f.rr_val = c->d_rr_val;
     f.mm_pairs = c->d_mm_pairs; f.n_mm = c->n_mm;
     f.scores = scores; f.counts = counts;
-    size_t ind = (size_t)2 * f.s.Mp * sizeof(float4) + 3 * sizeof(float4) + 4 * sizeof(long long) + 4 * sizeof(int) +
-                 (size_t)(f.NST + 4) * 4 + (size_t)(f.NST + 1) * 4 + (size_t)f.s.MW * 4;
-    ind = (ind + 15) / 16 * 16;
+    const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
-    const size_t queues = (size_t)4 * (kCandQ + kPairQ) * sizeof(uint32_t);
-    const size_t limit = 200 * 1024;
+    const size_t queues = kFusedQueues;
+    const size_t limit = kFusedSmemLimit;
     int S = (P >= 148 * 8) ? 1 : 4;
     if (S == 1 && 4 * ind + queues > limit) S = 4;
     if (ind + queues > limit) return GMM_OK;    // not handled

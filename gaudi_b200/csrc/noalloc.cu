@@ -1,9 +1,9 @@
 // gmm_evaluate_static: population evaluate for callers that must not allocate device memory.
 //
-// Who needs this.  gmm_evaluate() keeps the expressed coordinates (when the caller does not
-// ask for them), the per-individual zone bitmask and the per-chunk partial sums in a scratch
-// buffer owned by the context, and grows that buffer with cudaMalloc the first time it sees a
-// larger population.  Some hosts of this library cannot live with that:
+// Who needs this.  gmm_evaluate() parks the expressed coordinates (when the caller does not ask
+// for them; the tiled Contacts path also a per-individual zone bitmask and per-chunk partial
+// sums) in a scratch buffer owned by the context, and grows that buffer with cudaMalloc the first
+// time it sees a larger population.  Some hosts of this library cannot live with that:
 //   * a GA driver that shares the GPU with a framework which has already claimed the device
 //     memory for its own pool (a torch process capped with a memory fraction, a MIG / MPS
 //     slice with a fixed budget): a raw cudaMalloc from inside a plugin call can fail there,
@@ -20,8 +20,8 @@
 
 namespace {
 
-// 16 MiB.  Enough for e.g. 4,096 individuals x 40 atoms against a 5,000-atom receptor
-// (about 5 MB) or 1,024 individuals against a 20,000-atom receptor.
+// 16 MiB.  Enough for about 34,000 individuals of a 40-atom ligand on the default (fused)
+// Contacts path; with GMM_OPT_TILED, e.g. 4,096 individuals against a 5,000-atom receptor.
 constexpr size_t kStaticScratchBytes = 16u << 20;
 
 // The scratch itself.  In HOST code this name is only a handle for the symbol, not an
@@ -82,10 +82,10 @@ extern "C" int gmm_evaluate_static(gmm_ctx* c, int P, const double* torsion_deg_
     int rc = static_scratch_address(c->device, &ws);
     if (rc == GMM_OK) {
         // Layout inside the buffer is the one launch_contacts uses for the context scratch:
-        // coordinates first, then zone bitmask, then partial sums.  Every word that is read is
-        // written earlier in the same call (express writes all coordinates, the sweep writes all
-        // zone words and partial sums of the P individuals), so nothing has to be cleared even
-        // though the buffer still holds the previous call's data.
+        // coordinates first, then (tiled path only) zone bitmask and partial sums.  Every word
+        // that is read is written earlier in the same call (express writes all coordinates, the
+        // tiled sweep writes all zone words and partial sums of the P individuals), so nothing has
+        // to be cleared even though the buffer still holds the previous call's data.
         float* xyz = static_cast<float*>(ws);
         rc = gmm_express(c, P, torsion_deg_d, xform_d, rot_allele_d, xyz, stream);
         if (rc == GMM_OK)

@@ -148,9 +148,10 @@ int gmm_evaluate_host(gmm_ctx* ctx, int P, const double* torsion_deg_h, const do
 
 /* gmm_evaluate for callers that may not allocate device memory (no counterpart in the
  * reference, which runs on the CPU and has no device memory to manage).  Same inputs and
- * outputs as gmm_evaluate without out_xyz_d, but the scratch the evaluation needs
- * (coordinates, zone bitmask, partial sums) is a 16 MiB array built into the library instead
- * of the context's cudaMalloc'ed buffer: the call never calls cudaMalloc/cudaFree.
+ * outputs as gmm_evaluate without out_xyz_d, but the scratch the evaluation needs (the
+ * expressed coordinates, 12 bytes per mobile atom per individual; with GMM_OPT_TILED also a
+ * zone bitmask and partial sums) is a 16 MiB array built into the library instead of the
+ * context's cudaMalloc'ed buffer: the call never calls cudaMalloc/cudaFree.
  *   - populations whose scratch need exceeds 16 MiB are refused with GMM_ELIMIT (the message
  *     states both sizes); split them into smaller batches;
  *   - the first call on each device looks the array's device address up (one-time set-up);
