@@ -255,7 +255,11 @@ def run_b200(args):
                        "l2": "192 MiB buffer written between timed iterations",
                        "culling": "receptor tiles out of reach of a pose are skipped (results bit-identical to dense)"},
             "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": achieved, "peak": peak32,
-                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None, "traffic": None,
+                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel on this workload at
+                         # N=1, from the committed capture profiles/ncu_contacts_fused_r01j.txt (bytes/launch)
+                         "traffic": 31.76e6 if (name == "c3" and world == 1) else None,
+                         "algorithmic_bytes_per_launch": shard * (L * 12 + 16 + 8),
                          "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
                          "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
                          "kernel_ms": sweep, "express_ms": float(np.mean(expr_ms)), "finalize_ms": float(np.mean(fin_ms)),
@@ -358,7 +362,7 @@ def run_reference(args):
     pop, L, T, R = WORKLOADS[name]
     cores = os.cpu_count() or 1
     pool = CpuPool(name, cores)
-    per_step = max(cores * 8, min(args.cpu_sample, 4096) // max(1, args.steps))
+    per_step = max(cores * 16, args.cpu_sample // max(1, args.steps))
     for w in range(min(args.warmup, 1)):
         pool.run(0, per_step)
     total = 0.0
@@ -389,7 +393,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-sample", type=int, default=2048, help="individuals in the CPU baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=16384, help="individuals in the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--quick", action="store_true", help="skip the dense / configs[1] / RMSD side measurements")
     args = ap.parse_args()

@@ -46,6 +46,15 @@ int ensure_scratch(gmm_ctx* c, size_t bytes) {
     return GMM_OK;
 }
 
+int allow_dynamic_smem(const void* kernel, int device, size_t bytes) {
+    static std::vector<std::pair<const void*, int>> done;
+    for (auto& d : done)
+        if (d.first == kernel && d.second == device) return GMM_OK;
+    GMM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    done.emplace_back(kernel, device);
+    return GMM_OK;
+}
+
 static inline uint32_t spread10(uint32_t v) {
     v &= 0x3ff;
     v = (v | (v << 16)) & 0x030000ff;

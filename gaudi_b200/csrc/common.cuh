@@ -196,5 +196,7 @@ int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, 
 int launch_pairs_dump(gmm_ctx* c, const float* xyz_one, int max_pairs, int32_t* pairs_h,
                       int32_t* kind_h, double* ov_h, double* val_h, int* n_out, cudaStream_t s);
 int ensure_scratch(gmm_ctx* c, size_t bytes);
+// cudaFuncAttributeMaxDynamicSharedMemorySize, applied once per (kernel, device)
+int allow_dynamic_smem(const void* kernel, int device, size_t bytes);
 size_t contacts_scratch_bytes(const gmm_ctx* c, int P);
 }  // namespace gmm

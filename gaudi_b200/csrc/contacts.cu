@@ -509,10 +509,9 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
         const size_t smem = (size_t)kGroup * a.Mp * sizeof(float4) + kGroup * sizeof(float4) +
                             kGroup * 4 * sizeof(long long) + kSweepWarps * kPairQ * sizeof(uint2) +
                             kSweepWarps * kCandQ * sizeof(uint32_t) + (size_t)kGroup * a.MW * sizeof(uint32_t);
-        static bool attr = false;
-        if (smem > 48 * 1024 && !attr) {
-            GMM_CUDA(cudaFuncSetAttribute(contacts_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            attr = true;
+        if (smem > 48 * 1024) {
+            const int rc = allow_dynamic_smem((const void*)contacts_sweep_kernel, c->device, 200 * 1024);
+            if (rc) return rc;
         }
         dim3 grid(a.n_chunks, (P + kGroup - 1) / kGroup);
         if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
@@ -526,10 +525,9 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
     f.rr_val = c->d_rr_val; f.rr_kind = c->d_rr_kind;
     f.scores = scores; f.counts = counts; f.have_sweep = have_sweep;
     const size_t fsmem = (size_t)kFinWarps * a.Mp * sizeof(float4) + (size_t)kFinWarps * a.MW * sizeof(uint32_t);
-    static bool fattr = false;
-    if (fsmem > 48 * 1024 && !fattr) {
-        GMM_CUDA(cudaFuncSetAttribute(contacts_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        fattr = true;
+    if (fsmem > 48 * 1024) {
+        const int rc = allow_dynamic_smem((const void*)contacts_finalize_kernel, c->device, 200 * 1024);
+        if (rc) return rc;
     }
     if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[4], s));
     contacts_finalize_kernel<<<(P + kFinWarps - 1) / kFinWarps, kFinWarps * 32, fsmem, s>>>(f);

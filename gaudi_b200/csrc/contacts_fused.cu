@@ -109,8 +109,8 @@ contacts_fused_kernel(const FusedArgs f) {
     float4* misc = ligc + a.Mp;                                   // [0] sphere, [1] box lo, [2] box hi
     long long* accs = reinterpret_cast<long long*>(misc + 3);     // [4]
     int* nlist_p = reinterpret_cast<int*>(accs + 4);              // [4] (16 bytes)
-    uint32_t* list = reinterpret_cast<uint32_t*>(nlist_p + 4);    // [NST + 4], 16-byte aligned
-    uint32_t* zone = list + (f.NST + 4);                          // [NST + 1]
+    uint16_t* list = reinterpret_cast<uint16_t*>(nlist_p + 4);    // [NST + 4] leaf ids, 16-byte aligned
+    uint32_t* zone = reinterpret_cast<uint32_t*>(list + (f.NST + 4));   // [NST + 1] (NST is a multiple of 4)
     uint32_t* zm = zone + (f.NST + 1);                            // [MW]
     uint32_t* cq = reinterpret_cast<uint32_t*>(smem_raw + (size_t)IPC * f.ind_bytes) + warp * (kCandQ + kPairQ);
     uint32_t* pq = cq + kCandQ;
@@ -220,7 +220,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 if (lane == 0 && mask) b0 = atomicAdd(nlist_p, __popc(mask));
                 pos = __shfl_sync(0xffffffffu, b0, 0);
             }
-            if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint32_t)st;
+            if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)st;
         }
         if (S == 1 && a.cull) {
             // Refine: a leaf stays only if some mobile atom is within reach of its box (the
@@ -252,7 +252,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 }
                 const unsigned mask = __ballot_sync(0xffffffffu, keep);
                 __syncwarp();
-                if (keep) list[nout + __popc(mask & ((1u << lane) - 1u))] = st;
+                if (keep) list[nout + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)st;
                 nout += __popc(mask);
                 __syncwarp();
             }
@@ -262,14 +262,14 @@ contacts_fused_kernel(const FusedArgs f) {
         team_sync<S>();
         const int nlist = nlist_p[0];
         const int ngroups = (nlist + 3) >> 2;
-        if (tlane < 4 && nlist + tlane < ngroups * 4) list[nlist + tlane] = (uint32_t)f.NST;   // dummy far leaf
+        if (tlane < 4 && nlist + tlane < ngroups * 4) list[nlist + tlane] = (uint16_t)f.NST;   // dummy far leaf
         team_sync<S>();
 
         // ---- 2. sweep -----------------------------------------------------------------------
         int ncq = 0, npq = 0;
         for (int gi = wt; gi < ngroups; gi += S) {
-            const uint4 st4 = *reinterpret_cast<const uint4*>(list + 4 * gi);
-            const uint32_t stv[4] = {st4.x, st4.y, st4.z, st4.w};
+            const uint2 st4 = *reinterpret_cast<const uint2*>(list + 4 * gi);
+            const uint32_t stv[4] = {st4.x & 0xffffu, st4.x >> 16, st4.y & 0xffffu, st4.y >> 16};
             float ax[4], ay[4], az[4], nr[4], rw[4], ms[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -422,7 +422,7 @@ void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a);
 static size_t fused_ind_bytes(const gmm_ctx* c) {
     const int NST = c->Rpad / kSubTile, MW = (c->Mp + 31) / 32;
     size_t ind = (size_t)2 * c->Mp * sizeof(float4) + 3 * sizeof(float4) + 4 * sizeof(long long) + 4 * sizeof(int) +
-                 (size_t)(NST + 4) * 4 + (size_t)(NST + 1) * 4 + (size_t)MW * 4;
+                 (size_t)(NST + 4) * 2 + (size_t)(NST + 1) * 4 + (size_t)MW * 4;
     return (ind + 15) / 16 * 16;
 }
 static const size_t kFusedQueues = (size_t)4 * (kCandQ + kPairQ) * sizeof(uint32_t);
@@ -431,6 +431,7 @@ static const size_t kFusedSmemLimit = 200 * 1024;
 // True when gmm_contacts / gmm_evaluate will run the one-kernel path for this context.
 bool fused_applicable(const gmm_ctx* c) {
     if (c->prm.options & GMM_OPT_TILED) return false;
+    if (c->Rpad / kSubTile >= 65535) return false;      // leaf ids are 16-bit in shared memory
     return fused_ind_bytes(c) + kFusedQueues <= kFusedSmemLimit;
 }
 
@@ -439,6 +440,7 @@ bool fused_applicable(const gmm_ctx* c) {
 int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
                           int* handled) {
     *handled = 0;
+    if (!fused_applicable(c)) return GMM_OK;
     FusedArgs f;
     fill_sweep_args(c, P, xyz, f.s);
     f.NST = c->Rpad / kSubTile; f.R = c->R;
@@ -455,13 +457,12 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     if (ind + queues > limit) return GMM_OK;    // not handled
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
     GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));
-    static bool attr1 = false, attr4 = false;
     if (S == 1) {
-        if (!attr1) { GMM_CUDA(cudaFuncSetAttribute(contacts_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit)); attr1 = true; }
+        { const int rc = allow_dynamic_smem((const void*)contacts_fused_kernel<1>, c->device, limit); if (rc) return rc; }
         if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
         contacts_fused_kernel<1><<<(P + 3) / 4, 128, smem, s>>>(f);
     } else {
-        if (!attr4) { GMM_CUDA(cudaFuncSetAttribute(contacts_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit)); attr4 = true; }
+        { const int rc = allow_dynamic_smem((const void*)contacts_fused_kernel<4>, c->device, limit); if (rc) return rc; }
         if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
         contacts_fused_kernel<4><<<P, 128, smem, s>>>(f);
     }

@@ -137,11 +137,9 @@ int launch_express(gmm_ctx* c, int P, const double* tors, const double* xform, c
     a.tors = tors; a.xform = xform; a.rot = rot; a.out = out_xyz;
     a.cx = c->centre[0]; a.cy = c->centre[1]; a.cz = c->centre[2];
     const size_t smem = (size_t)kExprWarps * 3 * a.Mp * sizeof(double);
-    static bool attr_set = false;
-    if (smem > 48 * 1024 && !attr_set) {
-        GMM_CUDA(cudaFuncSetAttribute(express_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      200 * 1024));
-        attr_set = true;
+    if (smem > 48 * 1024) {
+        const int rc = allow_dynamic_smem((const void*)express_kernel, c->device, 200 * 1024);
+        if (rc) return rc;
     }
     int blocks = (P + kExprWarps - 1) / kExprWarps;
     const int cap = 148 * 16;

@@ -150,13 +150,9 @@ rmsd_tile_kernel(const RmsdArgs a) {
 }
 
 template <int RK>
-static int launch_rmsd_rk(const RmsdArgs& a, dim3 grid, cudaStream_t s) {
+static int launch_rmsd_rk(const RmsdArgs& a, dim3 grid, cudaStream_t s, int device) {
     const size_t smem = (size_t)4 * RK * kRS * sizeof(float);
-    static bool attr = false;
-    if (!attr) {
-        GMM_CUDA(cudaFuncSetAttribute(rmsd_tile_kernel<RK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
-    }
+    { const int rc = allow_dynamic_smem((const void*)rmsd_tile_kernel<RK>, device, smem); if (rc) return rc; }
     rmsd_tile_kernel<RK><<<grid, 256, smem, s>>>(a);
     GMM_LAUNCH_CHECK("rmsd_tile_kernel");
     return GMM_OK;
@@ -164,7 +160,6 @@ static int launch_rmsd_rk(const RmsdArgs& a, dim3 grid, cudaStream_t s) {
 
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s) {
-    (void)c;
     if (row1 <= row0 || N == 0) return GMM_OK;
     RmsdArgs a;
     a.N = N; a.A = A; a.K = 3 * A; a.row0 = row0; a.row1 = row1;
@@ -173,8 +168,8 @@ int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, 
     a.sym = (out_rmsd == nullptr && out_bits != nullptr && row0 % kRT == 0) ? 1 : 0;
     a.R0 = row0 / kRT; a.R1 = (row1 + kRT - 1) / kRT;
     dim3 grid((N + kRT - 1) / kRT, (row1 - row0 + kRT - 1) / kRT);
-    if (a.K % 36 == 0) return launch_rmsd_rk<36>(a, grid, s);
-    return launch_rmsd_rk<32>(a, grid, s);
+    if (a.K % 36 == 0) return launch_rmsd_rk<36>(a, grid, s, c->device);
+    return launch_rmsd_rk<32>(a, grid, s, c->device);
 }
 
 }  // namespace gmm
