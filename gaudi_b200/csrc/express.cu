@@ -26,7 +26,7 @@ struct ExpressArgs {
     float* out; double cx, cy, cz;
 };
 
-__global__ void __launch_bounds__(kExprWarps * 32)
+__global__ void __launch_bounds__(kExprWarps * 32, 8)
 express_kernel(const ExpressArgs a) {
     extern __shared__ double sm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -68,21 +68,21 @@ express_kernel(const ExpressArgs a) {
                     const int f = a.tfixed[t], m = a.tmoving[t];
                     const double bx = sx[m], by = sy[m], bz = sz[m];
                     double ux = bx - sx[f], uy = by - sy[f], uz = bz - sz[f];
-                    const double inv = 1.0 / sqrt(ux * ux + uy * uy + uz * uz);
+                    const double inv = rsqrt(ux * ux + uy * uy + uz * uz);
                     ux *= inv; uy *= inv; uz *= inv;
+                    // Rodrigues matrix R = c I + s [u]x + (1 - c) u u^T, built once per bond
                     const double omc = 1.0 - c;
+                    const double r00 = c + omc * ux * ux, r01 = omc * ux * uy - s * uz, r02 = omc * ux * uz + s * uy;
+                    const double r10 = omc * ux * uy + s * uz, r11 = c + omc * uy * uy, r12 = omc * uy * uz - s * ux;
+                    const double r20 = omc * ux * uz - s * uy, r21 = omc * uy * uz + s * ux, r22 = c + omc * uz * uz;
                     __syncwarp();
                     const uint64_t* mask = a.tmask + (size_t)t * a.W;
                     for (int i = lane; i < a.M; i += 32) {
                         if ((mask[i >> 6] >> (i & 63)) & 1ull) {
                             const double vx = sx[i] - bx, vy = sy[i] - by, vz = sz[i] - bz;
-                            const double crx = uy * vz - uz * vy;
-                            const double cry = uz * vx - ux * vz;
-                            const double crz = ux * vy - uy * vx;
-                            const double dot = ux * vx + uy * vy + uz * vz;
-                            sx[i] = bx + vx * c + crx * s + ux * dot * omc;
-                            sy[i] = by + vy * c + cry * s + uy * dot * omc;
-                            sz[i] = bz + vz * c + crz * s + uz * dot * omc;
+                            sx[i] = bx + (r00 * vx + r01 * vy + r02 * vz);
+                            sy[i] = by + (r10 * vx + r11 * vy + r12 * vz);
+                            sz[i] = bz + (r20 * vx + r21 * vy + r22 * vz);
                         }
                     }
                 }
