@@ -297,6 +297,17 @@ contacts_fused_kernel(const FusedArgs f) {
                 for (int k = 0; k < 4; ++k)
                     ms[k] = fminf(ms[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
             }
+            // Far group (the common case without culling): no atom of these four leaves is within
+            // radius + margin of a seed and none is always-in-zone -> their zone words stay as
+            // initialised and there is nothing to expand.
+            {
+                bool near = false;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    near = near || (ms[k] + nr[k] <= a.rad2 + 2e-4f + 1e-6f * (nr[k] + wmax));
+                if (a.n_sseed > 0) near = near || ((zone[stv[0]] | zone[stv[1]] | zone[stv[2]] | zone[stv[3]]) != 0u);
+                if (!__any_sync(0xffffffffu, near)) continue;
+            }
             float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
             for (s = a.n_seed; s < a.M; ++s) {
                 const float4 m = ligc[s];
