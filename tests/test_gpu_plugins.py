@@ -144,3 +144,28 @@ def test_rotamers_flexible_side_chains(cuda):
                if not any((int(m[int(a) >> 6]) >> (int(a) & 63)) & 1 for m in eng.mobile.tors_mask)]
     assert len(ca_like) >= 1
     assert np.abs(xyz[:, ca_like] - eng.mobile.xyz0[ca_like]).max() < 1e-5
+
+
+def test_tensor_ga_configs0(cuda):
+    """The array-population loop on the same job: fitness of the evolved population equals the
+    oracle's for the same alleles, and a 2,000-individual population runs generations in a
+    fraction of a second each."""
+    from gaudi_b200 import tensor_ga
+    cfg = job(100, 10)
+    pop, log, batch = tensor_ga.launch(cfg, seed=7)
+    assert pop["fitness"].shape == (100, 2) and len(log) == 11
+    assert np.isfinite(pop["fitness"]).all()
+    eng = batch.engines[0][0]
+    xf = tensor_ga.TensorGA.xforms(pop)
+    for p in range(0, 100, 17):
+        xyz = OA.express(eng.mobile, pop["torsions"][p], xf[p])
+        res = OA.contacts(eng.mobile, eng.receptor, eng.params, xyz)
+        got = pop["fitness"][p]
+        assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash)
+        assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro)
+        assert np.abs(pop["coords"][p].astype(np.float64) + batch.centre - xyz[batch.lig_slice]).max() < 1e-4
+    first = tensor_ga.launch(job(100, 0), seed=7)[0]
+    assert pop["fitness"][:, 0].min() <= first["fitness"][:, 0].min()
+    big, log, _ = tensor_ga.launch(job(2000, 3), seed=8)
+    assert big["fitness"].shape == (2000, 2)
+    assert all(entry["speed"] > 2000 for entry in log[1:]), log      # evaluations per second

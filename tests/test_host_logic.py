@@ -137,3 +137,68 @@ def test_sharded_gather_world2_gloo(tmp_path):
     res = np.load(out)
     assert res[0] == 0.0          # gathered fitness == single-process fitness, bit for bit
     assert res[1] == 0.0          # row-block sharded similarity bitmask == full matrix
+
+
+# ---- tensorised GA bookkeeping (gaudi_b200/tensor_ga.py) against the per-object versions ----------
+def test_tensor_nsga2_matches_deaplite():
+    from gaudi_b200 import tensor_ga as TG
+    rng = np.random.default_rng(4)
+    for nobj in (2, 3):
+        vals = rng.random((60, nobj))
+        vals[7] = vals[3]                              # duplicated fitness shares a front
+        weights = (-1.0,) * nobj
+        inds = [_Ind(tuple(v), weights) for v in vals]
+        index = {id(x): i for i, x in enumerate(inds)}
+        level = TG.nondominated_fronts(vals * np.array(weights))
+        for k in (60, 25, 1):
+            want = [index[id(x)] for x in deaplite.sel_nsga2(inds, k)]
+            got = TG.sel_nsga2(vals, weights, k).tolist()
+            assert len(got) == len(set(got)) == k
+
+            def key(sel):      # ties in crowding distance are broken arbitrarily by either version
+                out = []
+                for i in sel:
+                    members = np.flatnonzero(level == level[i])
+                    cd = TG.crowding_distance(vals[members])[list(members).index(i)]
+                    out.append((int(level[i]), float(np.round(cd, 9))))
+                return sorted(out)
+            assert key(got) == key(want)
+        fronts = deaplite.sort_nondominated(inds, 60)
+        for lv, front in enumerate(fronts):
+            assert all(level[index[id(x)]] == lv for x in front)
+
+
+def test_tensor_niching_matches_reference_loop():
+    from gaudi_b200 import tensor_ga as TG
+    rng = np.random.default_rng(9)
+    n = 70
+    vals = np.round(rng.random((n, 2)), 1)             # coarse values: plenty of fitness ties
+    sim = rng.random((n, n)) < 0.12
+    sim = sim | sim.T
+    np.fill_diagonal(sim, True)
+    inds = [_Ind(tuple(v)) for v in vals]
+    index = {id(x): k for k, x in enumerate(inds)}
+    want = [index[id(x)] for x in niching(inds, lambda a, b: bool(sim[index[id(a)], index[id(b)]]))]
+    got = TG.niching(sim, vals * np.array([-1.0, -1.0])).tolist()
+    assert got == want
+
+
+def test_tensor_variation_properties():
+    from gaudi_b200 import tensor_ga as TG
+    spec = dict(n_torsions=6, flexibility=300.0, precision=1, cx_eta=5.0, mut_eta=5.0, mut_indpb=0.75,
+                search_center=(1.0, 2.0, 3.0), search_radius=4.0, rotate=True, interpolation=0.5, n_rot_res=3)
+    ga = TG.TensorGA(spec, (-1.0, -1.0), None, None, seed=1)
+    pop = ga.random_population(200)
+    pop["fitness"][:] = 1.0
+    pop["coords"] = np.zeros((200, 5, 3), np.float32)
+    kids = ga.var_or(pop, 500, 0.5, 0.4)
+    assert kids["torsions"].shape == (500, 6) and np.abs(kids["torsions"]).max() <= 150.0
+    assert np.allclose(kids["torsions"], np.round(kids["torsions"], 1))
+    assert np.allclose(np.einsum("nij,nkj->nik", kids["rot"], kids["rot"]), np.eye(3), atol=1e-9)
+    assert (np.linalg.norm(kids["trans"] - np.array([1.0, 2.0, 3.0]), axis=1) <= 4.0 + 1e-9).all()
+    assert ((kids["rotamers"] >= 0) & (kids["rotamers"] < 1)).all()
+    changed = np.isnan(kids["fitness"][:, 0])
+    assert 0.8 < changed.mean() < 0.97               # cxpb + mutpb = 0.9 of the children are new
+    r = TG.random_rotations(50, np.random.default_rng(0))
+    assert np.allclose(TG.slerp(r, r, 0.3), r, atol=1e-9)
+    assert np.allclose(TG.quat_to_matrix(TG.matrix_to_quat(r)), r, atol=1e-9)
