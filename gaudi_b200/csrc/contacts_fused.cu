@@ -129,22 +129,20 @@ contacts_fused_kernel(const FusedArgs f) {
     if (tlane == 0) nlist_p[0] = 0;
     team_sync<S>();
     const bool internal = a.prm.options & GMM_OPT_ONLY_INTERNAL;
-    for (int w = tlane; w < a.MW; w += TL) {          // mobile atoms in the zone
-        uint32_t bits = 0;
-        for (int b = 0; b < 32; ++b) {
-            const int s = w * 32 + b;
-            if (s >= a.M) break;
-            bool in = s < a.n_seed;
-            if (!in && !internal) {
-                const float4 q = ligx[s];
-                for (int k = 0; k < a.n_seed && !in; ++k)
-                    in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
-                for (int k = 0; k < a.n_sseed && !in; ++k)
-                    in = dist2f(a.sseed[k].x, a.sseed[k].y, a.sseed[k].z, q.x, q.y, q.z) <= a.rad2;
-            }
-            if (in) bits |= 1u << b;
+    // mobile atoms in the zone: seeds always, the others (flexible side chains) iff within radius
+    // of a seed; one atom per lane, 32 atoms = one word per ballot
+    for (int base = wt * 32; base < a.MW * 32; base += TL) {
+        const int s = base + lane;
+        bool in = s < a.n_seed;
+        if (!in && s < a.M && !internal) {
+            const float4 q = ligx[s];
+            for (int k = 0; k < a.n_seed && !in; ++k)
+                in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
+            for (int k = 0; k < a.n_sseed && !in; ++k)
+                in = dist2f(a.sseed[k].x, a.sseed[k].y, a.sseed[k].z, q.x, q.y, q.z) <= a.rad2;
         }
-        zm[w] = bits;
+        const unsigned bits = __ballot_sync(0xffffffffu, in && s < a.M);
+        if (lane == 0) zm[base >> 5] = bits;
     }
     if (wt == 0) {                                     // bounding box and sphere of the pose
         float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
