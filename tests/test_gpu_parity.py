@@ -240,3 +240,56 @@ def test_rmsd_matrix(small_system, torch_cuda):
     o, _ = eng.rmsd_matrix(big, threshold=2.5, bits=False)
     assert torch_cuda.equal(o, o.T.contiguous())
     assert float(o.diagonal().abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("n_lig, n_tors, n_rec, pop", [
+    (1, 0, 7, 3),          # a single mobile atom, receptor smaller than one leaf
+    (5, 0, 33, 5),         # just over one leaf
+    (40, 10, 129, 1185),   # just over one 128-atom tile; population just over the warp/CTA switch
+    (70, 12, 1000, 9),     # mobile set larger than two lane-rounds
+])
+def test_ragged_sizes(torch_cuda, n_lig, n_tors, n_rec, pop):
+    """Sizes that do not line up with any tile, leaf, warp or team: fused == tiled bit for bit,
+    and both equal the oracle."""
+    from gaudi_b200.engine import Engine
+    params = M.ContactParams()
+    if n_lig >= 12:
+        lig = synth.make_ligand(n_lig, n_tors, seed=3)
+    else:
+        xyz0 = np.array([[0.0, 0.0, 0.0], [1.5, 0.0, 0.0], [2.2, 1.3, 0.0], [3.7, 1.3, 0.2], [4.4, 2.6, 0.1]])[:n_lig]
+        bonds = [(i, i + 1) for i in range(n_lig - 1)]
+        flags = np.full(n_lig, M.F_HYDROPHOBIC | M.F_SEED | M.F_XFORM, np.uint8)
+        lig = M.build_mobile(xyz0, np.full(n_lig, 1.7), flags, bonds, [], origin_atom=0)
+    rec = synth.make_receptor(n_rec, seed=4, cavity=2.0, params=params)
+    tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=5, radius=3.0)
+    eng = Engine(lig, rec, params, device=0)
+    s1, c1, x1 = eng.evaluate(tors, xf, want_xyz=True)
+    tiled = Engine(lig, rec, M.ContactParams(tiled=True), device=0)
+    s2, c2 = tiled.contacts(x1)
+    assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
+    s1 = s1.cpu().numpy(); x = x1.cpu().numpy().astype(np.float64) + eng.centre
+    for p in range(0, pop, max(1, pop // 6)):
+        res = OA.contacts(lig, rec, params, x[p])
+        assert score_close(s1[p, 0], res.clash, res.clash_slack), (p, s1[p], res.clash)
+        assert score_close(s1[p, 1], res.hydro, res.hydro_slack), (p, s1[p], res.hydro)
+    eng.close(); tiled.close()
+
+
+def test_zone_radius_zero_and_huge(small_system, torch_cuda):
+    """radius = 0: the zone is the probe itself (contacts.py:199-213 with an empty
+    neighbourhood); radius = 30: the zone is everything."""
+    from gaudi_b200.engine import Engine
+    lig, rec, _, _ = small_system
+    tors, xf = synth.make_alleles(12, lig.n_allele_torsions, seed=23)
+    for radius in (0.0, 30.0):
+        params = M.ContactParams(radius=radius)
+        rec2 = M.build_receptor(rec.xyz[:1500], rec.radius[:1500], rec.flags[:1500],
+                                rec.bonds[(rec.bonds < 1500).all(axis=1)], params, centre=rec.centre)
+        eng = Engine(lig, rec2, params, device=0)
+        s, c, x = eng.evaluate(tors, xf, want_xyz=True)
+        s = s.cpu().numpy(); x = x.cpu().numpy().astype(np.float64) + eng.centre
+        for p in range(0, 12, 3):
+            res = OA.contacts(lig, rec2, params, x[p])
+            assert score_close(s[p, 0], res.clash, res.clash_slack), (radius, p, s[p], res.clash)
+            assert score_close(s[p, 1], res.hydro, res.hydro_slack), (radius, p, s[p], res.hydro)
+        eng.close()
