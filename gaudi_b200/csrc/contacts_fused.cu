@@ -35,6 +35,7 @@ struct FusedArgs {
     const uint32_t* mm_pairs; int n_mm;
     double* scores; int32_t* counts;
     int ind_bytes;
+    int tma_pose;     // 1: stage each pose with one TMA bulk copy (size and alignment permit)
 };
 
 struct Acc { long long cfx, hfx; int nc, nh; };
@@ -116,14 +117,51 @@ contacts_fused_kernel(const FusedArgs f) {
     uint32_t* pq = cq + kCandQ;
 
     // ---- 0. stage the pose --------------------------------------------------------------
-    for (int s = tlane; s < a.Mp; s += TL) {
-        const int atom = a.slot2atom[s];
-        float4 v = make_float4(kFar, kFar, kFar, 0.f);
-        if (atom >= 0) {
-            const float* src = a.xyz + ((size_t)p * a.M + atom) * 3;
-            v = make_float4(src[0], src[1], src[2], a.mrad[s]);
+    // The pose's M x 3 floats are one contiguous, 16-byte aligned block in HBM: a single TMA
+    // bulk copy (cp.async.bulk, SASS UBLKCP) lands it in this team's queue area (unused until the
+    // sweep), completion signalled on an mbarrier; lanes then permute it into slot order.  Poses
+    // whose byte count is not a multiple of 16 or that do not fit the landing area are read with
+    // plain loads instead (f.tma_pose == 0, decided per launch).
+    if (f.tma_pose) {
+        const float* raw = reinterpret_cast<const float*>(smem_raw + (size_t)IPC * f.ind_bytes) +
+                           (size_t)(warp - wt) * (kCandQ + kPairQ);
+        unsigned long long* mbar = reinterpret_cast<unsigned long long*>(nlist_p + 2);
+        const unsigned mbar_s = (unsigned)__cvta_generic_to_shared(mbar);
+        const unsigned bytes = (unsigned)(a.M * 3 * sizeof(float));
+        if (tlane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_s));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
-        ligx[s] = v;
+        team_sync<S>();
+        if (tlane == 0) {
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_s), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(raw)), "l"(a.xyz + (size_t)p * a.M * 3),
+                           "r"(bytes), "r"(mbar_s) : "memory");
+        }
+        unsigned done = 0;
+        for (int spin = 0; !done; ++spin) {
+            asm volatile("{\n\t.reg .pred q;\n\t"
+                         "mbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0;\n\t"
+                         "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(done) : "r"(mbar_s) : "memory");
+            if (spin > (1 << 24)) __trap();          // never hang the GPU on a lost copy
+        }
+        for (int s = tlane; s < a.Mp; s += TL) {
+            const int atom = a.slot2atom[s];
+            float4 v = make_float4(kFar, kFar, kFar, 0.f);
+            if (atom >= 0) v = make_float4(raw[3 * atom], raw[3 * atom + 1], raw[3 * atom + 2], a.mrad[s]);
+            ligx[s] = v;
+        }
+    } else {
+        for (int s = tlane; s < a.Mp; s += TL) {
+            const int atom = a.slot2atom[s];
+            float4 v = make_float4(kFar, kFar, kFar, 0.f);
+            if (atom >= 0) {
+                const float* src = a.xyz + ((size_t)p * a.M + atom) * 3;
+                v = make_float4(src[0], src[1], src[2], a.mrad[s]);
+            }
+            ligx[s] = v;
+        }
     }
     if (tlane < 4) accs[tlane] = 0;
     if (tlane == 0) nlist_p[0] = 0;
@@ -459,6 +497,9 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.scores = scores; f.counts = counts;
     const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
+    const size_t pose_bytes = (size_t)c->M * 3 * sizeof(float);
+    f.tma_pose = (pose_bytes % 16 == 0 && pose_bytes <= (kCandQ + kPairQ) * sizeof(uint32_t) &&
+                  (reinterpret_cast<uintptr_t>(xyz) % 16) == 0) ? 1 : 0;
     const size_t queues = kFusedQueues;
     const size_t limit = kFusedSmemLimit;
     int S = (P >= 148 * 8) ? 1 : 4;
