@@ -219,7 +219,7 @@ contacts_fused_kernel(const FusedArgs f) {
     for (int st = tlane; st <= f.NST; st += TL) zone[st] = a.always[st];
 
     Acc acc; acc.cfx = 0; acc.hfx = 0; acc.nc = 0; acc.nh = 0;
-    unsigned long long tests = 0;
+    int swept_leaves = 0;
     const bool have_sweep = !internal && f.R > 0;
 
     if (have_sweep) {
@@ -303,6 +303,7 @@ contacts_fused_kernel(const FusedArgs f) {
 
         // ---- 2. sweep -----------------------------------------------------------------------
         int ncq = 0, npq = 0;
+        const float near_c = a.rad2 + 2e-4f + 1e-6f * wmax, near_m = 1e-6f - 1.f;
         for (int gi = wt; gi < ngroups; gi += S) {
             const uint2 st4 = *reinterpret_cast<const uint2*>(list + 4 * gi);
             const uint32_t stv[4] = {st4.x & 0xffffu, st4.x >> 16, st4.y & 0xffffu, st4.y >> 16};
@@ -315,11 +316,11 @@ contacts_fused_kernel(const FusedArgs f) {
                 nr[k] = fmaf(z, z, fmaf(y, y, x * x));
                 rw[k] = r.w;
                 ms[k] = 3e38f;
-                tests += (stv[k] < (uint32_t)f.NST) ? (unsigned long long)kSubTile * a.M : 0ull;
+                swept_leaves += (stv[k] < (uint32_t)f.NST) ? 1 : 0;
             }
             // two mobile atoms per step: 6 FFMA + one 3-input FMNMX3 per receptor atom
             int s = 0;
-#pragma unroll 2
+#pragma unroll 4
             for (; s + 1 < a.n_seed; s += 2) {
                 const float4 m = ligc[s], q = ligc[s + 1];
 #pragma unroll
@@ -337,10 +338,10 @@ contacts_fused_kernel(const FusedArgs f) {
             // radius + margin of a seed and none is always-in-zone -> their zone words stay as
             // initialised and there is nothing to expand.
             {
+                // ms + nr <= rad2 + margin(nr)  <=>  ms <= near_c - near_m * nr
                 bool near = false;
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    near = near || (ms[k] + nr[k] <= a.rad2 + 2e-4f + 1e-6f * (nr[k] + wmax));
+                for (int k = 0; k < 4; ++k) near = near || (ms[k] <= fmaf(near_m, nr[k], near_c));
                 if (a.n_sseed > 0) near = near || ((zone[stv[0]] | zone[stv[1]] | zone[stv[2]] | zone[stv[3]]) != 0u);
                 if (!__any_sync(0xffffffffu, near)) continue;
             }
@@ -452,7 +453,7 @@ contacts_fused_kernel(const FusedArgs f) {
         team_sync<S>();
         cfx = accs[0]; hfx = accs[1]; nc = accs[2]; nh = accs[3];
     }
-    if (lane == 0 && tests) atomicAdd(a.counters, tests);
+    if (lane == 0 && swept_leaves) atomicAdd(a.counters, (unsigned long long)swept_leaves * kSubTile * a.M);
     if (tlane == 0) {
         if (f.n_mm) atomicAdd(a.counters, (unsigned long long)f.n_mm);
         double clash = 2.0 * ((double)cfx / kFxScale);          // contacts.py:176-177
