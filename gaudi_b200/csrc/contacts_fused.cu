@@ -346,7 +346,14 @@ contacts_fused_kernel(const FusedArgs f) {
                 if (!__any_sync(0xffffffffu, near)) continue;
             }
             float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
-            for (s = a.n_seed; s < a.M; ++s) {
+            for (s = a.n_seed; s + 1 < a.M; s += 2) {      // mobile atoms that are not zone seeds
+                const float4 m = ligc[s], q = ligc[s + 1];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    ma[k] = fminf(ma[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
+                                               fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
+            }
+            if (s < a.M) {
                 const float4 m = ligc[s];
 #pragma unroll
                 for (int k = 0; k < 4; ++k)

@@ -14,6 +14,16 @@ from gaudi_b200.engine import Engine
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "culled"
 pop = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
+if mode == "rotamers":          # BASELINE configs[4] through bench.py's builder
+    import bench
+
+    def timed(fn, reps):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        return 1.0
+    print(bench.rotamers_measurement(torch, torch.device("cuda", 0), timed))
+    sys.exit(0)
 params = M.ContactParams(cull=(mode != "dense"), tiled=(mode == "tiled"))
 lig = synth.make_ligand(40, 10, seed=1)
 rec = synth.make_receptor(20000, seed=2, params=params)
