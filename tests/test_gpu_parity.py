@@ -293,3 +293,52 @@ def test_zone_radius_zero_and_huge(small_system, torch_cuda):
             assert score_close(s[p, 0], res.clash, res.clash_slack), (radius, p, s[p], res.clash)
             assert score_close(s[p, 1], res.hydro, res.hydro_slack), (radius, p, s[p], res.hydro)
         eng.close()
+
+
+def test_full_size_baseline_config(torch_cuda):
+    """BASELINE.json configs[2] at full size (65,536 poses x 20,000-atom receptor): culled ==
+    dense bit for bit over the whole population, a sample of it equals the oracle, and the
+    population evaluated in 8 shards (what 8 GPUs do) gives the same rows."""
+    from gaudi_b200.engine import Engine
+    params = M.ContactParams()
+    lig = synth.make_ligand(40, 10, seed=1)
+    rec = synth.make_receptor(20000, seed=2, params=params)
+    tors, xf = synth.make_alleles(65536, 10, seed=3)
+    eng = Engine(lig, rec, params, device=0)
+    dense = Engine(lig, rec, M.ContactParams(cull=False), device=0)
+    s1, c1, x1 = eng.evaluate(tors, xf, want_xyz=True)
+    s2, c2 = dense.contacts(x1)
+    assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
+    assert eng.last_pair_tests() * 10 < dense.last_pair_tests()
+    parts = [eng.evaluate(tors[k * 8192:(k + 1) * 8192], xf[k * 8192:(k + 1) * 8192])[0] for k in range(8)]
+    assert torch_cuda.equal(torch_cuda.cat(parts), s1)
+    s = s1.cpu().numpy(); x = x1.cpu().numpy().astype(np.float64) + eng.centre
+    for p in range(0, 65536, 2731):                      # 24 individuals spread over the population
+        assert np.abs(OA.express(lig, tors[p], xf[p]) - x[p]).max() < XYZ_TOL
+        res = OA.contacts(lig, rec, params, x[p])
+        assert score_close(s[p, 0], res.clash, res.clash_slack), (p, s[p], res.clash)
+        assert score_close(s[p, 1], res.hydro, res.hydro_slack), (p, s[p], res.hydro)
+    assert np.isfinite(s).all()
+
+
+def test_api_errors_and_reserve(small_system, torch_cuda):
+    import ctypes as C
+    from gaudi_b200 import _lib
+    lig, rec, params, eng = small_system
+    L = _lib.lib()
+    eng.reserve(10000)
+    tors, xf = synth.make_alleles(16, lig.n_allele_torsions, seed=1)
+    # a model with torsions needs the torsion alleles
+    with pytest.raises(_lib.GmmError) as e:
+        eng.express(None, xf)
+    assert e.value.code == _lib.GMM_EINVAL
+    # parameters cannot change once the receptor's static pair values exist
+    assert L.gmm_set_params(eng._h, 5.0, 0.6, -0.4, 0.2, 2.1, 0.0, 1.0, 0) == _lib.GMM_ESTATE
+    # a fresh context refuses to score before it has a model
+    h = C.c_void_p()
+    assert L.gmm_create(C.byref(h), 0) == 0
+    out = torch_cuda.zeros((1, 2), dtype=torch_cuda.float64, device="cuda")
+    x = torch_cuda.zeros((1, 3), dtype=torch_cuda.float32, device="cuda")
+    assert L.gmm_contacts(h, 1, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), None, None) == _lib.GMM_ESTATE
+    assert L.gmm_create(C.byref(C.c_void_p()), 9999) == _lib.GMM_EINVAL
+    assert L.gmm_destroy(h) == 0
