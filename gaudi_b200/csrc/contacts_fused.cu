@@ -23,6 +23,8 @@
 //   4  intra    pairs inside the mobile set (exclusions pre-removed);
 //   5  finish   fixed-point sums -> doubles, x2 (contacts.py:176-177), cutoff penalty
 //               (contacts.py:132-133).
+#include <cstdlib>
+
 #include "contacts_common.cuh"
 
 namespace gmm {
@@ -510,7 +512,9 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
                   (reinterpret_cast<uintptr_t>(xyz) % 16) == 0) ? 1 : 0;
     const size_t queues = kFusedQueues;
     const size_t limit = kFusedSmemLimit;
-    int S = (P >= 148 * 8) ? 1 : 4;
+    // warp-per-individual from this population on; below it a CTA per individual fills the GPU better
+    static const int team_switch = getenv("GMM_TEAM_SWITCH") ? atoi(getenv("GMM_TEAM_SWITCH")) : 148 * 18;
+    int S = (P >= team_switch) ? 1 : 4;
     if (S == 1 && 4 * ind + queues > limit) S = 4;
     if (ind + queues > limit) return GMM_OK;    // not handled
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;

@@ -245,7 +245,7 @@ def test_rmsd_matrix(small_system, torch_cuda):
 @pytest.mark.parametrize("n_lig, n_tors, n_rec, pop", [
     (1, 0, 7, 3),          # a single mobile atom, receptor smaller than one leaf
     (5, 0, 33, 5),         # just over one leaf
-    (40, 10, 129, 1185),   # just over one 128-atom tile; population just over the warp/CTA switch
+    (40, 10, 129, 2665),   # just over one 128-atom tile; population just over the warp/CTA switch
     (70, 12, 1000, 9),     # mobile set larger than two lane-rounds
 ])
 def test_ragged_sizes(torch_cuda, n_lig, n_tors, n_rec, pop):
