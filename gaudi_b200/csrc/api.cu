@@ -123,6 +123,8 @@ int gmm_destroy(gmm_ctx* c) {
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
+    for (int k = 0; k < 5; ++k) if (c->ev_copy[k]) cudaEventDestroy(c->ev_copy[k]);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     delete c;
     return GMM_OK;
 }
@@ -501,6 +503,49 @@ int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const doub
         GMM_CUDA(cudaMemcpyAsync(dp + off, hp + off, n, cudaMemcpyHostToDevice, s));
         return GMM_OK;
     };
+    // Large populations in page-locked buffers: split into chunks, queue every chunk's upload on
+    // a second stream and let the kernels of chunk k run while chunk k+1 is still in flight.
+    const bool all_pinned = (!nt || pinned(torsion_deg_h)) && (!nx || pinned(xform_h)) && (!nr || pinned(rot_allele_h)) &&
+                            pinned(out_scores_h) && (!out_counts_h || pinned(out_counts_h)) && !nxyz;
+    if (all_pinned && P >= 4 * 4096) {
+        // two chunks, 1/8 + 7/8: the small one starts the GPU early, the big one keeps the kernels at
+        // their efficient size while its upload hides behind the first chunk's compute
+        constexpr int kChunks = 2;
+        if (!c->copy_stream) {
+            GMM_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+            for (int k = 0; k <= kChunks; ++k) GMM_CUDA(cudaEventCreateWithFlags(&c->ev_copy[k], cudaEventDisableTiming));
+        }
+        if ((rc = ensure_scratch(c, contacts_scratch_bytes(c, P)))) return rc;   // before anything is queued
+        GMM_CUDA(cudaEventRecord(c->ev_copy[kChunks], s));
+        GMM_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_copy[kChunks], 0));   // staging area is free again
+        int bounds[kChunks + 1];
+        bounds[0] = 0; bounds[1] = (P / 8) & ~3; bounds[2] = P;
+        const size_t st = (size_t)c->n_allele_tors * sizeof(double), sx = 12 * sizeof(double),
+                     sr = (size_t)c->n_res * sizeof(double);
+        for (int k = 0; k < kChunks; ++k) {
+            const size_t a0 = bounds[k], n = bounds[k + 1] - bounds[k];
+            if (nt) GMM_CUDA(cudaMemcpyAsync(dp + o_t + a0 * st, (const char*)torsion_deg_h + a0 * st, n * st, cudaMemcpyHostToDevice, c->copy_stream));
+            if (nx) GMM_CUDA(cudaMemcpyAsync(dp + o_x + a0 * sx, (const char*)xform_h + a0 * sx, n * sx, cudaMemcpyHostToDevice, c->copy_stream));
+            if (nr) GMM_CUDA(cudaMemcpyAsync(dp + o_r + a0 * sr, (const char*)rot_allele_h + a0 * sr, n * sr, cudaMemcpyHostToDevice, c->copy_stream));
+            GMM_CUDA(cudaEventRecord(c->ev_copy[k], c->copy_stream));
+        }
+        for (int k = 0; k < kChunks; ++k) {
+            const size_t a0 = bounds[k];
+            const int n = bounds[k + 1] - bounds[k];
+            if (n == 0) continue;
+            GMM_CUDA(cudaStreamWaitEvent(s, c->ev_copy[k], 0));
+            rc = gmm_evaluate(c, n, nt ? (const double*)(dp + o_t + a0 * st) : nullptr,
+                              nx ? (const double*)(dp + o_x + a0 * sx) : nullptr,
+                              nr ? (const double*)(dp + o_r + a0 * sr) : nullptr, nullptr,
+                              (double*)(dp + o_s) + 2 * a0, (int32_t*)(dp + o_c) + 2 * a0, stream);
+            if (rc) return rc;
+            GMM_CUDA(cudaMemcpyAsync(out_scores_h + 2 * a0, (double*)(dp + o_s) + 2 * a0, (size_t)n * 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+            if (out_counts_h)
+                GMM_CUDA(cudaMemcpyAsync(out_counts_h + 2 * a0, (int32_t*)(dp + o_c) + 2 * a0, (size_t)n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+        }
+        GMM_CUDA(cudaStreamSynchronize(s));
+        return GMM_OK;
+    }
     if ((rc = h2d(o_t, torsion_deg_h, nt))) return rc;
     if ((rc = h2d(o_x, xform_h, nx))) return rc;
     if ((rc = h2d(o_r, rot_allele_h, nr))) return rc;

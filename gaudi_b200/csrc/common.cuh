@@ -176,6 +176,9 @@ struct gmm_ctx {
     bool prof = false;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool ev_used[3] = {false, false, false};
+    // second stream + events for the chunked upload/compute overlap of gmm_evaluate_host
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // pinned staging for gmm_evaluate_host
     void* h_pin = nullptr; size_t pin_bytes = 0;
     void* d_stage = nullptr; size_t stage_bytes = 0;

@@ -342,3 +342,19 @@ def test_api_errors_and_reserve(small_system, torch_cuda):
     assert L.gmm_contacts(h, 1, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), None, None) == _lib.GMM_ESTATE
     assert L.gmm_create(C.byref(C.c_void_p()), 9999) == _lib.GMM_EINVAL
     assert L.gmm_destroy(h) == 0
+
+
+def test_evaluate_host_pinned_chunked(small_system, torch_cuda):
+    """Page-locked host buffers take the chunked upload/compute-overlap path; same bits."""
+    lig, rec, params, eng = small_system
+    pop = 20001                                            # ragged: chunks of 2500 and 17501
+    tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=29)
+    want_s, want_c, _ = eng.evaluate(tors, xf)
+    t_pin = torch_cuda.as_tensor(tors).pin_memory()
+    x_pin = torch_cuda.as_tensor(xf).pin_memory()
+    s_pin = torch_cuda.full((pop, 2), float("nan"), dtype=torch_cuda.float64).pin_memory()
+    c_pin = torch_cuda.full((pop, 2), -1, dtype=torch_cuda.int32).pin_memory()
+    for _ in range(2):
+        eng.evaluate_host(t_pin, x_pin, scores_out=s_pin, counts_out=c_pin)
+        assert torch_cuda.equal(s_pin, want_s.cpu()) and torch_cuda.equal(c_pin, want_c.cpu())
+        s_pin.fill_(float("nan"))
