@@ -232,6 +232,13 @@ class BatchEvaluator(object):
         mobile_idx = np.concatenate([lig_idx, np.array(sorted(set(flex_idx) - set(lig_idx.tolist())), np.int64)])
         self.mobile_idx = mobile_idx
         self.lig_slice = slice(0, lig.mol.n_atoms)
+        # per molecule: (rows of the mobile array, atom indices inside the molecule) of its mobile atoms
+        self._mobile_of = {}
+        for name in mol_names:
+            lo_m, n_m = offsets[name], template._molecules[name].mol.n_atoms
+            rows = np.flatnonzero((mobile_idx >= lo_m) & (mobile_idx < lo_m + n_m))
+            if len(rows):
+                self._mobile_of[name] = (rows, mobile_idx[rows] - lo_m)
 
         origin = (search.origin_atom + lo) if search is not None else int(lig_idx[0])
         centre = np.asarray(search.center if search is not None else lig.mol.xyz.mean(axis=0), np.float64)
@@ -327,11 +334,24 @@ class BatchEvaluator(object):
             for p in range(len(individuals)):
                 for i, col in members:
                     out[p][i] = round(float(scores[p, col]), objectives[i].precision)
+        # post_express (gaudi/base.py:301-303): every Molecule gene gets its expressed, world-frame
+        # coordinates.  Molecules without mobile atoms share one array (the reference copies the
+        # whole protein on every evaluation); molecules with flexible side chains get a copy with
+        # the moved atoms written in.
+        world = xyz.astype(np.float64) + self.centre
         for p, ind in enumerate(individuals):
-            lig = xyz[p, self.lig_slice]
-            self._coords[id(ind)] = lig
-            # post_express (gaudi/base.py:301-303): cache world-frame coordinates for similarity
-            ind._molecules[self.ligand_name]._expressed_coordinates = lig.astype(np.float64) + self.centre
+            self._coords[id(ind)] = xyz[p, self.lig_slice]
+            for name, gene in ind._molecules.items():
+                lo = self.offsets[name]
+                sel = self._mobile_of.get(name)
+                if sel is None:
+                    gene._expressed_coordinates = gene.mol.xyz
+                elif name == self.ligand_name and len(sel[0]) == gene.mol.n_atoms:
+                    gene._expressed_coordinates = world[p, self.lig_slice]
+                else:
+                    full = gene.mol.xyz.copy()
+                    full[sel[1]] = world[p, sel[0]]
+                    gene._expressed_coordinates = full
             self._scores[id(ind)] = out[p]
         return out
 

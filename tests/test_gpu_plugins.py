@@ -169,3 +169,30 @@ def test_tensor_ga_configs0(cuda):
     big, log, _ = tensor_ga.launch(job(2000, 3), seed=8)
     assert big["fitness"].shape == (2000, 2)
     assert all(entry["speed"] > 2000 for entry in log[1:]), log      # evaluations per second
+
+
+def test_expressed_coordinates_of_every_molecule(cuda):
+    """post_express (gaudi/base.py:301-303) caches coordinates of every Molecule gene, the protein
+    included; with a Rotamers gene its flexible side chains carry the expressed positions."""
+    from gaudi_b200 import base, similarity
+    prot = G.load("5er1_protein_mol2")
+    lig = G.load("5er1_ligand_mol2")
+    library = {"LEU": [[60.0, 170.0], [-60.0, 60.0]], "ASP": [[-170.0, 20.0]], "TYR": [[180.0, 80.0]]}
+    res = sorted({int(prot.resseq[a]) for a in range(prot.n_atoms)
+                  if prot.resname[a][:3].upper() in library})[:5]
+    cfg = job(6, 0, rotamers=([("Protein", str(r)) for r in res], library))
+    random.seed(4)
+    pop = [base.MolecularIndividual(cfg) for _ in range(6)]
+    env = base.Environment(cfg)
+    cfg._environment = env
+    env.evaluate_population(pop)
+    for ind in pop:
+        p_xyz = ind.find_molecule("Protein")._expressed_coordinates
+        l_xyz = ind.find_molecule("Ligand")._expressed_coordinates
+        assert p_xyz.shape == (prot.n_atoms, 3) and l_xyz.shape == (lig.n_atoms, 3)
+        moved = np.abs(p_xyz - prot.xyz).max(axis=1) > 1e-4
+        assert moved.sum() <= 12 * len(res)               # only side-chain atoms of the chosen residues
+        assert set(int(prot.resseq[a]) for a in np.flatnonzero(moved)) <= set(res)
+    assert any((np.abs(i.find_molecule("Protein")._expressed_coordinates - prot.xyz) > 1e-4).any() for i in pop)
+    assert similarity.rmsd(pop[0], pop[0], ["Ligand", "Protein"], 0.5)
+    assert pop[0].similar(pop[0])
