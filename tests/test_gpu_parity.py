@@ -358,3 +358,34 @@ def test_evaluate_host_pinned_chunked(small_system, torch_cuda):
         eng.evaluate_host(t_pin, x_pin, scores_out=s_pin, counts_out=c_pin)
         assert torch_cuda.equal(s_pin, want_s.cpu()) and torch_cuda.equal(c_pin, want_c.cpu())
         s_pin.fill_(float("nan"))
+
+
+def test_whole_population_against_c_oracle(torch_cuda):
+    """EVERY individual of BASELINE.json configs[1] (4,096 poses, 5,000-atom receptor) and a 16,384
+    slice of configs[2] (20,000-atom receptor) against the oracle's C restatement (itself tied to
+    the numpy oracle and the reference's goldens by tests/test_c_oracle.py).  Individuals whose
+    score differs by more than 1e-4 relative must be explained by pairs within 1e-4 A of a cutoff
+    (north_star's exemption), which the numpy oracle adapter quantifies."""
+    import os, sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    import c_oracle
+    from gaudi_b200.engine import Engine
+    for n_rec, pop in ((5000, 4096), (20000, 16384)):
+        params = M.ContactParams()
+        lig = synth.make_ligand(40, 10, seed=1)
+        rec = synth.make_receptor(n_rec, seed=2, params=params)
+        tors, xf = synth.make_alleles(pop, 10, seed=3)
+        eng = Engine(lig, rec, params, device=0)
+        s, c, x = eng.evaluate(tors, xf, want_xyz=True)
+        s = s.cpu().numpy(); c = c.cpu().numpy(); x = x.cpu().numpy().astype(np.float64) + eng.centre
+        ref_s, ref_c, ref_x = c_oracle.COracle(lig, rec, params).evaluate(tors, xf, want_xyz=True)
+        assert np.abs(x - ref_x).max() < XYZ_TOL
+        rel = np.abs(s - ref_s) / np.maximum(1.0, np.abs(ref_s))
+        bad = np.flatnonzero((rel > SCORE_RTOL).any(axis=1) | (c != ref_c).any(axis=1))
+        assert len(bad) < 0.02 * pop, len(bad)            # borderline poses are rare
+        for p in bad[:40]:
+            res = OA.contacts(lig, rec, params, ref_x[p])
+            assert res.borderline, (p, s[p], ref_s[p])
+            assert score_close(s[p, 0], res.clash, res.clash_slack), (p, s[p], res.clash, res.clash_slack)
+            assert score_close(s[p, 1], res.hydro, res.hydro_slack), (p, s[p], res.hydro, res.hydro_slack)
+        eng.close()
