@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 
 #include "common.cuh"
@@ -47,6 +48,8 @@ int ensure_scratch(gmm_ctx* c, size_t bytes) {
 }
 
 int allow_dynamic_smem(const void* kernel, int device, size_t bytes) {
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
     static std::vector<std::pair<const void*, int>> done;
     for (auto& d : done)
         if (d.first == kernel && d.second == device) return GMM_OK;
@@ -55,14 +58,6 @@ int allow_dynamic_smem(const void* kernel, int device, size_t bytes) {
     return GMM_OK;
 }
 
-static inline uint32_t spread10(uint32_t v) {
-    v &= 0x3ff;
-    v = (v | (v << 16)) & 0x030000ff;
-    v = (v | (v << 8)) & 0x0300f00f;
-    v = (v | (v << 4)) & 0x030c30c3;
-    v = (v | (v << 2)) & 0x09249249;
-    return v;
-}
 
 struct DeviceGuard {
     int prev = -1;

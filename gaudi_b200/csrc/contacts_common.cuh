@@ -36,11 +36,6 @@ __device__ __forceinline__ bool ms_excluded(const int32_t* ms_ptr, const int32_t
     return false;
 }
 
-// Shared-memory carve-up used by sweep, finalize and dump.
-struct LigSmem {
-    float4* lig;      // [G][Mp]
-    uint32_t* zm;     // [G][MW]  mobile atoms in zone
-};
 
 // Load G individuals' mobile atoms into slot order and decide which mobile atoms are in the zone.
 template <int THREADS>
