@@ -229,6 +229,35 @@ contacts_fused_kernel(const FusedArgs f) {
         const float4 blo = misc[1], bhi = misc[2];
         const float prad = sqrtf(sph.w) * 1.00001f + 1e-4f;
         int nl = 0;
+        if (S == 1 && a.cull) {
+            // coarse level: 128-atom tiles (4 consecutive leaves); the refine pass below does the
+            // leaf-level work, so every leaf of a surviving tile simply goes on the list
+            for (int base = 0; base < a.n_tiles; base += 32) {
+                const int t = base + lane;
+                bool keep = false;
+                if (t < a.n_tiles) {
+                    const float* bx = a.tile_box + (size_t)t * 8;
+                    const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
+                    const float ex = fmaxf(fmaxf(bx[0] - sph.x, sph.x - bx[3]), 0.f);
+                    const float ey = fmaxf(fmaxf(bx[1] - sph.y, sph.y - bx[4]), 0.f);
+                    const float ez = fmaxf(fmaxf(bx[2] - sph.z, sph.z - bx[5]), 0.f);
+                    const float lim = prad + reach;
+                    keep = ex * ex + ey * ey + ez * ez <= lim * lim &&
+                           bx[0] <= bhi.x + reach && bx[3] >= blo.x - reach &&
+                           bx[1] <= bhi.y + reach && bx[4] >= blo.y - reach &&
+                           bx[2] <= bhi.z + reach && bx[5] >= blo.z - reach;
+                    if (a.n_sseed > 0)
+                        keep = keep || (a.always[4 * t] | a.always[4 * t + 1] | a.always[4 * t + 2] | a.always[4 * t + 3]) != 0u;
+                }
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                if (keep) {
+                    const int pos = nl + 4 * __popc(mask & ((1u << lane) - 1u));
+                    const unsigned l0 = 4u * (unsigned)t;
+                    *reinterpret_cast<uint2*>(list + pos) = make_uint2(l0 | ((l0 + 1u) << 16), (l0 + 2u) | ((l0 + 3u) << 16));
+                }
+                nl += 4 * __popc(mask);
+            }
+        } else
         for (int base = 0; base < f.NST; base += TL) {
             const int st = base + tlane;
             bool keep = false;
@@ -273,7 +302,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 if (i < nl) {
                     st = list[i];
                     keep = a.always[st] != 0u;
-                    if (!keep) {
+                    if (!keep && st * kSubTile < (uint32_t)f.R) {
                         const float* bx = f.sub_box + (size_t)st * 8;
                         const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
                         const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
