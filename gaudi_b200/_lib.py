@@ -33,6 +33,8 @@ SIGNATURES = {
     "gmm_evaluate": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_evaluate_host": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_evaluate_static": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_set_geometry": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_geometry": (_i, [_vp, _i, _vp, _vp, _vp]),
     "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),
     "gmm_contacts_pairs": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, C.POINTER(_i), _vp]),
     "gmm_measure_fp32_peak": (_i, [_i, C.POINTER(_d)]),

@@ -250,9 +250,12 @@ class BatchEvaluator(object):
         self.groups = []            # [(engine, [(objective index, column)])]
         contacts = [(i, o) for i, o in enumerate(environment.objectives.values())
                     if o.__class__.__name__ == "Contacts"]
-        others = [o for o in environment.objectives.values() if o.__class__.__name__ != "Contacts"]
+        self.geometry = [(i, o) for i, o in enumerate(environment.objectives.values())
+                         if getattr(o, "geometry", False)]
+        others = [o for o in environment.objectives.values()
+                  if o.__class__.__name__ != "Contacts" and not getattr(o, "geometry", False)]
         if others:
-            raise NotImplementedError("only Contacts objectives run on the B200 path: %s"
+            raise NotImplementedError("only Contacts, Distance and Angle objectives run on the B200 path: %s"
                                       % [o.name for o in others])
         grouped = OrderedDict()
         for i, o in contacts:
@@ -266,22 +269,25 @@ class BatchEvaluator(object):
             if not placed:
                 grouped[(o.model_key(), len(grouped))] = {"members": [(i, o)], "penalty": o.penalty_key()}
         self.engines = []
+        if not grouped and self.geometry:
+            # restraints only: one context for the expression, with nothing in the Contacts zone
+            grouped[(None, 0)] = {"members": [], "penalty": None}
         for key, g in grouped.items():
-            o = g["members"][0][1]
-            params = o.params()
+            o = g["members"][0][1] if g["members"] else None
+            params = o.params() if o is not None else M.ContactParams(only_internal=True)
             if g["penalty"]:
                 params.cutoff, params.weight = g["penalty"]
             else:
                 params.cutoff = 0.0
-            hyd = {e.upper() for e in o.hydrophobic_elements}
+            hyd = {e.upper() for e in o.hydrophobic_elements} if o is not None else set()
             flags = hb.copy()
             for a, e in enumerate(elements):
                 if e in hyd:
                     flags[a] |= M.F_HYDROPHOBIC
-            for pname in o._probes:
+            for pname in (o._probes if o is not None else [self.ligand_name]):
                 po = offsets[pname]
                 flags[po:po + template._molecules[pname].mol.n_atoms] |= M.F_SEED
-            if not o.only_internal:
+            if o is not None and not o.only_internal:
                 flags[np.asarray(cb_idx, np.int64)] |= M.F_SEED
             if search is not None:
                 flags[lig_idx] |= M.F_XFORM
@@ -296,6 +302,33 @@ class BatchEvaluator(object):
             eng = Engine(mob, rec, params, device=device)
             self.engines.append((eng, [(i, m.column) for i, m in g["members"]]))
         self.mobile, self.receptor = (self.engines[0][0].mobile, self.engines[0][0].receptor) if self.engines else (None, None)
+        # ---- Distance / Angle restraints: one term table on the first context ------------
+        if self.geometry:
+            row_of = {int(a): r for r, a in enumerate(mobile_idx)}
+
+            def locate(spec):
+                molname, serial = spec
+                mol = template._molecules[molname].mol
+                hit = np.flatnonzero(mol.serial == int(serial))
+                if len(hit) != 1:
+                    raise ValueError("atom %s/%s not found" % (molname, serial))
+                return offsets[molname] + int(hit[0])
+
+            def resolve(spec):
+                a = locate(spec)
+                return row_of[a] if a in row_of else [float(v) for v in xyz[a]]
+
+            def covalent(a, b):
+                # chimera.Element.bondLength is not vendored: sum of the bond radii used by the
+                # bond perception of molio (restated, unpinned)
+                ea, eb = elements[locate(a)], elements[locate(b)]
+                return molio.BOND_RADIUS.get(ea, 0.8) + molio.BOND_RADIUS.get(eb, 0.8)
+
+            terms = []
+            for col, (i, o) in enumerate(self.geometry):
+                for t in o.terms(resolve, covalent):
+                    terms.append(dict(t, obj=col))
+            self.engines[0][0].set_geometry(terms, len(self.geometry))
         self._scores = {}           # id(individual) -> list of raw scores
         self._coords = {}           # id(individual) -> (A, 3) float32 device-frame ligand coordinates
         self.centre = centre
@@ -334,6 +367,11 @@ class BatchEvaluator(object):
             for p in range(len(individuals)):
                 for i, col in members:
                     out[p][i] = round(float(scores[p, col]), objectives[i].precision)
+        if self.geometry:
+            geo = self.engines[0][0].geometry(xyz).cpu().numpy()
+            for p in range(len(individuals)):
+                for col, (i, o) in enumerate(self.geometry):
+                    out[p][i] = round(float(geo[p, col]), o.precision)
         # post_express (gaudi/base.py:301-303): every Molecule gene gets its expressed, world-frame
         # coordinates.  Molecules without mobile atoms share one array (the reference copies the
         # whole protein on every evaluation); molecules with flexible side chains get a copy with

@@ -111,7 +111,7 @@ int gmm_destroy(gmm_ctx* c) {
     release(c->d_rot_ptr); release(c->d_rot_delta);
     release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
-    release(c->d_edge); release(c->d_sub_box);
+    release(c->d_edge); release(c->d_sub_box); release(c->d_geo_terms);
     release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx);
     release(c->d_counters);
     if (c->d_scratch) cudaFree(c->d_scratch);
@@ -560,6 +560,45 @@ int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const doub
     for (auto& o : outs)
         if (o.n && !o.direct) memcpy(o.dst, hp + o.off, o.n);
     return GMM_OK;
+}
+
+int gmm_set_geometry(gmm_ctx* c, int n_terms, int n_obj, const int32_t* kind_h, const int32_t* obj_h,
+                     const int32_t* atoms_h, const double* points_h, const double* threshold_h,
+                     const double* tolerance_h, const double* weight_h, const int32_t* planar_h) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_geometry: ctx is NULL");
+    REQUIRE(c->has_mobile, GMM_ESTATE, "gmm_set_geometry: call gmm_set_mobile first");
+    REQUIRE(n_terms >= 0 && n_obj >= 0 && n_obj <= 64, GMM_EINVAL, "gmm_set_geometry: bad counts");
+    DeviceGuard g(c->device);
+    std::vector<GeoTerm> terms(n_terms);
+    for (int k = 0; k < n_terms; ++k) {
+        GeoTerm& t = terms[k];
+        REQUIRE(kind_h[k] >= 0 && kind_h[k] <= 2, GMM_EINVAL, "gmm_set_geometry: term %d has kind %d", k, kind_h[k]);
+        REQUIRE(obj_h[k] >= 0 && obj_h[k] < n_obj, GMM_EINVAL, "gmm_set_geometry: term %d objective out of range", k);
+        t.kind = kind_h[k]; t.obj = obj_h[k];
+        for (int j = 0; j < 4; ++j) {
+            t.atom[j] = atoms_h[4 * k + j];
+            REQUIRE(t.atom[j] < c->M, GMM_EINVAL, "gmm_set_geometry: term %d references mobile atom %d", k, t.atom[j]);
+            for (int d = 0; d < 3; ++d) t.point[j][d] = points_h[(4 * k + j) * 3 + d];
+        }
+        t.threshold = threshold_h[k];
+        t.has_tolerance = (tolerance_h && tolerance_h[k] == tolerance_h[k]) ? 1 : 0;      // NaN = none
+        t.tolerance = t.has_tolerance ? tolerance_h[k] : 0.0;
+        t.weight = weight_h ? weight_h[k] : 1.0;
+        t.planar = planar_h ? planar_h[k] : 0;
+    }
+    int rc = upload(&c->d_geo_terms, terms.data(), terms.size());
+    if (rc) return rc;
+    c->n_geo_terms = n_terms; c->n_geo_obj = n_obj;
+    return GMM_OK;
+}
+
+int gmm_geometry(gmm_ctx* c, int P, const float* xyz_d, double* out_d, void* stream) {
+    int rc = check_ready(c, P, "gmm_geometry");
+    if (rc) return rc;
+    REQUIRE(c->n_geo_obj > 0, GMM_ESTATE, "gmm_geometry: gmm_set_geometry has not been called");
+    REQUIRE((xyz_d && out_d) || P == 0, GMM_EINVAL, "gmm_geometry: NULL buffer");
+    DeviceGuard g(c->device);
+    return launch_geometry(c, P, xyz_d, out_d, (cudaStream_t)stream);
 }
 
 int gmm_rmsd_matrix(gmm_ctx* c, int N, int A, const float* xyz_d, int row0, int row1, float* out_rmsd_d,

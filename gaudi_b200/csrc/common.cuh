@@ -56,6 +56,16 @@ struct Params {
     float f_clash_thr, f_hydro_thr, f_allow, f_amv;   // fp32 copies for score_pair
 };
 
+// One term of a geometric restraint objective (geometry.cu)
+struct GeoTerm {
+    int kind;            // 0 distance, 1 angle (3 points), 2 dihedral (4 points)
+    int obj;             // which output column this term averages into
+    int atom[4];         // mobile atom index, or -1 = use point[k]
+    double point[4][3];  // world-frame coordinates of static atoms / literal points
+    double threshold, tolerance, weight;
+    int has_tolerance, planar;
+};
+
 struct PairScore {
     long long clash_fx;  // |volume overlap| * 2^32 (0 if not a clash)
     long long hydro_fx;  // LJ-like energy * 2^32   (0 if not a hydrophobic contact)
@@ -169,6 +179,9 @@ struct gmm_ctx {
     float rmax_static = 0.f;
     double centre[3] = {0, 0, 0};
 
+    // geometric restraint objectives (gmm_set_geometry)
+    gmm::GeoTerm* d_geo_terms = nullptr; int n_geo_terms = 0, n_geo_obj = 0;
+
     // scratch (grown on demand)
     void* d_scratch = nullptr; size_t scratch_bytes = 0;
     unsigned long long* d_counters = nullptr;   // [4] pair tests, ...
@@ -193,6 +206,7 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
 int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
                           int* handled);
 bool fused_applicable(const gmm_ctx* c);
+int launch_geometry(gmm_ctx* c, int P, const float* xyz, double* out, cudaStream_t s);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);

@@ -185,6 +185,42 @@ class Engine(object):
                                            _dev_ptr(bm), float(threshold), self._stream()))
         return out, bm
 
+    # -- geometric restraint objectives (Distance / Angle) -----------------------------------
+    def set_geometry(self, terms, n_obj):
+        """``terms``: dicts with ``kind`` (0 distance, 1 angle, 2 dihedral), ``obj`` (output column),
+        ``points``: up to 4 entries, each a mobile atom index (int) or world coordinates (3 floats),
+        ``threshold`` (float or ``'planar'`` for angles), optional ``tolerance``, ``weight``."""
+        n = len(terms)
+        kind = np.zeros(n, np.int32); obj = np.zeros(n, np.int32)
+        atoms = -np.ones((n, 4), np.int32); points = np.zeros((n, 4, 3), np.float64)
+        thr = np.zeros(n, np.float64); tol = np.full(n, np.nan); w = np.ones(n, np.float64)
+        planar = np.zeros(n, np.int32)
+        for k, t in enumerate(terms):
+            kind[k], obj[k] = t["kind"], t["obj"]
+            for j, pt in enumerate(t["points"]):
+                if isinstance(pt, (int, np.integer)):
+                    atoms[k, j] = int(pt)
+                else:
+                    points[k, j] = np.asarray(pt, np.float64)
+            if t["threshold"] == "planar":
+                planar[k] = 1
+            else:
+                thr[k] = float(t["threshold"])
+            if t.get("tolerance") is not None:
+                tol[k] = float(t["tolerance"])
+            w[k] = float(t.get("weight", 1.0) if t.get("weight") is not None else 1.0)
+        _lib.check(self._L.gmm_set_geometry(self._h, n, int(n_obj), _np_ptr(kind), _np_ptr(obj), _np_ptr(atoms),
+                                            _np_ptr(points), _np_ptr(thr), _np_ptr(tol), _np_ptr(w), _np_ptr(planar)))
+        self.n_geo_obj = int(n_obj)
+
+    def geometry(self, xyz):
+        """(P, n_obj) float64 restraint scores of expressed coordinates (P, M, 3)."""
+        xyz = self._dev(xyz, torch.float32)
+        P = int(xyz.shape[0])
+        out = torch.empty((P, self.n_geo_obj), dtype=torch.float64, device=self.torch_device)
+        _lib.check(self._L.gmm_geometry(self._h, P, _dev_ptr(xyz), _dev_ptr(out), self._stream()))
+        return out
+
     # -- parity / measurement helpers --------------------------------------------------
     def contact_pairs(self, xyz_one, max_pairs=1 << 16):
         """Pairs behind the Contacts score of one individual: list of

@@ -171,6 +171,20 @@ int gmm_evaluate_static(gmm_ctx* ctx, int P, const double* torsion_deg_d, const 
 int gmm_rmsd_matrix(gmm_ctx* ctx, int N, int A, const float* xyz_d, int row0, int row1,
                     float* out_rmsd_d, uint32_t* out_similar_d, double threshold, void* stream);
 
+/* Geometric restraint objectives on expressed coordinates ("next" row of the scope: Distance,
+ * gaudi/objectives/distance.py:102-129, and Angle, gaudi/objectives/angle.py:86-96).  A term is a
+ * distance (kind 0, points 0-1), an angle at point 1 (kind 1, points 0-2) or an IUPAC dihedral
+ * (kind 2, points 0-3); a point is a mobile atom (atoms_h >= 0) or fixed world coordinates
+ * (atoms_h == -1, points_h).  Terms with the same obj_h are averaged into one output column:
+ * distance terms contribute |d - threshold| (or |-1000 * weight| when d - threshold < tolerance;
+ * tolerance NaN = none), angle terms |threshold - angle| in degrees, or |sin(angle)| if planar. */
+int gmm_set_geometry(gmm_ctx* ctx, int n_terms, int n_obj, const int32_t* kind_h, const int32_t* obj_h,
+                     const int32_t* atoms_h /*[n,4]*/, const double* points_h /*[n,4,3]*/,
+                     const double* threshold_h, const double* tolerance_h, const double* weight_h,
+                     const int32_t* planar_h);
+/*   xyz_d [P, M, 3] fp32 device-frame coordinates; out_d [P, n_obj] fp64 */
+int gmm_geometry(gmm_ctx* ctx, int P, const float* xyz_d, double* out_d, void* stream);
+
 /* Parity / debugging: the pair lists the Contacts score of ONE individual is made of
  * (what Contacts.find_interactions returns, contacts.py:140-146).  Atom ids: mobile atoms
  * 0..M-1, static atoms M..M+R-1 (caller's receptor order).  kind: 0 = clash (volume),

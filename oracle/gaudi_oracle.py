@@ -349,3 +349,36 @@ def greedy_niching(order, similar, not_better):
                 kept = [k for j, k in enumerate(kept) if j not in to_delete]
             kept.append(i)
     return kept
+
+
+# --------------------------------------------------------------------------------------
+# Geometric restraint objectives ("next" row of the scope)
+# --------------------------------------------------------------------------------------
+def distance_objective(probe_xyz, target_xyz, threshold, tolerance=None, weight=1.0):
+    """gaudi/objectives/distance.py:102-129 (``evaluate_distances``): mean absolute deviation of
+    the probe-target distances from ``threshold``; a probe closer than ``threshold + tolerance``
+    contributes ``-1000 * weight`` before the absolute value."""
+    distances = []
+    target = np.asarray(target_xyz, dtype=np.float64)
+    for a in np.asarray(probe_xyz, dtype=np.float64).reshape(-1, 3):
+        d = math.sqrt(((a - target) ** 2).sum()) - threshold
+        if tolerance is not None and d < tolerance:
+            distances.append(-1000 * weight)
+        else:
+            distances.append(d)
+    return float(np.mean(np.absolute(distances)))
+
+
+def angle_objective(points, threshold):
+    """gaudi/objectives/angle.py:86-96: three points -> ``chimera.angle`` (angle at the middle
+    point), four -> ``chimera.dihedral``; ``'planar'`` -> |sin(angle)|, else |threshold - angle|."""
+    p = [np.asarray(x, dtype=np.float64) for x in points]
+    if len(p) == 3:
+        u, w = p[0] - p[1], p[2] - p[1]
+        c = np.dot(u, w) / (np.linalg.norm(u) * np.linalg.norm(w))
+        angle = math.degrees(math.acos(max(-1.0, min(1.0, c))))
+    else:
+        angle = dihedral(*p)
+    if threshold == 'planar':
+        return abs(math.sin(math.radians(angle)))
+    return abs(threshold - angle)
