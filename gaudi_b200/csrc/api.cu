@@ -59,12 +59,6 @@ int allow_dynamic_smem(const void* kernel, int device, size_t bytes) {
 }
 
 
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
-
 }  // namespace gmm
 
 using namespace gmm;

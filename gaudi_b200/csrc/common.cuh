@@ -33,6 +33,13 @@ extern unsigned long long g_launches;
         }                                                                           \
     } while (0)
 
+// selects the context's device for the duration of a call and restores the caller's
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 // ---- tunables ---------------------------------------------------------------------
 constexpr int kTileAtoms = 128;      // receptor atoms per tile (4 per lane)
 constexpr int kSubTile = 32;         // receptor atoms per sub-tile (k-d leaf), one per lane

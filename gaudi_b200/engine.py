@@ -185,6 +185,21 @@ class Engine(object):
                                            _dev_ptr(bm), float(threshold), self._stream()))
         return out, bm
 
+    def similar_lists(self, bits, n, row0=0):
+        """Partner lists of a similarity bitmask from ``rmsd_matrix`` (rows ``row0 ...`` of the
+        ``n x n`` matrix): ``(ptr int64 (rows + 1,), idx int32)`` host arrays, self excluded."""
+        rows = int(bits.shape[0])
+        counts = torch.empty(rows, dtype=torch.int32, device=self.torch_device)
+        _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
+                                             _dev_ptr(counts), None, None, self._stream()))
+        ptr = torch.zeros(rows + 1, dtype=torch.int64, device=self.torch_device)
+        torch.cumsum(counts, 0, out=ptr[1:])
+        total = int(ptr[-1].item())
+        idx = torch.empty(max(total, 1), dtype=torch.int32, device=self.torch_device)
+        _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
+                                             None, _dev_ptr(ptr), _dev_ptr(idx), self._stream()))
+        return ptr.cpu().numpy(), idx[:total].cpu().numpy()
+
     # -- geometric restraint objectives (Distance / Angle) -----------------------------------
     def set_geometry(self, terms, n_obj):
         """``terms``: dicts with ``kind`` (0 distance, 1 angle, 2 dihedral), ``obj`` (output column),
@@ -260,6 +275,17 @@ def measure_fp32_peak(device=0):
 
 def launch_count():
     return int(_lib.lib().gmm_launch_count())
+
+
+def niching_lists(ptr, idx, rank):
+    """Kept candidates (indices, ascending) of the greedy niching pass over partner lists
+    (``gmm_niching_host``); ``rank`` = lexicographic fitness rank, larger is fitter."""
+    ptr = np.ascontiguousarray(ptr, np.int64); idx = np.ascontiguousarray(idx, np.int32)
+    rank = np.ascontiguousarray(rank, np.int64)
+    n = len(rank)
+    kept = np.zeros(n, np.uint8)
+    _lib.check(_lib.lib().gmm_niching_host(n, _np_ptr(ptr), _np_ptr(idx), _np_ptr(rank), _np_ptr(kept)))
+    return np.flatnonzero(kept)
 
 
 def bits_to_bool(bits, n):

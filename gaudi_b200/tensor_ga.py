@@ -27,6 +27,13 @@ import numpy as np
 
 
 # ---- NSGA-II on arrays ---------------------------------------------------------------------
+def _first_below(neg_best, y):
+    """First front whose best second objective is < y; ``neg_best`` holds -best, ascending."""
+    from bisect import bisect_right
+    # best[f] < y  <=>  -best[f] > -y : first index with neg_best > -y
+    return bisect_right(neg_best, -y)
+
+
 def nondominated_fronts(w):
     """Front index of every row of ``w`` (N, M) under maximisation of each column (``wvalues``).
     Equal rows share a front, as in DEAP's sortNondominated (which groups by fitness)."""
@@ -37,28 +44,37 @@ def nondominated_fronts(w):
     inv = inv.reshape(-1)
     u = uniq.shape[0]
     ufront = np.full(u, -1, dtype=np.int64)
-    remaining = np.arange(u)
-    level = 0
-    while len(remaining):
-        sub = uniq[remaining]
-        if sub.shape[1] == 2:
-            # sweep: sort by first objective descending (ties: second descending); a point is
-            # non-dominated iff its second objective exceeds every second objective seen so far
-            order = np.lexsort((-sub[:, 1], -sub[:, 0]))
-            best = np.maximum.accumulate(sub[order, 1])
-            prev = np.concatenate([[-np.inf], best[:-1]])
-            nd = np.zeros(len(sub), dtype=bool)
-            nd[order] = sub[order, 1] > prev
-        else:
+    if uniq.shape[1] == 2:
+        # O(n log n) for two objectives: visit the unique points by first objective descending
+        # (ties: second descending), so every dominator of a point comes before it; front f keeps
+        # the largest second objective it holds (non-increasing in f), and a point joins the first
+        # front whose best is strictly below its own second objective.
+        order = np.lexsort((-uniq[:, 1], -uniq[:, 0]))
+        neg_best = []                      # -best[f], ascending
+        y = uniq[order, 1].tolist()
+        lev = [0] * u
+        for k in range(u):
+            f = _first_below(neg_best, y[k])
+            if f == len(neg_best):
+                neg_best.append(-y[k])
+            else:
+                neg_best[f] = -y[k]
+            lev[k] = f
+        ufront[order] = lev
+    else:
+        remaining = np.arange(u)
+        level = 0
+        while len(remaining):
+            sub = uniq[remaining]
             nd = np.ones(len(sub), dtype=bool)
             for s in range(0, len(sub), 512):          # chunked O(n^2) dominance test
                 blk = sub[s:s + 512]
                 ge = (sub[None, :, :] >= blk[:, None, :]).all(axis=2)
                 gt = (sub[None, :, :] > blk[:, None, :]).any(axis=2)
                 nd[s:s + 512] = ~(ge & gt).any(axis=1)
-        ufront[remaining[nd]] = level
-        remaining = remaining[~nd]
-        level += 1
+            ufront[remaining[nd]] = level
+            remaining = remaining[~nd]
+            level += 1
     front[:] = ufront[inv]
     return front
 
@@ -121,6 +137,11 @@ def niching(sim, w):
     when there is none evicts every similar kept one; hence per candidate: drop it if any similar
     kept individual has rank >= its own, else evict them all and keep it.  Returns kept indices in
     the reference's order."""
+    if isinstance(sim, tuple):                 # (ptr, idx) partner lists from the GPU compaction
+        from .engine import niching_lists
+        return niching_lists(sim[0], sim[1], lex_rank(w))
+    if sim.dtype != np.bool_:
+        return niching_bits(sim, w)
     n = sim.shape[0]
     rank = lex_rank(w)
     kept = np.zeros(n, dtype=bool)
@@ -131,6 +152,36 @@ def niching(sim, w):
                 continue
             kept[hits] = False
         kept[i] = True
+    return np.flatnonzero(kept)
+
+
+def niching_bits(words, w):
+    """``niching`` on the packed bitmask ``gmm_rmsd_matrix`` writes: ``words`` (N, ceil(N/32))
+    uint32/int32, bit ``j & 31`` of word ``j >> 5`` of row ``i`` set when i and j are similar.  A
+    population of 131,072 candidates is a 2 GiB bitmask; the boolean matrix would be 17 GB."""
+    words = np.ascontiguousarray(words).view(np.uint32)
+    n = words.shape[0]
+    rank = lex_rank(w)
+    kept = np.zeros(n, dtype=bool)
+    kept_words = np.zeros(words.shape[1], dtype=np.uint32)
+    for i in range(n):
+        both = words[i] & kept_words
+        nz = np.flatnonzero(both)
+        if len(nz):
+            hits = []
+            for k in nz.tolist():
+                v = int(both[k])
+                while v:
+                    hits.append(32 * k + ((v & -v).bit_length() - 1))
+                    v &= v - 1
+            hits = np.asarray(hits, dtype=np.int64)
+            if (rank[hits] >= rank[i]).any():
+                continue
+            kept[hits] = False
+            for h in hits.tolist():
+                kept_words[h >> 5] &= np.uint32(~(1 << (h & 31)) & 0xFFFFFFFF)
+        kept[i] = True
+        kept_words[i >> 5] |= np.uint32(1 << (i & 31))
     return np.flatnonzero(kept)
 
 
@@ -326,21 +377,28 @@ class TensorGA(object):
         population = self.take(population, order)
         log.append({"gen": 0, "nevals": nev, "speed": nev / max(time.time() - t0, 1e-9)})
         for gen in range(1, ngen + 1):
-            offspring = self.var_or(population, lambda_, cxpb, mutpb)
             t1 = time.time()
+            offspring = self.var_or(population, lambda_, cxpb, mutpb)
+            t2 = time.time()
             # children made by plain reproduction carry their parent's fitness and coordinates
             nev = self.score(offspring)
+            t3 = time.time()
             cand = self.concat(population, offspring)
             w = cand["fitness"] * self.weights[None, :]
             sim = self.similarity(cand["coords"], self.threshold)
+            t4 = time.time()
             kept = niching(sim, w)
             if len(kept) < mu:                                   # algorithms.py:156-158
                 extra = self.rng.integers(0, len(w), size=mu - len(kept))
                 kept = np.concatenate([kept, extra])
             new_pop = self.take(cand, kept)
+            t5 = time.time()
             sel = sel_nsga2(new_pop["fitness"], self.weights, mu)
             population = self.take(new_pop, sel)
-            log.append({"gen": gen, "nevals": nev, "speed": nev / max(time.time() - t1, 1e-9)})
+            t6 = time.time()
+            log.append({"gen": gen, "nevals": nev, "speed": nev / max(t3 - t2, 1e-9),
+                        "seconds": {"variation": t2 - t1, "evaluate": t3 - t2, "similarity": t4 - t3,
+                                    "niching": t5 - t4, "select": t6 - t5, "generation": t6 - t1}})
         return population, log
 
 
@@ -393,8 +451,10 @@ def launch(cfg, device=0, seed=None):
         return out, np.ascontiguousarray(xyz[:, batch.lig_slice])
 
     def similarity(coords, threshold):
-        _, bits = batch.engines[0][0].rmsd_matrix(coords, threshold=threshold, values=False)
-        return bits_to_bool(bits, len(coords))
+        # the N x N bitmask stays on the device; only the (sparse) partner lists come back
+        eng = batch.engines[0][0]
+        _, bits = eng.rmsd_matrix(coords, threshold=threshold, values=False)
+        return eng.similar_lists(bits, len(coords))
 
     ga = TensorGA(spec, cfg.weights, evaluate, similarity, threshold=cfg.similarity.args[1], seed=seed)
     n = cfg.ga.population

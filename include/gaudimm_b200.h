@@ -171,6 +171,22 @@ int gmm_evaluate_static(gmm_ctx* ctx, int P, const double* torsion_deg_d, const 
 int gmm_rmsd_matrix(gmm_ctx* ctx, int N, int A, const float* xyz_d, int row0, int row1,
                     float* out_rmsd_d, uint32_t* out_similar_d, double threshold, void* stream);
 
+/* Partner lists of the similarity bitmask gmm_rmsd_matrix wrote, for the niching pass of
+ * gaudi/algorithms.py:139-155 (which asks ind.similar(other) pair by pair).  bits_d holds rows
+ * [row0,row1) of the N x N matrix, ceil(N/32) uint32 words per row.  Two passes:
+ *   count pass  counts_d != NULL: counts_d[r] = set bits of row r, its own column excluded;
+ *   fill pass   ptr_d + idx_d   : idx_d[ptr_d[r] ...] = partner columns of row r, ascending;
+ * ptr_d is the exclusive prefix sum of the counts (int64, rows + 1 entries), made by the caller. */
+int gmm_similar_lists(gmm_ctx* ctx, int N, int row0, int row1, const uint32_t* bits_d, int32_t* counts_d,
+                      const int64_t* ptr_d, int32_t* idx_d, void* stream);
+
+/* HOST function: the greedy pass of gaudi/algorithms.py:139-155 over HOST partner lists
+ * (ptr_h int64 [N+1], idx_h int32) and the candidates' lexicographic fitness ranks (rank_h,
+ * larger = fitter, as ``i.fitness <= n_i.fitness`` compares wvalues): visit candidates in order;
+ * drop one when a kept partner has rank >= its own, else evict its kept partners and keep it.
+ * kept_h [N] uint8 out. */
+int gmm_niching_host(int N, const int64_t* ptr_h, const int32_t* idx_h, const int64_t* rank_h, uint8_t* kept_h);
+
 /* Geometric restraint objectives on expressed coordinates ("next" row of the scope: Distance,
  * gaudi/objectives/distance.py:102-129, and Angle, gaudi/objectives/angle.py:86-96).  A term is a
  * distance (kind 0, points 0-1), an angle at point 1 (kind 1, points 0-2) or an IUPAC dihedral

@@ -235,6 +235,13 @@ def test_rmsd_matrix(small_system, torch_cuda):
     for r0, r1 in ((128, 1500), (256, 777), (100, 900)):                  # row blocks (multi-GPU shards)
         _, b_blk = eng.rmsd_matrix(big, row0=r0, row1=r1, threshold=2.5, values=False)
         assert torch_cuda.equal(b_blk, b_full[r0:r1]), (r0, r1)
+    # partner lists compacted on the device == the set bits of the bitmask, self excluded
+    for r0, r1 in ((0, 1500), (100, 900)):
+        ptr, idx = eng.similar_lists(b_full[r0:r1], 1500, row0=r0)
+        want = bits_to_bool(b_full[r0:r1], 1500)
+        want[np.arange(r1 - r0), np.arange(r0, r1)] = False
+        assert np.array_equal(ptr, np.concatenate([[0], np.cumsum(want.sum(axis=1))]))
+        assert np.array_equal(idx, np.nonzero(want)[1])
     # properties at full size: symmetric, zero diagonal
     big = synth.make_conformers(n=2048, n_atoms=60, seed=5)
     o, _ = eng.rmsd_matrix(big, threshold=2.5, bits=False)

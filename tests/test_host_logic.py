@@ -179,8 +179,35 @@ def test_tensor_niching_matches_reference_loop():
     inds = [_Ind(tuple(v)) for v in vals]
     index = {id(x): k for k, x in enumerate(inds)}
     want = [index[id(x)] for x in niching(inds, lambda a, b: bool(sim[index[id(a)], index[id(b)]]))]
-    got = TG.niching(sim, vals * np.array([-1.0, -1.0])).tolist()
+    w = vals * np.array([-1.0, -1.0])
+    got = TG.niching(sim, w).tolist()
     assert got == want
+    # same pass on the packed words gmm_rmsd_matrix writes, and on partner lists (gmm_niching_host)
+    padded = np.zeros((n, 96), np.uint8)
+    padded[:, :n] = sim
+    words = np.packbits(padded, axis=1, bitorder="little").view(np.uint32).view(np.int32)
+    assert TG.niching(words, w).tolist() == want
+    off = sim.copy()
+    np.fill_diagonal(off, False)
+    ptr = np.concatenate([[0], np.cumsum(off.sum(axis=1))])
+    assert TG.niching((ptr, np.nonzero(off)[1]), w).tolist() == want
+    assert TG.niching((np.zeros(1, np.int64), np.zeros(0, np.int32)), np.zeros((0, 2))).tolist() == []
+
+
+def test_two_objective_fronts_match_peeling():
+    from gaudi_b200 import tensor_ga as TG
+    rng = np.random.default_rng(4)
+    for n in (1, 2, 37, 400):
+        w = np.round(rng.normal(size=(n, 2)), 1)
+        uniq, inv = np.unique(w, axis=0, return_inverse=True)
+        level = np.full(len(uniq), -1)
+        rem, lv = np.arange(len(uniq)), 0
+        while len(rem):                                   # definition: peel non-dominated layers
+            sub = uniq[rem]
+            dom = ((sub[None] >= sub[:, None]).all(2) & (sub[None] > sub[:, None]).any(2)).any(1)
+            level[rem[~dom]] = lv
+            rem, lv = rem[dom], lv + 1
+        assert np.array_equal(TG.nondominated_fronts(w), level[inv.reshape(-1)])
 
 
 def test_tensor_variation_properties():
