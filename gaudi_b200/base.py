@@ -329,8 +329,6 @@ class BatchEvaluator(object):
                 for t in o.terms(resolve, covalent):
                     terms.append(dict(t, obj=col))
             self.engines[0][0].set_geometry(terms, len(self.geometry))
-        self._scores = {}           # id(individual) -> list of raw scores
-        self._coords = {}           # id(individual) -> (A, 3) float32 device-frame ligand coordinates
         self.centre = centre
         self._sim = None
 
@@ -378,9 +376,7 @@ class BatchEvaluator(object):
         # the moved atoms written in.
         world = xyz.astype(np.float64) + self.centre
         for p, ind in enumerate(individuals):
-            self._coords[id(ind)] = xyz[p, self.lig_slice]
             for name, gene in ind._molecules.items():
-                lo = self.offsets[name]
                 sel = self._mobile_of.get(name)
                 if sel is None:
                     gene._expressed_coordinates = gene.mol.xyz
@@ -390,7 +386,6 @@ class BatchEvaluator(object):
                     full = gene.mol.xyz.copy()
                     full[sel[1]] = world[p, sel[0]]
                     gene._expressed_coordinates = full
-            self._scores[id(ind)] = out[p]
         return out
 
     def score_of(self, individual, objective):
@@ -412,13 +407,16 @@ class BatchEvaluator(object):
                              for ind in individuals])
             _, bits = eng.rmsd_matrix(conf, threshold=threshold, values=False)
             sim &= bits_to_bool(bits, len(individuals))
-        self._sim = ({id(ind): k for k, ind in enumerate(individuals)}, sim, tuple(subjects), float(threshold))
+        # keyed by identity: the tuple keeps the individuals alive so that no later individual can
+        # be handed the id of one of these and read its row by mistake
+        self._sim = ({id(ind): k for k, ind in enumerate(individuals)}, sim, tuple(subjects), float(threshold),
+                     list(individuals))
         return sim
 
     def lookup_similarity(self, ind1, ind2, subjects, threshold):
         if self._sim is None:
             return None
-        index, sim, subj, thr = self._sim
+        index, sim, subj, thr, _alive = self._sim
         a, b = index.get(id(ind1)), index.get(id(ind2))
         if a is None or b is None or subj != tuple(subjects) or thr != float(threshold):
             return None

@@ -67,31 +67,58 @@ __device__ __forceinline__ void fused_drain_pairs(const SweepArgs& a, uint32_t* 
     npq = 0;
 }
 
+// Expand candidates (receptor atoms that can have a contact at all) against the mobile atoms.
+// One candidate per lane.  The pre-filter uses the sweep's expanded form relative to the pose
+// centre: d^2 ~ n + (a . m + |m|^2) with a = -2 (r - c), three FFMA per pair, accepted when
+// d^2 <= (r_m + r_r - thr_min)^2 widened by the same error bound the sweep uses; it only has to
+// be a superset, score_pair decides every pair with exact differences.  Hits are collected as a
+// bit per mobile atom and the set bits of all lanes are then compacted into the pair queue one
+// ballot per round (rounds = the largest hit count of any lane, a handful) instead of one ballot
+// per mobile atom.
 __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint32_t* cq, int& ncq, uint32_t* pq,
-                                                       int& npq, const float4* ligx, const uint32_t* zm, Acc& acc,
-                                                       int lane) {
+                                                       int& npq, const float4* ligx, const float4* ligc,
+                                                       const float4 sph, const uint32_t* zm, Acc& acc, int lane) {
+    const unsigned lt = (1u << lane) - 1u;
     for (int base = 0; base < ncq; base += 32) {
         const int e = base + lane;
-        const bool valid = e < ncq;
         int j = 0;
-        float4 r = make_float4(kFar, kFar, kFar, 0.f);
-        if (valid) { j = (int)cq[e]; r = a.rec4[j]; }
-        for (int s = 0; s < a.M; ++s) {
-            const float4 m = ligx[s];
-            const float d2 = dist2f(r.x, r.y, r.z, m.x, m.y, m.z);
-            const bool hit = valid && d2 <= loose_c2(m.w, r.w, a.thr_min) && ((zm[s >> 5] >> (s & 31)) & 1u);
-            const unsigned mask = __ballot_sync(0xffffffffu, hit);
-            if (mask) {
-                if (hit) pq[npq + __popc(mask & ((1u << lane) - 1u))] = ((uint32_t)s << 22) | (uint32_t)j;
-                npq += __popc(mask);
+        float ax = 0.f, ay = 0.f, az = 0.f, cr = 0.f, slack = -3e38f;      // idle lane: nothing passes
+        if (e < ncq) {
+            j = (int)cq[e];
+            const float4 r = a.rec4[j];
+            const float x = r.x - sph.x, y = r.y - sph.y, z = r.z - sph.z;
+            const float nr = fmaf(z, z, fmaf(y, y, x * x));
+            ax = -2.f * x; ay = -2.f * y; az = -2.f * z;
+            cr = r.w - a.thr_min;
+            slack = 2e-4f + 2e-6f * (nr + sph.w) - nr;                      // error bound of the form, minus n
+        }
+        for (int s0 = 0; s0 < a.M; s0 += 32) {
+            const int n = min(32, a.M - s0);
+            unsigned hits = 0;
+#pragma unroll 4
+            for (int k = 0; k < n; ++k) {
+                const float4 m = ligc[s0 + k];
+                const float t = ligx[s0 + k].w + cr;
+                const float dot = fmaf(ax, m.x, fmaf(ay, m.y, fmaf(az, m.z, m.w)));
+                if (dot <= fmaf(t * 1.000004f, t, slack)) hits |= 1u << k;
+            }
+            hits &= zm[s0 >> 5];
+            unsigned live = __ballot_sync(0xffffffffu, hits != 0u);
+            while (live) {
+                if (hits) {
+                    const int k = __ffs(hits) - 1;
+                    hits &= hits - 1u;
+                    pq[npq + __popc(live & lt)] = ((uint32_t)(s0 + k) << 22) | (uint32_t)j;
+                }
+                npq += __popc(live);
                 __syncwarp();
                 if (npq > kPairQ - 32) fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+                live = __ballot_sync(0xffffffffu, hits != 0u);
             }
         }
     }
     __syncwarp();
-    ncq = 0;
-    fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+    ncq = 0;                 // pairs still queued stay in pq; the caller flushes after the sweep
 }
 
 template <int S>
@@ -335,7 +362,13 @@ contacts_fused_kernel(const FusedArgs f) {
         // ---- 2. sweep -----------------------------------------------------------------------
         int ncq = 0, npq = 0;
         const float near_c = a.rad2 + 2e-4f + 1e-6f * wmax, near_m = 1e-6f - 1.f;
-        for (int gi = wt; gi < ngroups; gi += S) {
+        for (int gi = wt;; gi += S) {
+            // one call site for the expansion keeps the kernel's code (and its instruction-cache
+            // footprint) small: queue nearly full, or nothing left to sweep
+            if (gi >= ngroups || ncq > kCandQ - 128) {
+                fused_drain_candidates(a, cq, ncq, pq, npq, ligx, ligc, sph, zm, acc, lane);
+                if (gi >= ngroups) break;
+            }
             const uint2 st4 = *reinterpret_cast<const uint2*>(list + 4 * gi);
             const uint32_t stv[4] = {st4.x & 0xffffu, st4.x >> 16, st4.y & 0xffffu, st4.y >> 16};
             float ax[4], ay[4], az[4], nr[4], rw[4], ms[4];
@@ -417,9 +450,8 @@ contacts_fused_kernel(const FusedArgs f) {
                 }
             }
             __syncwarp();
-            if (ncq > kCandQ - 128) fused_drain_candidates(a, cq, ncq, pq, npq, ligx, zm, acc, lane);
         }
-        fused_drain_candidates(a, cq, ncq, pq, npq, ligx, zm, acc, lane);
+        fused_drain_pairs(a, pq, npq, ligx, acc, lane);
         team_sync<S>();
 
         // ---- 3. static-static pairs with both atoms in the zone ------------------------------

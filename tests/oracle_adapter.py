@@ -51,6 +51,8 @@ def express(mob, tors, xform, rot_allele=None):
 
 
 def _system(mob, rec):
+    # keyed by identity; the cached entry holds references to both objects so that their ids
+    # cannot be recycled for a different model while the entry is alive
     key = (id(mob), id(rec))
     hit = _graph_cache.get(key)
     if hit is None:
@@ -62,8 +64,8 @@ def _system(mob, rec):
         graph = O.Graph(m + rec.n_atoms, bonds)
         radius = np.concatenate([np.asarray(mob.radius, np.float32), np.asarray(rec.radius, np.float32)]).astype(np.float64)
         flags = np.concatenate([mob.flags, rec.flags]).astype(np.uint8)
-        hit = _graph_cache[key] = (graph, radius, flags)
-    return hit
+        hit = _graph_cache[key] = (graph, radius, flags, mob, rec)
+    return hit[:3]
 
 
 def contacts(mob, rec, params, xyz_mobile, with_slack=True):
