@@ -203,8 +203,10 @@ contacts_fused_kernel(const FusedArgs f) {
         bool in = s < a.n_seed;
         if (!in && s < a.M && !internal) {
             const float4 q = ligx[s];
+#pragma unroll 1
             for (int k = 0; k < a.n_seed && !in; ++k)
                 in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
+#pragma unroll 1
             for (int k = 0; k < a.n_sseed && !in; ++k)
                 in = dist2f(a.sseed[k].x, a.sseed[k].y, a.sseed[k].z, q.x, q.y, q.z) <= a.rad2;
         }
@@ -410,6 +412,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 if (!__any_sync(0xffffffffu, near)) continue;
             }
             float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
+#pragma unroll 2
             for (s = a.n_seed; s + 1 < a.M; s += 2) {      // mobile atoms that are not zone seeds
                 const float4 m = ligc[s], q = ligc[s + 1];
 #pragma unroll
@@ -433,6 +436,7 @@ contacts_fused_kernel(const FusedArgs f) {
                     if (band) {     // re-decide with exact differences (same arithmetic as the dump kernel)
                         const float4 r = a.rec4[stv[k] * kSubTile + lane];
                         float e = 3e38f;
+#pragma unroll 2
                         for (int s = 0; s < a.n_seed; ++s)
                             e = fminf(e, dist2f(r.x, r.y, r.z, ligx[s].x, ligx[s].y, ligx[s].z));
                         in = e <= a.rad2;
