@@ -348,7 +348,7 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
         if ((rc = upload(&c->d_rr_idx, idx.data(), idx.size()))) return rc;
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_val, sizeof(long long) * 2 * pr.size()));
         GMM_CUDA(cudaMalloc((void**)&c->d_rr_kind, pr.size()));
-        GMM_CUDA(cudaMalloc((void**)&c->d_edge, sizeof(uint32_t) * pr.size()));
+        GMM_CUDA(cudaMalloc((void**)&c->d_edge, sizeof(uint4) * pr.size()));
         rr_ptr_s.swap(ptr); rr_idx_s.swap(idx);
     }
     // mobile-static exclusions (flexible side chains bonded to the static backbone)

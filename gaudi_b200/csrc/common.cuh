@@ -176,7 +176,8 @@ struct gmm_ctx {
     int32_t* d_rr_ptr = nullptr; int32_t* d_rr_idx = nullptr;   // sorted index space
     long long* d_rr_val = nullptr;   // [nnz,2] clash_fx, hydro_fx
     uint8_t* d_rr_kind = nullptr;    // [nnz]
-    uint32_t* d_edge = nullptr;      // [nnz]   b | a_local << 24 | kind << 29 (fused kernel)
+    uint4* d_edge = nullptr;         // [nnz]   x: b | a_local << 24 | kind << 29, (z, w): the pair's value
+                                     //         (clash or hydrophobic, never both) as int64 fixed point (fused kernel)
     float* d_sub_box = nullptr;      // [Rpad/32 + 1, 8] sub-tile boxes (last = dummy leaf)
     int rr_nnz = 0;
     float4* d_sseed = nullptr; int n_sseed = 0;                  // static zone seeds (CB atoms)

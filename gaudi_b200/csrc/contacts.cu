@@ -315,7 +315,7 @@ contacts_finalize_kernel(const FinArgs f) {
 // static-static pair values and always-in-zone atoms (run once per gmm_set_receptor)
 // ---------------------------------------------------------------------------------------
 __global__ void rr_values_kernel(int R, const int32_t* rr_ptr, const int32_t* rr_idx, const float4* rec4,
-                                 const uint8_t* rflags, Params prm, long long* val, uint8_t* kind, uint32_t* edge) {
+                                 const uint8_t* rflags, Params prm, long long* val, uint8_t* kind, uint4* edge) {
     const int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia >= R) return;
     const float4 A = rec4[ia];
@@ -327,7 +327,10 @@ __global__ void rr_values_kernel(int R, const int32_t* rr_ptr, const int32_t* rr
         val[2 * (size_t)e] = ps.clash_fx;
         val[2 * (size_t)e + 1] = ps.hydro_fx;
         kind[e] = (uint8_t)ps.kind;
-        edge[e] = (uint32_t)ib | ((uint32_t)(ia & 31) << 24) | ((uint32_t)ps.kind << 29);
+        // the two scores exclude each other (overlap above / not above the clash threshold)
+        const unsigned long long v = (unsigned long long)((ps.kind & 1) ? ps.clash_fx : ps.hydro_fx);
+        edge[e] = make_uint4((uint32_t)ib | ((uint32_t)(ia & 31) << 24) | ((uint32_t)ps.kind << 29), 0u,
+                             (uint32_t)v, (uint32_t)(v >> 32));
     }
 }
 

@@ -17,9 +17,9 @@
 //               to the direct-difference definition.  Candidates (atoms that can have a contact
 //               at all) are expanded against the mobile atoms with exact differences and the
 //               surviving pairs scored with all lanes busy (score_pair), as in contacts.cu;
-//   3  static   static-static pairs are stored as per-leaf edge lists; leaves with a non-empty
-//               zone word walk their edges with coalesced loads and test both zone bits in
-//               shared memory;
+//   3  static   static-static pairs are stored as per-leaf edge lists of 16-byte records (partner,
+//               kind, precomputed value); leaves with a non-empty zone word walk their edges with
+//               coalesced 128-bit loads and test both zone bits in shared memory;
 //   4  intra    pairs inside the mobile set (exclusions pre-removed);
 //   5  finish   fixed-point sums -> doubles, x2 (contacts.py:176-177), cutoff penalty
 //               (contacts.py:132-133).
@@ -33,7 +33,7 @@ struct FusedArgs {
     SweepArgs s;
     int NST, R;
     const float* sub_box;
-    const int32_t* rr_ptr; const uint32_t* edge; const long long* rr_val;
+    const int32_t* rr_ptr; const uint4* edge;
     const uint32_t* mm_pairs; int n_mm;
     double* scores; int32_t* counts;
     int ind_bytes;
@@ -319,11 +319,10 @@ contacts_fused_kernel(const FusedArgs f) {
             if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)st;
         }
         if (S == 1 && a.cull) {
-            // Refine: a leaf stays only if some mobile atom is within reach of its box (the
-            // sphere/box test above keeps ~40 leaves, this keeps ~27; the sweep of a leaf costs
-            // more than this test).  One leaf per lane, compacted in place.
+            // Leaf level, cheap test first: the sphere/box test again, now on the 32-atom boxes
+            // (about half of the leaves of the surviving tiles go).  Compacted in place.
             __syncwarp();
-            int nout = 0;
+            int nmid = 0;
             for (int base = 0; base < nl; base += 32) {
                 const int i = base + lane;
                 uint32_t st = 0;
@@ -332,6 +331,38 @@ contacts_fused_kernel(const FusedArgs f) {
                     st = list[i];
                     keep = a.always[st] != 0u;
                     if (!keep && st * kSubTile < (uint32_t)f.R) {
+                        const float4 b0 = *reinterpret_cast<const float4*>(f.sub_box + (size_t)st * 8);
+                        const float4 b1 = *reinterpret_cast<const float4*>(f.sub_box + (size_t)st * 8 + 4);
+                        const float reach = fmaxf(sqrtf(a.rad2), b1.z + a.rmax_mobile - a.thr_min) + a.reach_extra;
+                        const float ex = fmaxf(fmaxf(b0.x - sph.x, sph.x - b0.w), 0.f);
+                        const float ey = fmaxf(fmaxf(b0.y - sph.y, sph.y - b1.x), 0.f);
+                        const float ez = fmaxf(fmaxf(b0.z - sph.z, sph.z - b1.y), 0.f);
+                        const float lim = prad + reach;
+                        keep = ex * ex + ey * ey + ez * ez <= lim * lim &&
+                               b0.x <= bhi.x + reach && b0.w >= blo.x - reach &&
+                               b0.y <= bhi.y + reach && b1.x >= blo.y - reach &&
+                               b0.z <= bhi.z + reach && b1.y >= blo.z - reach;
+                    }
+                }
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                __syncwarp();
+                if (keep) list[nmid + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)st;
+                nmid += __popc(mask);
+                __syncwarp();
+            }
+            nl = nmid;
+            // Refine: a leaf stays only if some mobile atom is within reach of its box (the
+            // sphere/box test above keeps ~40 leaves, this keeps ~27; the sweep of a leaf costs
+            // more than this test).  One leaf per lane, compacted in place.
+            int nout = 0;
+            for (int base = 0; base < nl; base += 32) {
+                const int i = base + lane;
+                uint32_t st = 0;
+                bool keep = false;
+                if (i < nl) {
+                    st = list[i];
+                    keep = a.always[st] != 0u;
+                    if (!keep) {
                         const float* bx = f.sub_box + (size_t)st * 8;
                         const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
                         const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
@@ -480,17 +511,17 @@ contacts_fused_kernel(const FusedArgs f) {
                     const int e0 = __shfl_sync(0xffffffffu, my_e0, src), e1 = __shfl_sync(0xffffffffu, my_e1, src);
                     for (int e = e0 + lane; e < e1; e += 64) {      // two independent edges in flight
                         const int e2 = e + 32;
-                        const uint32_t en = f.edge[e];
-                        const uint32_t en2 = e2 < e1 ? f.edge[e2] : 0u;
-                        const uint32_t kind = en >> 29, al = (en >> 24) & 31u, b = en & 0x3fffffu;
-                        const uint32_t kind2 = en2 >> 29, al2 = (en2 >> 24) & 31u, b2 = en2 & 0x3fffffu;
+                        const uint4 en = f.edge[e];                 // the value rides with the edge: no
+                        const uint4 en2 = e2 < e1 ? f.edge[e2] : make_uint4(0u, 0u, 0u, 0u);   // dependent gather
+                        const uint32_t kind = en.x >> 29, al = (en.x >> 24) & 31u, b = en.x & 0x3fffffu;
+                        const uint32_t kind2 = en2.x >> 29, al2 = (en2.x >> 24) & 31u, b2 = en2.x & 0x3fffffu;
                         if (kind && ((z >> al) & 1u) && ((zone[b >> 5] >> (b & 31u)) & 1u)) {
-                            if (kind & 1) { acc.cfx += f.rr_val[2 * (size_t)e]; ++acc.nc; }
-                            if (kind & 2) { acc.hfx += f.rr_val[2 * (size_t)e + 1]; ++acc.nh; }
+                            const long long v = (long long)(((unsigned long long)en.w << 32) | en.z);
+                            if (kind & 1) { acc.cfx += v; ++acc.nc; } else { acc.hfx += v; ++acc.nh; }
                         }
                         if (kind2 && ((z >> al2) & 1u) && ((zone[b2 >> 5] >> (b2 & 31u)) & 1u)) {
-                            if (kind2 & 1) { acc.cfx += f.rr_val[2 * (size_t)e2]; ++acc.nc; }
-                            if (kind2 & 2) { acc.hfx += f.rr_val[2 * (size_t)e2 + 1]; ++acc.nh; }
+                            const long long v = (long long)(((unsigned long long)en2.w << 32) | en2.z);
+                            if (kind2 & 1) { acc.cfx += v; ++acc.nc; } else { acc.hfx += v; ++acc.nh; }
                         }
                     }
                 }
@@ -567,7 +598,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     fill_sweep_args(c, P, xyz, f.s);
     f.NST = c->Rpad / kSubTile; f.R = c->R;
     f.sub_box = c->d_sub_box;
-    f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge; f.rr_val = c->d_rr_val;
+    f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge;
     f.mm_pairs = c->d_mm_pairs; f.n_mm = c->n_mm;
     f.scores = scores; f.counts = counts;
     const size_t ind = fused_ind_bytes(c);
