@@ -95,7 +95,7 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
         for (int s0 = 0; s0 < a.M; s0 += 32) {
             const int n = min(32, a.M - s0);
             unsigned hits = 0;
-#pragma unroll 4
+#pragma unroll 2
             for (int k = 0; k < n; ++k) {
                 const float4 m = ligc[s0 + k];
                 const float t = ligx[s0 + k].w + cr;
@@ -367,6 +367,7 @@ contacts_fused_kernel(const FusedArgs f) {
                         const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
                         const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
                         float mn = 3e38f;
+#pragma unroll 2
                         for (int s = 0; s < a.M; ++s) {
                             const float4 m = ligx[s];
                             const float ex = fmaxf(fmaxf(b0 - m.x, m.x - b3), 0.f);
