@@ -247,7 +247,9 @@ contacts_fused_kernel(const FusedArgs f) {
         const float x = m.x - sph.x, y = m.y - sph.y, z = m.z - sph.z;
         ligc[s] = make_float4(x, y, z, fmaf(z, z, fmaf(y, y, x * x)));
     }
-    for (int st = tlane; st <= f.NST; st += TL) zone[st] = a.always[st];
+    // always-in-zone receptor atoms exist only when the receptor holds zone seeds (n_sseed > 0)
+    const bool has_always = a.n_sseed > 0;
+    for (int st = tlane; st <= f.NST; st += TL) zone[st] = has_always ? a.always[st] : 0u;
 
     Acc acc; acc.cfx = 0; acc.hfx = 0; acc.nc = 0; acc.nh = 0;
     int swept_leaves = 0;
@@ -265,17 +267,18 @@ contacts_fused_kernel(const FusedArgs f) {
                 const int t = base + lane;
                 bool keep = false;
                 if (t < a.n_tiles) {
-                    const float* bx = a.tile_box + (size_t)t * 8;
-                    const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
-                    const float ex = fmaxf(fmaxf(bx[0] - sph.x, sph.x - bx[3]), 0.f);
-                    const float ey = fmaxf(fmaxf(bx[1] - sph.y, sph.y - bx[4]), 0.f);
-                    const float ez = fmaxf(fmaxf(bx[2] - sph.z, sph.z - bx[5]), 0.f);
+                    const float4 b0 = *reinterpret_cast<const float4*>(a.tile_box + (size_t)t * 8);
+                    const float4 b1 = *reinterpret_cast<const float4*>(a.tile_box + (size_t)t * 8 + 4);
+                    const float reach = fmaxf(sqrtf(a.rad2), b1.z + a.rmax_mobile - a.thr_min) + a.reach_extra;
+                    const float ex = fmaxf(fmaxf(b0.x - sph.x, sph.x - b0.w), 0.f);
+                    const float ey = fmaxf(fmaxf(b0.y - sph.y, sph.y - b1.x), 0.f);
+                    const float ez = fmaxf(fmaxf(b0.z - sph.z, sph.z - b1.y), 0.f);
                     const float lim = prad + reach;
                     keep = ex * ex + ey * ey + ez * ez <= lim * lim &&
-                           bx[0] <= bhi.x + reach && bx[3] >= blo.x - reach &&
-                           bx[1] <= bhi.y + reach && bx[4] >= blo.y - reach &&
-                           bx[2] <= bhi.z + reach && bx[5] >= blo.z - reach;
-                    if (a.n_sseed > 0)
+                           b0.x <= bhi.x + reach && b0.w >= blo.x - reach &&
+                           b0.y <= bhi.y + reach && b1.x >= blo.y - reach &&
+                           b0.z <= bhi.z + reach && b1.y >= blo.z - reach;
+                    if (has_always)
                         keep = keep || (a.always[4 * t] | a.always[4 * t + 1] | a.always[4 * t + 2] | a.always[4 * t + 3]) != 0u;
                 }
                 const unsigned mask = __ballot_sync(0xffffffffu, keep);
@@ -291,7 +294,7 @@ contacts_fused_kernel(const FusedArgs f) {
             const int st = base + tlane;
             bool keep = false;
             if (st < f.NST && st * kSubTile < f.R) {
-                if (!a.cull || a.always[st] != 0u) {
+                if (!a.cull || (has_always && a.always[st] != 0u)) {
                     keep = true;
                 } else {
                     const float* bx = f.sub_box + (size_t)st * 8;
@@ -329,7 +332,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 bool keep = false;
                 if (i < nl) {
                     st = list[i];
-                    keep = a.always[st] != 0u;
+                    keep = has_always && a.always[st] != 0u;
                     if (!keep && st * kSubTile < (uint32_t)f.R) {
                         const float4 b0 = *reinterpret_cast<const float4*>(f.sub_box + (size_t)st * 8);
                         const float4 b1 = *reinterpret_cast<const float4*>(f.sub_box + (size_t)st * 8 + 4);
@@ -361,7 +364,7 @@ contacts_fused_kernel(const FusedArgs f) {
                 bool keep = false;
                 if (i < nl) {
                     st = list[i];
-                    keep = a.always[st] != 0u;
+                    keep = has_always && a.always[st] != 0u;
                     if (!keep) {
                         const float* bx = f.sub_box + (size_t)st * 8;
                         const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
