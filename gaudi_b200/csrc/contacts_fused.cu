@@ -121,7 +121,11 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
     ncq = 0;                 // pairs still queued stay in pq; the caller flushes after the sweep
 }
 
-template <int S>
+// S: warps per individual.  CULL: leaves out of reach of the pose are skipped (the normal mode);
+// without it every leaf is swept (the dense mode the FP32 roofline is quoted for).  A template
+// parameter rather than a run-time flag: the kernel is sensitive to its instruction footprint
+// and each variant carries only its own code.
+template <int S, bool CULL>
 __global__ void __launch_bounds__(128, 8)
 contacts_fused_kernel(const FusedArgs f) {
     const SweepArgs& a = f.s;
@@ -260,7 +264,7 @@ contacts_fused_kernel(const FusedArgs f) {
         const float4 blo = misc[1], bhi = misc[2];
         const float prad = sqrtf(sph.w) * 1.00001f + 1e-4f;
         int nl = 0;
-        if (S == 1 && a.cull) {
+        if (S == 1 && CULL) {
             // coarse level: 128-atom tiles (4 consecutive leaves); the refine pass below does the
             // leaf-level work, so every leaf of a surviving tile simply goes on the list
             for (int base = 0; base < a.n_tiles; base += 32) {
@@ -294,7 +298,7 @@ contacts_fused_kernel(const FusedArgs f) {
             const int st = base + tlane;
             bool keep = false;
             if (st < f.NST && st * kSubTile < f.R) {
-                if (!a.cull || (has_always && a.always[st] != 0u)) {
+                if (!CULL || (has_always && a.always[st] != 0u)) {
                     keep = true;
                 } else {
                     const float* bx = f.sub_box + (size_t)st * 8;
@@ -321,7 +325,7 @@ contacts_fused_kernel(const FusedArgs f) {
             }
             if (keep) list[pos + __popc(mask & ((1u << lane) - 1u))] = (uint16_t)st;
         }
-        if (S == 1 && a.cull) {
+        if (S == 1 && CULL) {
             // Leaf level, cheap test first: the sphere/box test again, now on the 32-atom boxes
             // (about half of the leaves of the surviving tiles go).  Compacted in place.
             __syncwarp();
@@ -421,13 +425,24 @@ contacts_fused_kernel(const FusedArgs f) {
             }
             // two mobile atoms per step: 6 FFMA + one 3-input FMNMX3 per receptor atom
             int s = 0;
+            if (CULL) {
 #pragma unroll 2
-            for (; s + 1 < a.n_seed; s += 2) {
-                const float4 m = ligc[s], q = ligc[s + 1];
+                for (; s + 1 < a.n_seed; s += 2) {
+                    const float4 m = ligc[s], q = ligc[s + 1];
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    ms[k] = fminf(ms[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
-                                               fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
+                    for (int k = 0; k < 4; ++k)
+                        ms[k] = fminf(ms[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
+                                                   fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
+                }
+            } else {
+#pragma unroll 4
+                for (; s + 1 < a.n_seed; s += 2) {
+                    const float4 m = ligc[s], q = ligc[s + 1];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        ms[k] = fminf(ms[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
+                                                   fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
+                }
             }
             if (s < a.n_seed) {
                 const float4 m = ligc[s];
@@ -619,15 +634,12 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     if (ind + queues > limit) return GMM_OK;    // not handled
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
     GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));
-    if (S == 1) {
-        { const int rc = allow_dynamic_smem((const void*)contacts_fused_kernel<1>, c->device, limit); if (rc) return rc; }
-        if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
-        contacts_fused_kernel<1><<<(P + 3) / 4, 128, smem, s>>>(f);
-    } else {
-        { const int rc = allow_dynamic_smem((const void*)contacts_fused_kernel<4>, c->device, limit); if (rc) return rc; }
-        if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
-        contacts_fused_kernel<4><<<P, 128, smem, s>>>(f);
-    }
+    const bool cull = f.s.cull != 0;
+    void (*kernel)(const FusedArgs) = S == 1 ? (cull ? contacts_fused_kernel<1, true> : contacts_fused_kernel<1, false>)
+                                             : (cull ? contacts_fused_kernel<4, true> : contacts_fused_kernel<4, false>);
+    { const int rc = allow_dynamic_smem((const void*)kernel, c->device, limit); if (rc) return rc; }
+    if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
+    kernel<<<S == 1 ? (P + 3) / 4 : P, 128, smem, s>>>(f);
     GMM_LAUNCH_CHECK("contacts_fused_kernel");
     if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[3], s)); c->ev_used[1] = true; c->ev_used[2] = false; }
     *handled = 1;
