@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgaudimm_b200.so")
 
 GMM_OK, GMM_EINVAL, GMM_ECUDA, GMM_ESTATE, GMM_ELIMIT = 0, -1, -2, -3, -4
-OPT_ONLY_INTERNAL, OPT_NO_CULL, OPT_TILED = 1, 2, 4
+OPT_ONLY_INTERNAL, OPT_NO_CULL, OPT_TILED, OPT_SEQUENTIAL_EXPRESS = 1, 2, 4, 8
 MAX_MOBILE_ATOMS, MAX_TORSIONS = 1024, 1024
 
 _vp, _i, _d = C.c_void_p, C.c_int, C.c_double
@@ -33,6 +33,7 @@ SIGNATURES = {
     "gmm_evaluate": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_evaluate_host": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_evaluate_static": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_express_is_tree": (_i, [_vp]),
     "gmm_set_geometry": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_geometry": (_i, [_vp, _i, _vp, _vp, _vp]),
     "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),

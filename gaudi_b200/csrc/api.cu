@@ -101,6 +101,7 @@ int gmm_destroy(gmm_ctx* c) {
     cudaDeviceSynchronize();
     release(c->d_xyz0); release(c->d_mflags_atom); release(c->d_tfixed); release(c->d_tmoving);
     release(c->d_tsrc); release(c->d_tsnap); release(c->d_tmask); release(c->d_slot2atom);
+    release(c->d_tree_src); release(c->d_tree_snap); release(c->d_tree_axis); release(c->d_tree_amask);
     release(c->d_mrad_slot); release(c->d_mflags_slot); release(c->d_mm_pairs);
     release(c->d_rot_ptr); release(c->d_rot_delta);
     release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
@@ -135,6 +136,97 @@ int gmm_set_params(gmm_ctx* c, double zone_radius, double clash_threshold, doubl
     return GMM_OK;
 }
 
+
+// ---- kinematic-tree form of the torsions ----------------------------------------------------------
+// The reference applies its BondRots one after another on the current coordinates
+// (torsion.py:153-164, rotamers.py:186-189).  When the moving sets form a tree (nested or
+// disjoint, which is what one anchor per molecule gives) the same result is obtained by rotating
+// about the TEMPLATE axes, innermost moving set first: every rotation matrix then depends only on
+// its own angle and all of them can be built at once.  Whether a given model has that property is
+// not argued but tested here, on the host, against the sequential definition with random angles;
+// models that fail (or have more than 64 bonds) keep the sequential kernel.
+static void rodrigues(const double* u, double ang_deg, double R[9]) {
+    const double th = ang_deg * (3.14159265358979323846 / 180.0), c = std::cos(th), s = std::sin(th), o = 1.0 - c;
+    R[0] = c + o * u[0] * u[0]; R[1] = o * u[0] * u[1] - s * u[2]; R[2] = o * u[0] * u[2] + s * u[1];
+    R[3] = o * u[0] * u[1] + s * u[2]; R[4] = c + o * u[1] * u[1]; R[5] = o * u[1] * u[2] - s * u[0];
+    R[6] = o * u[0] * u[2] - s * u[1]; R[7] = o * u[1] * u[2] + s * u[0]; R[8] = c + o * u[2] * u[2];
+}
+
+static int build_tree_form(gmm_ctx* c, const double* xyz0, const int32_t* tf, const int32_t* tm, const uint64_t* mask,
+                           const uint8_t* snap, const int32_t* src) {
+    const int M = c->M, T = c->T, W = c->W;
+    c->tree_ok = false;
+    if (T == 0 || T > 64) return GMM_OK;
+    auto in_mask = [&](int t, int i) { return (mask[(size_t)t * W + (i >> 6)] >> (i & 63)) & 1ull; };
+    std::vector<int> order(T), count(T, 0);
+    for (int t = 0; t < T; ++t)
+        for (int i = 0; i < M; ++i) count[t] += in_mask(t, i) ? 1 : 0;
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return count[a] < count[b]; });
+    std::vector<double> axis((size_t)T * 6);
+    std::vector<int32_t> tsrc(T);
+    std::vector<uint8_t> tsnap(T);
+    std::vector<uint64_t> amask(M, 0);
+    for (int k = 0; k < T; ++k) {
+        const int t = order[k];
+        const double* a = xyz0 + 3 * (size_t)tf[t];
+        const double* b = xyz0 + 3 * (size_t)tm[t];
+        double u[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+        const double n = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        if (!(n > 0.0)) return GMM_OK;                       // degenerate bond: sequential kernel decides
+        for (int d = 0; d < 3; ++d) { axis[(size_t)k * 6 + d] = u[d] / n; axis[(size_t)k * 6 + 3 + d] = b[d]; }
+        tsrc[k] = src[t]; tsnap[k] = snap[t];
+        for (int i = 0; i < M; ++i)
+            if (in_mask(t, i)) amask[i] |= 1ull << k;
+    }
+    // the test: three sets of random angles, both definitions in fp64
+    uint64_t lcg = 0x9E3779B97F4A7C15ull;
+    double worst = 0.0;
+    for (int trial = 0; trial < 3; ++trial) {
+        std::vector<double> ang(T);
+        for (int t = 0; t < T; ++t) {
+            lcg = lcg * 6364136223846793005ull + 1442695040888963407ull;
+            ang[t] = ((double)(lcg >> 11) / 9007199254740992.0) * 360.0 - 180.0;
+        }
+        std::vector<double> seq(xyz0, xyz0 + (size_t)M * 3), tree(xyz0, xyz0 + (size_t)M * 3);
+        for (int t = 0; t < T; ++t) {                        // sequential, current axes
+            const double* a = &seq[3 * (size_t)tf[t]];
+            const double b[3] = {seq[3 * (size_t)tm[t]], seq[3 * (size_t)tm[t] + 1], seq[3 * (size_t)tm[t] + 2]};
+            double u[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+            const double n = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+            for (double& v : u) v /= n;
+            double R[9];
+            rodrigues(u, ang[t], R);
+            for (int i = 0; i < M; ++i) {
+                if (!in_mask(t, i)) continue;
+                double* x = &seq[3 * (size_t)i];
+                const double v[3] = {x[0] - b[0], x[1] - b[1], x[2] - b[2]};
+                for (int d = 0; d < 3; ++d) x[d] = b[d] + R[3 * d] * v[0] + R[3 * d + 1] * v[1] + R[3 * d + 2] * v[2];
+            }
+        }
+        for (int k = 0; k < T; ++k) {                        // tree form, template axes, innermost first
+            double R[9];
+            rodrigues(&axis[(size_t)k * 6], ang[order[k]], R);
+            const double* b = &axis[(size_t)k * 6 + 3];
+            for (int i = 0; i < M; ++i) {
+                if (!((amask[i] >> k) & 1ull)) continue;
+                double* x = &tree[3 * (size_t)i];
+                const double v[3] = {x[0] - b[0], x[1] - b[1], x[2] - b[2]};
+                for (int d = 0; d < 3; ++d) x[d] = b[d] + R[3 * d] * v[0] + R[3 * d + 1] * v[1] + R[3 * d + 2] * v[2];
+            }
+        }
+        for (size_t e = 0; e < seq.size(); ++e) worst = std::max(worst, std::fabs(seq[e] - tree[e]));
+    }
+    if (!(worst < 1e-9)) return GMM_OK;
+    int rc;
+    if ((rc = upload(&c->d_tree_src, tsrc.data(), (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tree_snap, tsnap.data(), (size_t)T))) return rc;
+    if ((rc = upload(&c->d_tree_axis, axis.data(), axis.size()))) return rc;
+    if ((rc = upload(&c->d_tree_amask, amask.data(), (size_t)M))) return rc;
+    c->tree_ok = true;
+    return GMM_OK;
+}
+
 int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_h, const uint8_t* flags_h,
                    int T, const int32_t* tors_fixed_h, const int32_t* tors_moving_h,
                    const uint64_t* tors_mask_h, const uint8_t* tors_snap_h, const int32_t* tors_src_h,
@@ -165,6 +257,8 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
     if ((rc = upload(&c->d_tsrc, tors_src_h, (size_t)T))) return rc;
     if ((rc = upload(&c->d_tsnap, tors_snap_h, (size_t)T))) return rc;
     if ((rc = upload(&c->d_tmask, tors_mask_h, (size_t)T * W))) return rc;
+
+    if ((rc = build_tree_form(c, xyz0_h, tors_fixed_h, tors_moving_h, tors_mask_h, tors_snap_h, tors_src_h))) return rc;
 
     // slot order for the Contacts kernels: zone seeds first (their min-distance decides zone
     // membership of receptor atoms), the other mobile atoms after; padded to an even count.
@@ -202,6 +296,11 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
     if ((rc = upload(&c->d_mm_pairs, mm.data(), mm.size()))) return rc;
     c->has_mobile = true;
     return GMM_OK;
+}
+
+int gmm_express_is_tree(gmm_ctx* c) {
+    REQUIRE(c && c->has_mobile, GMM_ESTATE, "gmm_express_is_tree: gmm_set_mobile has not been called");
+    return (c->tree_ok && !(c->prm.options & GMM_OPT_SEQUENTIAL_EXPRESS)) ? 1 : 0;
 }
 
 int gmm_set_rotamers(gmm_ctx* c, int n_res, const int32_t* rot_ptr_h, const double* rot_delta_h) {

@@ -155,6 +155,12 @@ struct gmm_ctx {
     uint8_t* d_mflags_atom = nullptr;// [M]     caller order (express needs F_XFORM)
     int32_t* d_tfixed = nullptr; int32_t* d_tmoving = nullptr; int32_t* d_tsrc = nullptr;
     uint8_t* d_tsnap = nullptr; uint64_t* d_tmask = nullptr;
+    // kinematic-tree form of the same torsions (express.cu), valid when tree_ok: bonds in
+    // application order (innermost moving set first), template axes, per-atom bond bitmask
+    bool tree_ok = false;
+    int32_t* d_tree_src = nullptr; uint8_t* d_tree_snap = nullptr;
+    double* d_tree_axis = nullptr;   // [T,6] unit axis (fixed -> moving) and the moving atom's template position
+    uint64_t* d_tree_amask = nullptr;  // [M] bit t: atom turns with bond t (T <= 64)
     int32_t* d_slot2atom = nullptr;  // [Mp]    slot -> caller atom index (-1 = padding)
     float* d_mrad_slot = nullptr;    // [Mp]
     uint8_t* d_mflags_slot = nullptr;// [Mp]

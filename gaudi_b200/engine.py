@@ -45,7 +45,8 @@ class Engine(object):
         self._h = h
         p = self.params
         opts = ((_lib.OPT_ONLY_INTERNAL if p.only_internal else 0) | (0 if p.cull else _lib.OPT_NO_CULL)
-                | (_lib.OPT_TILED if p.tiled else 0))
+                | (_lib.OPT_TILED if p.tiled else 0)
+                | (_lib.OPT_SEQUENTIAL_EXPRESS if getattr(p, 'sequential_express', False) else 0))
         _lib.check(self._L.gmm_set_params(h, p.radius, p.clash_threshold, p.hydrophobic_threshold,
                                           p.hbond_allowance, p.assumed_max_vdw, p.cutoff, p.weight,
                                           opts))
@@ -184,6 +185,13 @@ class Engine(object):
         _lib.check(self._L.gmm_rmsd_matrix(self._h, n, a, _dev_ptr(xyz), int(row0), row1, _dev_ptr(out),
                                            _dev_ptr(bm), float(threshold), self._stream()))
         return out, bm
+
+    def express_is_tree(self):
+        """True when this model is expressed in the kinematic-tree form (see ``gmm_express_is_tree``)."""
+        rc = self._L.gmm_express_is_tree(self._h)
+        if rc < 0:
+            _lib.check(rc)
+        return bool(rc)
 
     def similar_lists(self, bits, n, row0=0):
         """Partner lists of a similarity bitmask from ``rmsd_matrix`` (rows ``row0 ...`` of the

@@ -50,6 +50,9 @@ extern "C" {
 #define GMM_OPT_ONLY_INTERNAL  1  /* Contacts(only_internal=True), contacts.py:199 */
 #define GMM_OPT_NO_CULL        2  /* score every receptor tile (dense), no bounding-box culling */
 #define GMM_OPT_TILED          4  /* use the two-kernel tiled Contacts path instead of the fused one */
+#define GMM_OPT_SEQUENTIAL_EXPRESS 8 /* apply the bond rotations one after another on the current coordinates
+                                     * (the reference's own order of operations) even when the model allows the
+                                     * faster kinematic-tree form; results agree to fp64 rounding */
 
 #define GMM_MAX_MOBILE_ATOMS   1024
 #define GMM_MAX_TORSIONS       1024
@@ -170,6 +173,11 @@ int gmm_evaluate_static(gmm_ctx* ctx, int P, const double* torsion_deg_d, const 
  *   out_similar_d    [row1-row0, ceil(N/32)] uint32 bitmask of NOT(rmsd^2 > thr^2), or NULL */
 int gmm_rmsd_matrix(gmm_ctx* ctx, int N, int A, const float* xyz_d, int row0, int row1,
                     float* out_rmsd_d, uint32_t* out_similar_d, double threshold, void* stream);
+
+/* 1 when gmm_express / gmm_evaluate use the kinematic-tree form for this model (moving sets nested
+ * or disjoint, verified numerically in gmm_set_mobile), 0 when they apply the bond rotations one
+ * after another, negative on error.  Informational: both forms give the reference's coordinates. */
+int gmm_express_is_tree(gmm_ctx* ctx);
 
 /* Partner lists of the similarity bitmask gmm_rmsd_matrix wrote, for the niching pass of
  * gaudi/algorithms.py:139-155 (which asks ind.similar(other) pair by pair).  bits_d holds rows

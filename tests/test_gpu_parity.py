@@ -57,6 +57,33 @@ def test_express_matches_oracle(small_system, torch_cuda):
     assert np.abs(xyz[:, lig.origin_atom] - xf.reshape(-1, 3, 4)[:, :, 3]).max() < 1e-5
 
 
+def test_express_tree_form_and_sequential_agree(small_system, torch_cuda):
+    """The kinematic-tree express kernel (template axes, all bond maps built at once) against the
+    kernel that applies the rotations one after another, as the reference does; and a model whose
+    moving sets do NOT form a tree, which must be detected and expressed sequentially."""
+    import copy
+    from gaudi_b200.engine import Engine
+    lig, rec, params, eng = small_system
+    tors, xf = synth.make_alleles(777, lig.n_allele_torsions, seed=31)
+    seq = Engine(lig, rec, M.ContactParams(sequential_express=True), device=0)
+    a = eng.express(tors, xf)
+    b = seq.express(tors, xf)
+    assert eng.express_is_tree() and not seq.express_is_tree()
+    assert float((a - b).abs().max()) <= 2e-6          # same fp64 maths up to rounding, fp32 output
+    # overlapping (not nested) moving sets: bond 1 also drags half of bond 0's moving side along
+    odd = copy.deepcopy(lig)
+    odd.tors_mask = lig.tors_mask.copy()
+    m0 = lig.moving_indices(0)
+    extra = [int(i) for i in m0[: max(1, len(m0) // 2)] if i not in (int(lig.tors_fixed[1]), int(lig.tors_moving[1]))]
+    for i in extra:
+        odd.tors_mask[1, i >> 6] |= np.uint64(1) << np.uint64(i & 63)
+    e_odd = Engine(odd, rec, params, device=0)
+    assert not e_odd.express_is_tree()
+    got = e_odd.express(tors[:64], xf[:64]).cpu().numpy().astype(np.float64) + e_odd.centre
+    for p in range(0, 64, 7):
+        assert np.abs(OA.express(odd, tors[p], xf[p]) - got[p]).max() < XYZ_TOL
+
+
 def test_express_identity(small_system):
     lig, rec, params, eng = small_system
     tors = np.zeros((3, lig.n_allele_torsions))
