@@ -265,8 +265,13 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
     std::vector<int32_t> order(M);
     std::iota(order.begin(), order.end(), 0);
     std::stable_partition(order.begin(), order.end(), [&](int i) { return (flags_h[i] & GMM_F_SEED) != 0; });
-    int n_seed = 0;
+    int n_seed = 0, n_hseed = 0;
     for (int i = 0; i < M; ++i) n_seed += (flags_h[i] & GMM_F_SEED) ? 1 : 0;
+    // among the seeds, hydrophobic ones first: the pair pre-filter of the fused kernel uses a
+    // tighter cutoff for partners that cannot make a hydrophobic contact
+    std::stable_partition(order.begin(), order.begin() + n_seed, [&](int i) { return (flags_h[i] & GMM_F_HYDROPHOBIC) != 0; });
+    for (int i = 0; i < M; ++i) n_hseed += ((flags_h[i] & GMM_F_SEED) && (flags_h[i] & GMM_F_HYDROPHOBIC)) ? 1 : 0;
+    c->n_hseed = n_hseed;
     const int Mp = (M + 1) & ~1;
     c->Mp = Mp; c->n_seed = n_seed; c->all_seed = (n_seed == M);
     c->h_slot2atom.assign(Mp, -1);

@@ -150,6 +150,7 @@ struct gmm_ctx {
 
     // mobile model (slot order = seeds first; d_slot2atom maps back to the caller's order)
     int M = 0, Mp = 0, T = 0, W = 0, n_allele_tors = 0, n_seed = 0;
+    int n_hseed = 0;                 // zone seeds that are hydrophobic: slots [0, n_hseed)
     int origin_atom = 0, tors_before_search = 1;
     double* d_xyz0 = nullptr;        // [M,3]   caller order
     uint8_t* d_mflags_atom = nullptr;// [M]     caller order (express needs F_XFORM)

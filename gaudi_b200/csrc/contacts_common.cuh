@@ -6,7 +6,7 @@
 namespace gmm {
 
 struct SweepArgs {
-    int P, M, Mp, MW, n_seed, n_tiles, tiles_per_chunk, n_chunks, ZW, n_sseed, cull, all_seed;
+    int P, M, Mp, MW, n_seed, n_hseed, n_tiles, tiles_per_chunk, n_chunks, ZW, n_sseed, cull, all_seed;
     const float* xyz;
     const int32_t* slot2atom; const float* mrad; const uint8_t* mflags;
     const float4* rec4; const uint8_t* rflags; const float* tile_box; const uint32_t* always;
@@ -14,7 +14,7 @@ struct SweepArgs {
     const int32_t* ms_ptr; const int32_t* ms_idx;
     uint32_t* zone; long long* partial; unsigned long long* counters;
     Params prm;
-    float rad2, thr_min, rmax_mobile, reach_extra;
+    float rad2, thr_min, thr_tight, rmax_mobile, reach_extra;
 };
 
 __device__ __forceinline__ float dist2f(float ax, float ay, float az, float bx, float by, float bz) {

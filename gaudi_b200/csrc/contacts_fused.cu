@@ -82,23 +82,28 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
     for (int base = 0; base < ncq; base += 32) {
         const int e = base + lane;
         int j = 0;
-        float ax = 0.f, ay = 0.f, az = 0.f, cr = 0.f, slack = -3e38f;      // idle lane: nothing passes
+        float ax = 0.f, ay = 0.f, az = 0.f, cr_h = 0.f, cr_c = 0.f, slack = -3e38f;   // idle lane: nothing passes
         if (e < ncq) {
             j = (int)cq[e];
             const float4 r = a.rec4[j];
+            const bool rh = (a.rflags[j] & GMM_F_HYDROPHOBIC) != 0;
             const float x = r.x - sph.x, y = r.y - sph.y, z = r.z - sph.z;
             const float nr = fmaf(z, z, fmaf(y, y, x * x));
             ax = -2.f * x; ay = -2.f * y; az = -2.f * z;
-            cr = r.w - a.thr_min;
-            slack = 2e-4f + 2e-6f * (nr + sph.w) - nr;                      // error bound of the form, minus n
+            cr_c = r.w - a.thr_tight;                    // partner that cannot make a hydrophobic contact
+            cr_h = rh ? r.w - a.thr_min : cr_c;          // partner that can (if this atom can)
+            slack = 2e-4f + 2e-6f * (nr + sph.w) - nr;   // error bound of the form, minus n
         }
         for (int s0 = 0; s0 < a.M; s0 += 32) {
             const int n = min(32, a.M - s0);
             unsigned hits = 0;
+            // slots [0, n_hseed) are hydrophobic seeds, [n_hseed, n_seed) the other seeds; mobile
+            // atoms that are not seeds (flexible side chains) are not sorted and keep the wide cutoff
 #pragma unroll 2
             for (int k = 0; k < n; ++k) {
-                const float4 m = ligc[s0 + k];
-                const float t = ligx[s0 + k].w + cr;
+                const int s = s0 + k;
+                const float4 m = ligc[s];
+                const float t = ligx[s].w + ((s < a.n_hseed || s >= a.n_seed) ? cr_h : cr_c);
                 const float dot = fmaf(ax, m.x, fmaf(ay, m.y, fmaf(az, m.z, m.w)));
                 if (dot <= fmaf(t * 1.000004f, t, slack)) hits |= 1u << k;
             }
@@ -554,8 +559,10 @@ contacts_fused_kernel(const FusedArgs f) {
         const int sa = pr & 0xffff, sb = pr >> 16;
         if (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u)) continue;
         const float4 A = ligx[sa], B = ligx[sb];
-        if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > loose_c2(A.w, B.w, a.thr_min)) continue;
-        const PairScore ps = score_pair(A.x, A.y, A.z, A.w, a.mflags[sa], B.x, B.y, B.z, B.w, a.mflags[sb], a.prm);
+        const unsigned fa = a.mflags[sa], fb = a.mflags[sb];
+        const float thr = (fa & fb & GMM_F_HYDROPHOBIC) ? a.thr_min : a.thr_tight;
+        if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > loose_c2(A.w, B.w, thr)) continue;
+        const PairScore ps = score_pair(A.x, A.y, A.z, A.w, fa, B.x, B.y, B.z, B.w, fb, a.prm);
         if (ps.kind & 1) { acc.cfx += ps.clash_fx; ++acc.nc; }
         if (ps.kind & 2) { acc.hfx += ps.hydro_fx; ++acc.nh; }
     }
