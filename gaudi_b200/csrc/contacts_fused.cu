@@ -424,7 +424,9 @@ contacts_fused_kernel(const FusedArgs f) {
                 const float x = r.x - sph.x, y = r.y - sph.y, z = r.z - sph.z;
                 ax[k] = -2.f * x; ay[k] = -2.f * y; az[k] = -2.f * z;
                 nr[k] = fmaf(z, z, fmaf(y, y, x * x));
-                rw[k] = r.w;
+                // candidate reach of this atom: its radius minus the overlap cutoff it can reach at
+                // all (an atom that is not hydrophobic only takes part in clashes)
+                rw[k] = r.w - ((a.rflags[stv[k] * kSubTile + lane] & GMM_F_HYDROPHOBIC) ? a.thr_min : a.thr_tight);
                 ms[k] = 3e38f;
                 swept_leaves += (stv[k] < (uint32_t)f.NST) ? 1 : 0;
             }
@@ -497,7 +499,7 @@ contacts_fused_kernel(const FusedArgs f) {
                         in = e <= a.rad2;
                     }
                 }
-                const float c = rw[k] + a.rmax_mobile - a.thr_min;
+                const float c = rw[k] + a.rmax_mobile;
                 const bool cand = in && (ma[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin);
                 const unsigned zb = __ballot_sync(0xffffffffu, in);
                 const unsigned cb = __ballot_sync(0xffffffffu, cand);
