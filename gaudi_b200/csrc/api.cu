@@ -102,7 +102,7 @@ int gmm_destroy(gmm_ctx* c) {
     release(c->d_xyz0); release(c->d_mflags_atom); release(c->d_tfixed); release(c->d_tmoving);
     release(c->d_tsrc); release(c->d_tsnap); release(c->d_tmask); release(c->d_slot2atom);
     release(c->d_tree_src); release(c->d_tree_snap); release(c->d_tree_axis); release(c->d_tree_amask);
-    release(c->d_mrad_slot); release(c->d_mflags_slot); release(c->d_mm_pairs);
+    release(c->d_mrad_slot); release(c->d_mflags_slot); release(c->d_mm_pairs); release(c->d_mm_c2);
     release(c->d_rot_ptr); release(c->d_rot_delta);
     release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
@@ -298,6 +298,7 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
             if (!excl) mm.push_back((uint32_t)c->h_atom2slot[a] | ((uint32_t)c->h_atom2slot[b] << 16));
         }
     c->n_mm = (int)mm.size();
+    c->h_mm_pairs = mm; c->h_mflags_slot = fl;
     if ((rc = upload(&c->d_mm_pairs, mm.data(), mm.size()))) return rc;
     c->has_mobile = true;
     return GMM_OK;
@@ -495,6 +496,18 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
             if ((rc = launch_rr_values(c, 0))) return rc;     // same values, compacted order
             GMM_CUDA(cudaDeviceSynchronize());
         }
+    }
+    {   // squared pre-filter cutoff of every intra-mobile pair: constant per pair under these parameters
+        float thr_min, thr_tight;
+        prefilter_cutoffs(c, &thr_min, &thr_tight);
+        std::vector<float> c2(c->h_mm_pairs.size());
+        for (size_t e = 0; e < c2.size(); ++e) {
+            const int sa = c->h_mm_pairs[e] & 0xffff, sb = c->h_mm_pairs[e] >> 16;
+            const bool both = (c->h_mflags_slot[sa] & c->h_mflags_slot[sb] & GMM_F_HYDROPHOBIC) != 0;
+            const float cc = c->h_mrad[sa] + c->h_mrad[sb] - (both ? thr_min : thr_tight);
+            c2[e] = cc * cc * 1.000004f + 1e-6f;
+        }
+        if ((rc = upload(&c->d_mm_c2, c2.data(), c2.size()))) return rc;
     }
     c->has_receptor = true;
     return GMM_OK;

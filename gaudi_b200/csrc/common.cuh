@@ -167,6 +167,8 @@ struct gmm_ctx {
     uint8_t* d_mflags_slot = nullptr;// [Mp]
     uint32_t* d_mm_pairs = nullptr;  // [n_mm]  slotA | slotB << 16, not excluded
     int n_mm = 0;
+    float* d_mm_c2 = nullptr;        // [n_mm]  squared pre-filter cutoff of each pair (set with the receptor)
+    std::vector<uint32_t> h_mm_pairs; std::vector<uint8_t> h_mflags_slot;
     float rmax_mobile = 0.f;
     bool all_seed = true;
     std::vector<int32_t> h_slot2atom, h_atom2slot;
@@ -220,6 +222,7 @@ int launch_contacts(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t
                     cudaStream_t s, void* workspace = nullptr);
 int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, int32_t* counts, cudaStream_t s,
                           int* handled);
+void prefilter_cutoffs(const gmm_ctx* c, float* thr_min, float* thr_tight);
 bool fused_applicable(const gmm_ctx* c);
 int launch_geometry(gmm_ctx* c, int P, const float* xyz, double* out, cudaStream_t s);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);

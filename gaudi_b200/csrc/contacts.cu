@@ -471,6 +471,15 @@ size_t contacts_scratch_bytes(const gmm_ctx* c, int P) {
     return b + 256;
 }
 
+// Pre-filter cutoffs on the overlap r_a + r_b - d: a hydrophobic contact needs both atoms
+// hydrophobic and overlap >= hydro_thr, a clash needs overlap > clash_thr (after an H-bond
+// allowance that only ever lowers the overlap when it is positive).  thr_min admits either,
+// thr_tight is enough for a pair that cannot be a hydrophobic contact.
+void prefilter_cutoffs(const gmm_ctx* c, float* thr_min, float* thr_tight) {
+    *thr_tight = (float)(c->prm.clash_thr + fmin(0.0, c->prm.hb_allow));
+    *thr_min = fminf((float)c->prm.hydro_thr, *thr_tight);
+}
+
 void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a) {
     a.P = P; a.M = c->M; a.Mp = c->Mp; a.MW = (c->Mp + 31) / 32; a.n_seed = c->n_seed; a.n_hseed = c->n_hseed;
     a.n_tiles = c->n_tiles; a.ZW = c->n_tiles * 4;
@@ -483,12 +492,7 @@ void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a) {
     a.counters = c->d_counters;
     a.prm = c->prm;
     a.rad2 = (float)(c->prm.zone_radius * c->prm.zone_radius);
-    // pre-filter cutoffs on the overlap r_a + r_b - d: a hydrophobic contact needs both atoms
-    // hydrophobic and overlap >= hydro_thr, a clash needs overlap > clash_thr (after an H-bond
-    // allowance that only ever lowers the overlap when it is positive).  thr_min admits either,
-    // thr_tight is enough for a pair that cannot be a hydrophobic contact.
-    a.thr_tight = (float)(c->prm.clash_thr + fmin(0.0, c->prm.hb_allow));
-    a.thr_min = fminf((float)c->prm.hydro_thr, a.thr_tight);
+    prefilter_cutoffs(c, &a.thr_min, &a.thr_tight);
     a.rmax_mobile = c->rmax_mobile;
     a.reach_extra = 2e-3f;
     plan_chunks(c, P, &a.tiles_per_chunk, &a.n_chunks);

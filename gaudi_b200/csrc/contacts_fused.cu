@@ -34,7 +34,7 @@ struct FusedArgs {
     int NST, R;
     const float* sub_box;
     const int32_t* rr_ptr; const uint4* edge;
-    const uint32_t* mm_pairs; int n_mm;
+    const uint32_t* mm_pairs; const float* mm_c2; int n_mm;
     double* scores; int32_t* counts;
     int ind_bytes;
     int tma_pose;     // 1: stage each pose with one TMA bulk copy (size and alignment permit)
@@ -558,13 +558,12 @@ contacts_fused_kernel(const FusedArgs f) {
     // ---- 4. pairs inside the mobile set ------------------------------------------------------
     for (int e = tlane; e < f.n_mm; e += TL) {
         const uint32_t pr = f.mm_pairs[e];
+        const float c2 = f.mm_c2[e];                   // (r_a + r_b - cutoff)^2, fixed per pair
         const int sa = pr & 0xffff, sb = pr >> 16;
-        if (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u)) continue;
+        if (!a.all_seed && (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u))) continue;
         const float4 A = ligx[sa], B = ligx[sb];
-        const unsigned fa = a.mflags[sa], fb = a.mflags[sb];
-        const float thr = (fa & fb & GMM_F_HYDROPHOBIC) ? a.thr_min : a.thr_tight;
-        if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > loose_c2(A.w, B.w, thr)) continue;
-        const PairScore ps = score_pair(A.x, A.y, A.z, A.w, fa, B.x, B.y, B.z, B.w, fb, a.prm);
+        if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > c2) continue;
+        const PairScore ps = score_pair(A.x, A.y, A.z, A.w, a.mflags[sa], B.x, B.y, B.z, B.w, a.mflags[sb], a.prm);
         if (ps.kind & 1) { acc.cfx += ps.clash_fx; ++acc.nc; }
         if (ps.kind & 2) { acc.hfx += ps.hydro_fx; ++acc.nh; }
     }
@@ -627,7 +626,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.NST = c->Rpad / kSubTile; f.R = c->R;
     f.sub_box = c->d_sub_box;
     f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge;
-    f.mm_pairs = c->d_mm_pairs; f.n_mm = c->n_mm;
+    f.mm_pairs = c->d_mm_pairs; f.mm_c2 = c->d_mm_c2; f.n_mm = c->n_mm;
     f.scores = scores; f.counts = counts;
     const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
