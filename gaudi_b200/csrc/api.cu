@@ -107,6 +107,7 @@ int gmm_destroy(gmm_ctx* c) {
     release(c->d_rec4); release(c->d_rflags); release(c->d_tile_box); release(c->d_always);
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
     release(c->d_edge); release(c->d_sub_box); release(c->d_geo_terms);
+    if (c->d_rmsd_ws) { cudaFree(c->d_rmsd_ws); c->d_rmsd_ws = nullptr; c->rmsd_ws_bytes = 0; }
     release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx);
     release(c->d_counters);
     if (c->d_scratch) cudaFree(c->d_scratch);

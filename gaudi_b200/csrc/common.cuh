@@ -212,6 +212,7 @@ struct gmm_ctx {
     // pinned staging for gmm_evaluate_host
     void* h_pin = nullptr; size_t pin_bytes = 0;
     void* d_stage = nullptr; size_t stage_bytes = 0;
+    void* d_rmsd_ws = nullptr; size_t rmsd_ws_bytes = 0;   // centred conformers + norms (rmsd.cu, bitmask path)
 };
 
 namespace gmm {

@@ -11,6 +11,9 @@
 // 4 LDS.128 feeding 64 FADD + 64 FFMA.  Staging is double-buffered with cp.async (LDGSTS):
 // the transposing scatter of chunk c+1 runs while chunk c is being consumed, without passing
 // through registers.
+#include <cuda_fp16.h>
+#include <mma.h>
+
 #include "common.cuh"
 
 namespace gmm {
@@ -149,6 +152,251 @@ rmsd_tile_kernel(const RmsdArgs a) {
     }
 }
 
+
+// ---- similarity bitmask through the tensor cores ------------------------------------------------
+// A bitmask-only call does not need the RMSD values, only on which side of the threshold each
+// pair falls.  With the conformers re-centred on their column means, sum_k (a_k - b_k)^2 =
+// |a|^2 + |b|^2 - 2 a.b, and a.b over all pairs of a tile is a GEMM: it runs on the tensor
+// cores in FP16 with fp32 accumulation (mma.sync through the WMMA interface; the re-centred
+// coordinates are a few Angstrom, well inside half range, and half carries the same 11
+// significant bits as TF32 at half the shared-memory traffic and a quarter of the MMA
+// instructions).  That product is only a PRE-FILTER: its error is bounded by
+// 2^-10 (|a|^2 + |b|^2) (Cauchy-Schwarz on the rounded inputs, plus slack for the
+// accumulation), so pairs whose approximate sum is further than that from threshold^2 * A are
+// decided, and the others (about one in a hundred) are queued and re-decided by the same
+// sequential fp32 direct-difference sum the FP32 kernel above computes, on the original
+// coordinates.  The bits are therefore identical to that kernel's (tests compare them).
+constexpr int kMK = 64;          // coordinates per staged chunk (4 k-steps of the m16n16k16 MMA)
+constexpr int kMS = kMK + 8;     // padded row stride of a staged chunk (halves)
+constexpr int kMD = kRT + 4;     // padded row stride of the dot-product tile (floats)
+constexpr int kMQ = 4096;        // queue of pairs to re-decide, per tile
+
+struct RmsdMmaArgs {
+    int N, K, Kp, row0, row1, words;
+    const float* xyz;            // original coordinates [N][K]
+    const __half* xc;            // re-centred, rounded to half, zero-padded [N][Kp]
+    const int* overflow;         // != 0: some re-centred coordinate does not fit half -> nothing is pre-decided
+    const float* norm;           // [N] |xc|^2
+    uint32_t* bits;
+    float thr2, inv_a, cut;      // cut = thr2 * A: the threshold on the un-normalised sum
+    int sym, R0, R1;
+};
+
+__global__ void rmsd_colsum_kernel(int N, int K, const float* __restrict__ xyz, float* __restrict__ colsum) {
+    // grid.x blocks of 256 conformers each add their column sums into colsum[K] (pre-zeroed)
+    const int n0 = blockIdx.x * 256;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        float s = 0.f;
+        const int n1 = min(N, n0 + 256);
+        for (int n = n0; n < n1; ++n) s += xyz[(size_t)n * K + k];
+        atomicAdd(&colsum[k], s);
+    }
+}
+
+__global__ void rmsd_center_kernel(int N, int K, int Kp, const float* __restrict__ xyz, const float* __restrict__ colsum,
+                                   __half* __restrict__ xc, float* __restrict__ norm, int* __restrict__ overflow) {
+    const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (n >= N) return;
+    const float inv = 1.0f / (float)N;
+    float s = 0.f;
+    bool big = false;
+    for (int k = lane; k < Kp; k += 32) {
+        float v = 0.f;
+        if (k < K) v = xyz[(size_t)n * K + k] - colsum[k] * inv;
+        big = big || !(fabsf(v) < 6.0e4f);
+        xc[(size_t)n * Kp + k] = __float2half_rn(v);
+        s = fmaf(v, v, s);                       // the norm is of the unrounded value
+    }
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) norm[n] = s;
+    if (big) atomicExch(overflow, 1);
+}
+
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+}
+
+__global__ void __launch_bounds__(256, 2)
+rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
+    using namespace nvcuda;
+    extern __shared__ __align__(128) float smem_m[];
+    // staging: As[2][128][kMS], Bs[2][128][kMS] halves; afterwards the same memory holds the
+    // dot-product tile D[128][kMD] floats; behind it: norms, bit tile, queue
+    constexpr size_t kStageBytes = (size_t)4 * kRT * kMS * sizeof(__half), kDBytes = (size_t)kRT * kMD * sizeof(float);
+    constexpr size_t kUnion = kStageBytes > kDBytes ? kStageBytes : kDBytes;
+    __half* As = reinterpret_cast<__half*>(smem_m);
+    __half* Bs = As + 2 * kRT * kMS;
+    float* D = smem_m;
+    float* na = smem_m + kUnion / sizeof(float);   // [128]
+    float* nb = na + kRT;                          // [128]
+    uint32_t* Wn = reinterpret_cast<uint32_t*>(nb + kRT);   // [128][4]
+    uint32_t* queue = Wn + kRT * 4;                // [kMQ] row << 16 | col
+    int* nq = reinterpret_cast<int*>(queue + kMQ);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int r_base = a.row0 + blockIdx.y * kRT, c_base = blockIdx.x * kRT;
+    const int rb = a.R0 + blockIdx.y, cbk = blockIdx.x;
+    const bool in_square = a.sym && cbk >= a.R0 && cbk < a.R1;
+    if (in_square && cbk < rb) return;                        // written by tile (cbk, rb)
+    const bool mirror = in_square && cbk > rb;
+    if (tid == 0) *nq = 0;
+    if (tid < kRT) {
+        na[tid] = (r_base + tid < a.row1) ? a.norm[r_base + tid] : 0.f;
+        nb[tid] = (c_base + tid < a.N) ? a.norm[c_base + tid] : 0.f;
+    }
+    for (int w = tid; w < kRT * 4; w += 256) Wn[w] = 0u;
+
+    const int n_chunks = (a.Kp + kMK - 1) / kMK;
+    auto stage = [&](int c, int buf) {
+        const int k0 = c * kMK;
+        // 128 rows x 8 sixteen-byte pieces per operand; consecutive threads read consecutive pieces
+        for (int e = tid; e < kRT * (kMK / 8); e += 256) {
+            const int r = e / (kMK / 8), q = e - r * (kMK / 8);
+            const int gk = k0 + 8 * q, ra = r_base + r, cb = c_base + r;
+            __half* da = As + ((size_t)buf * kRT + r) * kMS + 8 * q;
+            __half* db = Bs + ((size_t)buf * kRT + r) * kMS + 8 * q;
+            if (gk < a.Kp && ra < a.row1) cp_async_16(da, a.xc + (size_t)ra * a.Kp + gk);
+            else *reinterpret_cast<uint4*>(da) = make_uint4(0u, 0u, 0u, 0u);
+            if (gk < a.Kp && cb < a.N) cp_async_16(db, a.xc + (size_t)cb * a.Kp + gk);
+            else *reinterpret_cast<uint4*>(db) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        cp_async_commit();
+    };
+
+    // warp (wy, wx) of a 2 x 4 grid owns rows [64 wy, 64 wy + 64) x columns [32 wx, 32 wx + 32)
+    const int wy = warp >> 2, wx = warp & 3;
+    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) wmma::fill_fragment(acc[i][j], 0.0f);
+
+    stage(0, 0);
+    for (int c = 0; c < n_chunks; ++c) {
+        const int buf = c & 1;
+        if (c + 1 < n_chunks) { stage(c + 1, buf ^ 1); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncthreads();
+        const __half* Ab = As + (size_t)buf * kRT * kMS;
+        const __half* Bb = Bs + (size_t)buf * kRT * kMS;
+#pragma unroll
+        for (int k16 = 0; k16 < kMK; k16 += 16) {
+            wmma::fragment<wmma::matrix_a, 16, 16, 16, __half, wmma::row_major> fa[4];
+            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) wmma::load_matrix_sync(fa[i], Ab + (size_t)(wy * 64 + i * 16) * kMS + k16, kMS);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) wmma::load_matrix_sync(fb[j], Bb + (size_t)(wx * 32 + j * 16) * kMS + k16, kMS);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+            wmma::store_matrix_sync(D + (size_t)(wy * 64 + i * 16) * kMD + wx * 32 + j * 16, acc[i][j], kMD, wmma::mem_row_major);
+    __syncthreads();
+    const bool nothing_decided = *a.overflow != 0;
+
+    // pass 1: decided pairs -> bits, undecided pairs -> queue.  Warp w takes rows 16 w .. 16 w + 15,
+    // lanes take 32 consecutive columns: one ballot is one word of the bit tile.
+    for (int rr = 0; rr < 16; ++rr) {
+        const int r = warp * 16 + rr;
+        const bool row_ok = r_base + r < a.row1;
+        const float nr = na[r];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int col = q * 32 + lane;
+            const bool ok = row_ok && c_base + col < a.N;
+            const float nc = nb[col];
+            const float approx = nr + nc - 2.f * D[(size_t)r * kMD + col];
+            const float margin = nothing_decided ? 3e38f : 1.2e-3f * (nr + nc) + 1e-4f * a.cut + 1e-4f;
+            const bool yes = ok && approx < a.cut - margin;
+            const bool maybe = ok && !yes && approx <= a.cut + margin;
+            const unsigned word = __ballot_sync(0xffffffffu, yes);
+            if (lane == 0) Wn[r * 4 + q] = word;
+            __syncwarp();
+            if (maybe) {
+                const int at = atomicAdd(nq, 1);
+                if (at < kMQ) queue[at] = ((uint32_t)r << 16) | (uint32_t)col;
+                else {
+                    // queue full (threshold in the middle of a dense cluster): decide here and now
+                    const float* x = a.xyz + (size_t)(r_base + r) * a.K;
+                    const float* y = a.xyz + (size_t)(c_base + col) * a.K;
+                    float s = 0.f;
+                    for (int k = 0; k < a.K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
+                    if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + q], 1u << lane);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // pass 2: the queue, every thread busy; the sum runs over k in order, exactly as the FP32 kernel's
+    const int n_queued = min(*nq, kMQ);
+    for (int e = tid; e < n_queued; e += 256) {
+        const int r = queue[e] >> 16, col = queue[e] & 0xffff;
+        const float* x = a.xyz + (size_t)(r_base + r) * a.K;
+        const float* y = a.xyz + (size_t)(c_base + col) * a.K;
+        float s = 0.f;
+        for (int k = 0; k < a.K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
+        // similarity.py:67-69: "if rmsd_squared > threshold*threshold: return False"
+        if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + (col >> 5)], 1u << (col & 31));
+    }
+    __syncthreads();
+    for (int w = tid; w < kRT * 4; w += 256) {
+        const int r = w >> 2, q = w & 3, row = r_base + r, wc = c_base / 32 + q;
+        if (row < a.row1 && wc < a.words) a.bits[(size_t)(row - a.row0) * a.words + wc] = Wn[w];
+    }
+    if (mirror) {
+        for (int w = tid; w < kRT * 4; w += 256) {
+            const int cidx = w & 127, rw = w >> 7;
+            unsigned t = 0;
+#pragma unroll 8
+            for (int r = 0; r < 32; ++r) t |= ((Wn[(32 * rw + r) * 4 + (cidx >> 5)] >> (cidx & 31)) & 1u) << r;
+            const int mrow = c_base + cidx, wc = r_base / 32 + rw;
+            if (mrow < a.row1 && mrow < a.N && wc < a.words) a.bits[(size_t)(mrow - a.row0) * a.words + wc] = t;
+        }
+    }
+}
+
+static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, uint32_t* out_bits,
+                           double thr, cudaStream_t s) {
+    const int K = 3 * A, Kp = (K + 15) & ~15;
+    const size_t xc_bytes = ((size_t)N * Kp * sizeof(__half) + 255) / 256 * 256;
+    const size_t need = xc_bytes + ((size_t)N + Kp + 64) * sizeof(float);
+    if (need > c->rmsd_ws_bytes) {
+        if (c->d_rmsd_ws) { GMM_CUDA(cudaDeviceSynchronize()); cudaFree(c->d_rmsd_ws); c->d_rmsd_ws = nullptr; c->rmsd_ws_bytes = 0; }
+        GMM_CUDA(cudaMalloc(&c->d_rmsd_ws, need));
+        c->rmsd_ws_bytes = need;
+    }
+    __half* xc = static_cast<__half*>(c->d_rmsd_ws);
+    float* norm = reinterpret_cast<float*>(static_cast<unsigned char*>(c->d_rmsd_ws) + xc_bytes);
+    float* colsum = norm + N;
+    int* overflow = reinterpret_cast<int*>(colsum + Kp);
+    GMM_CUDA(cudaMemsetAsync(colsum, 0, sizeof(float) * (Kp + 1), s));       // column sums and the flag
+    rmsd_colsum_kernel<<<(N + 255) / 256, 192, 0, s>>>(N, K, xyz, colsum);
+    GMM_LAUNCH_CHECK("rmsd_colsum_kernel");
+    rmsd_center_kernel<<<(int)(((size_t)N * 32 + 255) / 256), 256, 0, s>>>(N, K, Kp, xyz, colsum, xc, norm, overflow);
+    GMM_LAUNCH_CHECK("rmsd_center_kernel");
+    RmsdMmaArgs a;
+    a.N = N; a.K = K; a.Kp = Kp; a.row0 = row0; a.row1 = row1; a.words = (N + 31) / 32;
+    a.xyz = xyz; a.xc = xc; a.norm = norm; a.overflow = overflow; a.bits = out_bits;
+    a.thr2 = (float)(thr * thr); a.inv_a = 1.0f / (float)A; a.cut = a.thr2 * (float)A;
+    a.sym = (row0 % kRT == 0) ? 1 : 0;
+    a.R0 = row0 / kRT; a.R1 = (row1 + kRT - 1) / kRT;
+    dim3 grid((N + kRT - 1) / kRT, (row1 - row0 + kRT - 1) / kRT);
+    const size_t staging = (size_t)4 * kRT * kMS * sizeof(__half), dtile = (size_t)kRT * kMD * sizeof(float);
+    const size_t smem = (staging > dtile ? staging : dtile) + (2 * kRT + kRT * 4 + kMQ + 4) * sizeof(float);
+    { const int rc = allow_dynamic_smem((const void*)rmsd_bits_mma_kernel, c->device, smem); if (rc) return rc; }
+    rmsd_bits_mma_kernel<<<grid, 256, smem, s>>>(a);
+    GMM_LAUNCH_CHECK("rmsd_bits_mma_kernel");
+    return GMM_OK;
+}
+
 template <int RK>
 static int launch_rmsd_rk(const RmsdArgs& a, dim3 grid, cudaStream_t s, int device) {
     const size_t smem = (size_t)4 * RK * kRS * sizeof(float);
@@ -161,6 +409,9 @@ static int launch_rmsd_rk(const RmsdArgs& a, dim3 grid, cudaStream_t s, int devi
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s) {
     if (row1 <= row0 || N == 0) return GMM_OK;
+    // bitmask only: tensor-core pre-filter + exact re-decision (identical bits, several times faster)
+    if (out_rmsd == nullptr && out_bits != nullptr && !(c->prm.options & GMM_OPT_RMSD_SIMT) && A >= 8)
+        return launch_rmsd_mma(c, N, A, xyz, row0, row1, out_bits, thr, s);
     RmsdArgs a;
     a.N = N; a.A = A; a.K = 3 * A; a.row0 = row0; a.row1 = row1;
     a.xyz = xyz; a.out = out_rmsd; a.bits = out_bits; a.words = (N + 31) / 32;

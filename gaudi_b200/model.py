@@ -109,6 +109,7 @@ class ContactParams:
     cull: bool = True       # B200 path only: skip receptor tiles out of reach of a pose
     tiled: bool = False     # B200 path only: two-kernel tiled Contacts path instead of the fused one
     sequential_express: bool = False   # B200 path only: bond rotations one after another (reference order)
+    rmsd_simt: bool = False            # B200 path only: similarity bitmask by the FP32 direct-difference kernel
 
 
 @dataclass

@@ -50,6 +50,8 @@ extern "C" {
 #define GMM_OPT_ONLY_INTERNAL  1  /* Contacts(only_internal=True), contacts.py:199 */
 #define GMM_OPT_NO_CULL        2  /* score every receptor tile (dense), no bounding-box culling */
 #define GMM_OPT_TILED          4  /* use the two-kernel tiled Contacts path instead of the fused one */
+#define GMM_OPT_RMSD_SIMT      16  /* bitmask-only gmm_rmsd_matrix calls: use the FP32 direct-difference kernel
+                                    * instead of the tensor-core pre-filter + exact re-decision (same bits) */
 #define GMM_OPT_SEQUENTIAL_EXPRESS 8 /* apply the bond rotations one after another on the current coordinates
                                      * (the reference's own order of operations) even when the model allows the
                                      * faster kinematic-tree form; results agree to fp64 rounding */
