@@ -247,17 +247,26 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
     for (int w = tid; w < kRT * 4; w += 256) Wn[w] = 0u;
 
     const int n_chunks = (a.Kp + kMK - 1) / kMK;
+    // 128 rows x 8 sixteen-byte pieces per operand and chunk: thread t always moves piece t % 8 of
+    // rows t / 8 + 32 i, so its source rows and validity are fixed for the whole tile
+    const int sq = tid & 7, sr = tid >> 3;
+    const __half* srcA[4]; const __half* srcB[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int ra = r_base + sr + 32 * i, cb = c_base + sr + 32 * i;
+        srcA[i] = ra < a.row1 ? a.xc + (size_t)ra * a.Kp + 8 * sq : nullptr;
+        srcB[i] = cb < a.N ? a.xc + (size_t)cb * a.Kp + 8 * sq : nullptr;
+    }
     auto stage = [&](int c, int buf) {
         const int k0 = c * kMK;
-        // 128 rows x 8 sixteen-byte pieces per operand; consecutive threads read consecutive pieces
-        for (int e = tid; e < kRT * (kMK / 8); e += 256) {
-            const int r = e / (kMK / 8), q = e - r * (kMK / 8);
-            const int gk = k0 + 8 * q, ra = r_base + r, cb = c_base + r;
-            __half* da = As + ((size_t)buf * kRT + r) * kMS + 8 * q;
-            __half* db = Bs + ((size_t)buf * kRT + r) * kMS + 8 * q;
-            if (gk < a.Kp && ra < a.row1) cp_async_16(da, a.xc + (size_t)ra * a.Kp + gk);
+        const bool k_ok = k0 + 8 * sq < a.Kp;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __half* da = As + ((size_t)buf * kRT + sr + 32 * i) * kMS + 8 * sq;
+            __half* db = Bs + ((size_t)buf * kRT + sr + 32 * i) * kMS + 8 * sq;
+            if (k_ok && srcA[i]) cp_async_16(da, srcA[i] + k0);
             else *reinterpret_cast<uint4*>(da) = make_uint4(0u, 0u, 0u, 0u);
-            if (gk < a.Kp && cb < a.N) cp_async_16(db, a.xc + (size_t)cb * a.Kp + gk);
+            if (k_ok && srcB[i]) cp_async_16(db, srcB[i] + k0);
             else *reinterpret_cast<uint4*>(db) = make_uint4(0u, 0u, 0u, 0u);
         }
         cp_async_commit();
@@ -303,33 +312,46 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
     const bool nothing_decided = *a.overflow != 0;
 
     // pass 1: decided pairs -> bits, undecided pairs -> queue.  Warp w takes rows 16 w .. 16 w + 15,
-    // lanes take 32 consecutive columns: one ballot is one word of the bit tile.
+    // lanes take 32 consecutive columns: one ballot is one word of the bit tile.  With
+    // e = 1.2e-3 (|a|^2 + |b|^2) + c0 the bound on the error of the approximate sum
+    // |a|^2 + |b|^2 - 2 D, a pair is certainly similar when D > ((1 + 1.2e-3)(|a|^2 + |b|^2) - cut + c0) / 2
+    // and certainly not when D < ((1 - 1.2e-3)(|a|^2 + |b|^2) - cut - c0) / 2.
+    const float c0 = 1e-4f * a.cut + 1e-4f;
+    float hi_c[4], lo_c[4];
+    bool col_ok[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float nc = nb[q * 32 + lane];
+        hi_c[q] = 0.5f * (1.0012f * nc - a.cut + c0);
+        lo_c[q] = 0.5f * (0.9988f * nc - a.cut - c0);
+        col_ok[q] = c_base + q * 32 + lane < a.N;
+    }
     for (int rr = 0; rr < 16; ++rr) {
         const int r = warp * 16 + rr;
-        const bool row_ok = r_base + r < a.row1;
+        if (r_base + r >= a.row1) break;                     // warp-uniform; the bit tile is zeroed
         const float nr = na[r];
+        const float hi_r = 0.5f * 1.0012f * nr, lo_r = 0.5f * 0.9988f * nr;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const int col = q * 32 + lane;
-            const bool ok = row_ok && c_base + col < a.N;
-            const float nc = nb[col];
-            const float approx = nr + nc - 2.f * D[(size_t)r * kMD + col];
-            const float margin = nothing_decided ? 3e38f : 1.2e-3f * (nr + nc) + 1e-4f * a.cut + 1e-4f;
-            const bool yes = ok && approx < a.cut - margin;
-            const bool maybe = ok && !yes && approx <= a.cut + margin;
+            const float d = D[(size_t)r * kMD + q * 32 + lane];
+            const bool yes = col_ok[q] && !nothing_decided && d > hi_r + hi_c[q];
+            const bool maybe = col_ok[q] && !yes && (nothing_decided || !(d < lo_r + lo_c[q]));
             const unsigned word = __ballot_sync(0xffffffffu, yes);
             if (lane == 0) Wn[r * 4 + q] = word;
-            __syncwarp();
-            if (maybe) {
-                const int at = atomicAdd(nq, 1);
-                if (at < kMQ) queue[at] = ((uint32_t)r << 16) | (uint32_t)col;
-                else {
-                    // queue full (threshold in the middle of a dense cluster): decide here and now
-                    const float* x = a.xyz + (size_t)(r_base + r) * a.K;
-                    const float* y = a.xyz + (size_t)(c_base + col) * a.K;
-                    float s = 0.f;
-                    for (int k = 0; k < a.K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
-                    if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + q], 1u << lane);
+            if (__any_sync(0xffffffffu, maybe)) {
+                __syncwarp();
+                if (maybe) {
+                    const int col = q * 32 + lane;
+                    const int at = atomicAdd(nq, 1);
+                    if (at < kMQ) queue[at] = ((uint32_t)r << 16) | (uint32_t)col;
+                    else {
+                        // queue full (threshold in the middle of a dense cluster): decide here and now
+                        const float* x = a.xyz + (size_t)(r_base + r) * a.K;
+                        const float* y = a.xyz + (size_t)(c_base + col) * a.K;
+                        float s = 0.f;
+                        for (int k = 0; k < a.K; ++k) { const float dd = x[k] - y[k]; s = fmaf(dd, dd, s); }
+                        if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + q], 1u << lane);
+                    }
                 }
             }
         }
@@ -352,13 +374,21 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
         if (row < a.row1 && wc < a.words) a.bits[(size_t)(row - a.row0) * a.words + wc] = Wn[w];
     }
     if (mirror) {
-        for (int w = tid; w < kRT * 4; w += 256) {
-            const int cidx = w & 127, rw = w >> 7;
-            unsigned t = 0;
-#pragma unroll 8
-            for (int r = 0; r < 32; ++r) t |= ((Wn[(32 * rw + r) * 4 + (cidx >> 5)] >> (cidx & 31)) & 1u) << r;
-            const int mrow = c_base + cidx, wc = r_base / 32 + rw;
-            if (mrow < a.row1 && mrow < a.N && wc < a.words) a.bits[(size_t)(mrow - a.row0) * a.words + wc] = t;
+        // the tile transposed: sixteen 32 x 32 bit blocks, each turned by one warp with a five-step
+        // butterfly of shuffles (lane = row of the block in, column of the block out)
+        for (int blk = warp; blk < 16; blk += 8) {
+            const int rw = blk >> 2, q = blk & 3;
+            unsigned x = Wn[(32 * rw + lane) * 4 + q];
+#pragma unroll
+            for (int step = 0; step < 5; ++step) {
+                const int j = 16 >> step;
+                const unsigned m = step == 0 ? 0x0000ffffu : step == 1 ? 0x00ff00ffu : step == 2 ? 0x0f0f0f0fu
+                                 : step == 3 ? 0x33333333u : 0x55555555u;
+                const unsigned y = __shfl_xor_sync(0xffffffffu, x, j);
+                x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y & m) << j));
+            }
+            const int mrow = c_base + 32 * q + lane, wc = r_base / 32 + rw;
+            if (mrow < a.row1 && mrow < a.N && wc < a.words) a.bits[(size_t)(mrow - a.row0) * a.words + wc] = x;
         }
     }
 }
