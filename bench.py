@@ -161,7 +161,7 @@ def run_rmsd(args):
         return eng.rmsd_matrix(allc, row0=r0, row1=r1, threshold=2.5, values=False)[1]
 
     def step():
-        return parallel.sharded_rmsd_bits(rows, mine)
+        return parallel.sharded_rmsd_bits(rows, mine, counts=[b[r + 1] - b[r] for r in range(world)])
 
     for _ in range(max(3, args.warmup)):
         bits = step()

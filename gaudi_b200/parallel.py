@@ -49,30 +49,44 @@ def sharded_evaluate(evaluate_shard, alleles, n_out=2, device=None, group=None):
     return out
 
 
-def sharded_rmsd_bits(rmsd_rows, coords, group=None):
+def sharded_rmsd_bits(rmsd_rows, coords, group=None, counts=None):
     """Row-block sharded similarity bitmask.  ``coords``: this rank's (n_r, A, 3) float32 block
-    of conformers (blocks follow ``shard_bounds``); ``rmsd_rows(all_coords, row0, row1)`` returns
-    the (row1-row0, ceil(N/32)) int32 words for those rows.  Returns the full (N, words) tensor
-    on every rank."""
+    of conformers; ``rmsd_rows(all_coords, row0, row1)`` returns the (row1-row0, ceil(N/32)) int32
+    words for those rows.  ``counts``: conformers per rank when the caller knows them (blocks that
+    follow ``shard_bounds``); without it the ranks exchange their block sizes first, which costs a
+    host round trip per rank.  Returns the full (N, words) tensor on every rank."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     if world == 1:
         return rmsd_rows(coords, 0, coords.shape[0])
-    counts = [torch.zeros(1, dtype=torch.int64, device=coords.device) for _ in range(world)]
-    dist.all_gather(counts, torch.tensor([coords.shape[0]], dtype=torch.int64, device=coords.device), group=group)
-    counts = [int(c.item()) for c in counts]
+    if counts is None:
+        sizes = torch.zeros(world, dtype=torch.int64, device=coords.device)
+        dist.all_gather_into_tensor(sizes, torch.tensor([coords.shape[0]], dtype=torch.int64, device=coords.device),
+                                    group=group)
+        counts = sizes.tolist()                     # one device-to-host copy
+    counts = [int(c) for c in counts]
     m = max(counts)
-    padded = torch.zeros((m,) + tuple(coords.shape[1:]), dtype=coords.dtype, device=coords.device)
-    padded[:coords.shape[0]] = coords
+    even = min(counts) == m                         # equal blocks: gather in place, no padding, no re-packing
+    if even:
+        padded = coords.contiguous()
+    else:
+        padded = torch.zeros((m,) + tuple(coords.shape[1:]), dtype=coords.dtype, device=coords.device)
+        padded[:coords.shape[0]] = coords
     allc = torch.empty((world * m,) + tuple(coords.shape[1:]), dtype=coords.dtype, device=coords.device)
     dist.all_gather_into_tensor(allc, padded, group=group)
-    allc = torch.cat([allc[r * m:r * m + counts[r]] for r in range(world)])
+    if not even:
+        allc = torch.cat([allc[r * m:r * m + counts[r]] for r in range(world)])
     n = allc.shape[0]
     row0 = sum(counts[:rank])
     mine = rmsd_rows(allc, row0, row0 + counts[rank])
     words = (n + 31) // 32
-    pad = torch.zeros((m, words), dtype=mine.dtype, device=mine.device)
-    pad[:counts[rank]] = mine
+    if even:
+        pad = mine
+    else:
+        pad = torch.zeros((m, words), dtype=mine.dtype, device=mine.device)
+        pad[:counts[rank]] = mine
     allb = torch.empty((world * m, words), dtype=mine.dtype, device=mine.device)
     dist.all_gather_into_tensor(allb, pad, group=group)
+    if even:
+        return allb
     return torch.cat([allb[r * m:r * m + counts[r]] for r in range(world)])

@@ -276,6 +276,47 @@ def test_rmsd_matrix(small_system, torch_cuda):
     assert float(o.diagonal().abs().max()) == 0.0
 
 
+def test_similarity_bitmask_tensor_core_path_edges(small_system, torch_cuda):
+    """The tensor-core bitmask kernel decides most pairs from an fp16 product and re-decides the rest
+    exactly; the cases here push everything through the re-decision machinery: every pair at the
+    threshold (queue overflow), coordinates that do not fit fp16 (nothing pre-decided), identical
+    conformers, sizes that are multiples of nothing, few atoms (FP32 kernel)."""
+    from gaudi_b200.engine import Engine, bits_to_bool
+    lig, rec, params, eng = small_system
+    simt = Engine(lig, rec, M.ContactParams(rmsd_simt=True), device=0)
+    rng = np.random.default_rng(12)
+
+    def both(conf, thr):
+        conf = torch_cuda.as_tensor(np.ascontiguousarray(conf, np.float32)).cuda()
+        _, a = eng.rmsd_matrix(conf, threshold=thr, values=False)
+        _, b = simt.rmsd_matrix(conf, threshold=thr, values=False)
+        assert torch_cuda.equal(a, b)
+        return bits_to_bool(a, conf.shape[0])
+
+    base = rng.normal(scale=4.0, size=(1, 47, 3))
+    # every pair's RMSD within a few 1e-4 of the threshold: sqrt(2) * sigma * ... = 2.5
+    noise = rng.normal(size=(700, 47, 3))
+    noise *= 2.5 / np.sqrt(2.0) / np.sqrt((noise ** 2).sum(axis=(1, 2), keepdims=True) / 47)
+    sim = both(base + noise, 2.5)
+    frac = sim.mean()
+    assert 0.02 < frac < 0.98                       # genuinely undecided population, both outcomes occur
+    # far from the origin and spread over kilometres: the fp16 copy overflows, all pairs exact
+    far = base + rng.normal(scale=3.0e5, size=(300, 1, 3)) + rng.normal(scale=1.0, size=(300, 47, 3))
+    far[1] = far[0]
+    sim = both(far, 2.5)
+    assert sim[0, 1] and sim[1, 0] and sim.sum() < 300 * 300
+    # identical conformers: everything similar, including threshold 0 (rmsd == 0 is "not greater")
+    same = np.repeat(base, 130, axis=0)
+    assert both(same, 2.5).all() and both(same, 0.0).all()
+    # ragged: N = 1, N = 129 (one full tile + one row), A = 9 (K = 27), A = 3 (FP32 kernel)
+    for n, a_ in ((1, 20), (129, 9), (257, 33), (40, 3)):
+        conf = rng.normal(scale=2.0, size=(n, a_, 3))
+        sim = both(conf, 2.5)
+        ref = OA.rmsd_matrix(conf.astype(np.float32).astype(np.float64))
+        clear = np.abs(ref - 2.5) > 1e-4
+        assert np.array_equal(sim[clear], (ref <= 2.5)[clear])
+
+
 @pytest.mark.parametrize("n_lig, n_tors, n_rec, pop", [
     (1, 0, 7, 3),          # a single mobile atom, receptor smaller than one leaf
     (5, 0, 33, 5),         # just over one leaf

@@ -119,6 +119,14 @@ def _gloo_worker(rank, world, port, out):
                             axis=1, bitorder="little").view(np.uint32).astype(np.int64)
         return torch.as_tensor(words.astype(np.uint32).view(np.int32))
     bits = parallel.sharded_rmsd_bits(rows, torch.as_tensor(conf[b[rank]:b[rank + 1]]))
+    # block sizes known to the caller (no size exchange), and equal blocks (gathered in place)
+    known = parallel.sharded_rmsd_bits(rows, torch.as_tensor(conf[b[rank]:b[rank + 1]]),
+                                       counts=[b[r + 1] - b[r] for r in range(world)])
+    assert torch.equal(known, bits)
+    b8 = parallel.shard_bounds(8, world)
+    even = parallel.sharded_rmsd_bits(rows, torch.as_tensor(conf[:8][b8[rank]:b8[rank + 1]]),
+                                      counts=[b8[r + 1] - b8[r] for r in range(world)])
+    assert torch.equal(even, rows(torch.as_tensor(conf[:8]), 0, 8))
     if rank == 0:
         want = shard(tors, xf)
         ref = OA.rmsd_matrix(conf.astype(np.float64)) <= 2.5
