@@ -217,6 +217,27 @@ __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
 }
 
+// sum_k (x_k - y_k)^2 accumulated in k order with one FFMA per term: the very sequence of roundings
+// the FP32 kernel's accumulators go through, so the decision taken from it is that kernel's.
+__device__ __forceinline__ float exact_sum(const float* __restrict__ x, const float* __restrict__ y, int K, bool vec) {
+    float s = 0.f;
+    if (vec) {      // K a multiple of 4 and both rows 16-byte aligned: same order, a quarter of the loads
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const float4* y4 = reinterpret_cast<const float4*>(y);
+#pragma unroll 5
+        for (int k = 0; k < K / 4; ++k) {
+            const float4 p = x4[k], q = y4[k];
+            float d = p.x - q.x; s = fmaf(d, d, s);
+            d = p.y - q.y; s = fmaf(d, d, s);
+            d = p.z - q.z; s = fmaf(d, d, s);
+            d = p.w - q.w; s = fmaf(d, d, s);
+        }
+    } else {
+        for (int k = 0; k < K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
+    }
+    return s;
+}
+
 __global__ void __launch_bounds__(256, 2)
 rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
     using namespace nvcuda;
@@ -310,6 +331,7 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
             wmma::store_matrix_sync(D + (size_t)(wy * 64 + i * 16) * kMD + wx * 32 + j * 16, acc[i][j], kMD, wmma::mem_row_major);
     __syncthreads();
     const bool nothing_decided = *a.overflow != 0;
+    const bool vec = (a.K % 4 == 0) && (reinterpret_cast<uintptr_t>(a.xyz) % 16 == 0);
 
     // pass 1: decided pairs -> bits, undecided pairs -> queue.  Warp w takes rows 16 w .. 16 w + 15,
     // lanes take 32 consecutive columns: one ballot is one word of the bit tile.  With
@@ -348,8 +370,7 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
                         // queue full (threshold in the middle of a dense cluster): decide here and now
                         const float* x = a.xyz + (size_t)(r_base + r) * a.K;
                         const float* y = a.xyz + (size_t)(c_base + col) * a.K;
-                        float s = 0.f;
-                        for (int k = 0; k < a.K; ++k) { const float dd = x[k] - y[k]; s = fmaf(dd, dd, s); }
+                        const float s = exact_sum(x, y, a.K, vec);
                         if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + q], 1u << lane);
                     }
                 }
@@ -363,8 +384,7 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
         const int r = queue[e] >> 16, col = queue[e] & 0xffff;
         const float* x = a.xyz + (size_t)(r_base + r) * a.K;
         const float* y = a.xyz + (size_t)(c_base + col) * a.K;
-        float s = 0.f;
-        for (int k = 0; k < a.K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
+        const float s = exact_sum(x, y, a.K, vec);
         // similarity.py:67-69: "if rmsd_squared > threshold*threshold: return False"
         if (!(s * a.inv_a > a.thr2)) atomicOr(&Wn[r * 4 + (col >> 5)], 1u << (col & 31));
     }
