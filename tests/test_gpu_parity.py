@@ -84,6 +84,23 @@ def test_express_tree_form_and_sequential_agree(small_system, torch_cuda):
         assert np.abs(OA.express(odd, tors[p], xf[p]) - got[p]).max() < XYZ_TOL
 
 
+@pytest.mark.parametrize("n_atoms, n_tors, tree", [(120, 40, True), (200, 70, False)])
+def test_express_many_torsions(torch_cuda, n_atoms, n_tors, tree):
+    """More than 32 bonds (two rounds of per-lane bond maps, 64-bit bond masks) and more than 64
+    (past what the tree form holds: sequential kernel)."""
+    from gaudi_b200.engine import Engine
+    lig = synth.make_ligand(n_atoms, n_tors, seed=9)
+    assert lig.n_allele_torsions == n_tors
+    eng = Engine(lig, M.empty_receptor(), M.ContactParams(only_internal=True), device=0)
+    assert eng.express_is_tree() == tree
+    tors, xf = synth.make_alleles(40, n_tors, seed=4)
+    tors[3] = 0.0                                    # an individual with every bond at rest
+    tors[5, ::2] = 0.0                               # and one with every other bond at rest
+    xyz = eng.express(tors, xf).cpu().numpy().astype(np.float64) + eng.centre
+    for p in range(0, 40, 3):
+        assert np.abs(OA.express(lig, tors[p], xf[p]) - xyz[p]).max() < XYZ_TOL
+
+
 def test_express_identity(small_system):
     lig, rec, params, eng = small_system
     tors = np.zeros((3, lig.n_allele_torsions))
