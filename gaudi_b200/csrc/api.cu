@@ -14,7 +14,7 @@
 namespace gmm {
 
 static thread_local char g_err[512] = "";
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -75,7 +75,7 @@ extern "C" {
 
 const char* gmm_last_error(void) { return gmm::g_err; }
 int gmm_version(void) { return 100; }
-unsigned long long gmm_launch_count(void) { return gmm::g_launches; }
+unsigned long long gmm_launch_count(void) { return gmm::g_launches.load(); }
 
 int gmm_create(gmm_ctx** out, int device) {
     REQUIRE(out != nullptr, GMM_EINVAL, "gmm_create: out is NULL");

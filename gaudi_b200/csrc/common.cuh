@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -11,7 +12,7 @@ namespace gmm {
 
 // ---- error handling ---------------------------------------------------------------
 void set_error(const char* fmt, ...);
-extern unsigned long long g_launches;
+extern std::atomic<unsigned long long> g_launches;   // kernels launched by this library (any thread)
 
 #define GMM_CUDA(call)                                                              \
     do {                                                                            \

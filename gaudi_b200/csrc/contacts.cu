@@ -573,16 +573,23 @@ int launch_pairs_dump(gmm_ctx* c, const float* xyz_one, int max_pairs, int32_t* 
     d.mm_pairs = c->d_mm_pairs; d.n_mm = c->n_mm;
     d.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; d.rr_idx = c->d_rr_idx;
     d.R = c->R; d.max_pairs = max_pairs;
-    int32_t* d_s2o = nullptr; uint32_t* d_zone = nullptr;
-    int32_t* d_pairs = nullptr; int32_t* d_kind = nullptr; double* d_ov = nullptr; double* d_val = nullptr; int* d_n = nullptr;
+    // temporaries of this diagnostic call; freed on every path out of the function
+    struct Scratch {
+        void* p[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        ~Scratch() { for (void* q : p) if (q) cudaFree(q); }
+    } tmp;
     const size_t zw = (size_t)(c->n_tiles * 4 + 1);
-    GMM_CUDA(cudaMalloc(&d_s2o, sizeof(int32_t) * (c->R + 1)));
-    GMM_CUDA(cudaMalloc(&d_zone, sizeof(uint32_t) * zw));
-    GMM_CUDA(cudaMalloc(&d_pairs, sizeof(int32_t) * 2 * (max_pairs + 1)));
-    GMM_CUDA(cudaMalloc(&d_kind, sizeof(int32_t) * (max_pairs + 1)));
-    GMM_CUDA(cudaMalloc(&d_ov, sizeof(double) * (max_pairs + 1)));
-    GMM_CUDA(cudaMalloc(&d_val, sizeof(double) * (max_pairs + 1)));
-    GMM_CUDA(cudaMalloc(&d_n, sizeof(int)));
+    GMM_CUDA(cudaMalloc(&tmp.p[0], sizeof(int32_t) * (c->R + 1)));
+    GMM_CUDA(cudaMalloc(&tmp.p[1], sizeof(uint32_t) * zw));
+    GMM_CUDA(cudaMalloc(&tmp.p[2], sizeof(int32_t) * 2 * (max_pairs + 1)));
+    GMM_CUDA(cudaMalloc(&tmp.p[3], sizeof(int32_t) * (max_pairs + 1)));
+    GMM_CUDA(cudaMalloc(&tmp.p[4], sizeof(double) * (max_pairs + 1)));
+    GMM_CUDA(cudaMalloc(&tmp.p[5], sizeof(double) * (max_pairs + 1)));
+    GMM_CUDA(cudaMalloc(&tmp.p[6], sizeof(int)));
+    int32_t* d_s2o = static_cast<int32_t*>(tmp.p[0]); uint32_t* d_zone = static_cast<uint32_t*>(tmp.p[1]);
+    int32_t* d_pairs = static_cast<int32_t*>(tmp.p[2]); int32_t* d_kind = static_cast<int32_t*>(tmp.p[3]);
+    double* d_ov = static_cast<double*>(tmp.p[4]); double* d_val = static_cast<double*>(tmp.p[5]);
+    int* d_n = static_cast<int*>(tmp.p[6]);
     GMM_CUDA(cudaMemsetAsync(d_n, 0, sizeof(int), s));
     if (c->R) GMM_CUDA(cudaMemcpyAsync(d_s2o, c->h_sorted2orig.data(), sizeof(int32_t) * c->R, cudaMemcpyHostToDevice, s));
     d.sorted2orig = d_s2o; d.zone_tmp = d_zone;
@@ -601,7 +608,6 @@ int launch_pairs_dump(gmm_ctx* c, const float* xyz_one, int max_pairs, int32_t* 
         GMM_CUDA(cudaMemcpy(val_h, d_val, sizeof(double) * w, cudaMemcpyDeviceToHost));
     }
     *n_out = n;
-    cudaFree(d_s2o); cudaFree(d_zone); cudaFree(d_pairs); cudaFree(d_kind); cudaFree(d_ov); cudaFree(d_val); cudaFree(d_n);
     return GMM_OK;
 }
 
