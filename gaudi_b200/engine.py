@@ -194,6 +194,22 @@ class Engine(object):
             _lib.check(rc)
         return bool(rc)
 
+    def nondominated_fronts(self, w):
+        """Front index (0 = non-dominated) of every row of ``w`` (N, M) weighted fitness values,
+        larger is better; equal rows share a front (``gmm_nondominated_fronts``).  numpy in, numpy out."""
+        w = np.ascontiguousarray(w, np.float64)
+        n, m = w.shape
+        if n == 0:
+            return np.zeros(0, np.int64)
+        order = np.lexsort(tuple(-w[:, c] for c in range(m - 1, -1, -1)))     # descending, column 0 first
+        ws = torch.as_tensor(w[order]).to(self.torch_device)
+        front = torch.empty(n, dtype=torch.int32, device=self.torch_device)
+        _lib.check(self._L.gmm_nondominated_fronts(self._h, int(n), int(m), _dev_ptr(ws), _dev_ptr(front),
+                                                   self._stream()))
+        out = np.empty(n, np.int64)
+        out[order] = front.cpu().numpy()
+        return out
+
     def similar_lists(self, bits, n, row0=0):
         """Partner lists of a similarity bitmask from ``rmsd_matrix`` (rows ``row0 ...`` of the
         ``n x n`` matrix): ``(ptr int64 (rows + 1,), idx int32)`` host arrays, self excluded."""

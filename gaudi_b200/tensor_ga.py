@@ -34,10 +34,23 @@ def _first_below(neg_best, y):
     return bisect_right(neg_best, -y)
 
 
+_fronts_backend = None      # set by launch(): Engine.nondominated_fronts (GPU) for three or more objectives
+
+
+def set_fronts_backend(fn):
+    """``fn(w) -> fronts`` used for more than two objectives (``gmm_nondominated_fronts`` through an
+    Engine); ``None`` restores the host restatement (O(N^2) numpy, small populations only)."""
+    global _fronts_backend
+    _fronts_backend = fn
+
+
 def nondominated_fronts(w):
     """Front index of every row of ``w`` (N, M) under maximisation of each column (``wvalues``).
-    Equal rows share a front, as in DEAP's sortNondominated (which groups by fitness)."""
+    Equal rows share a front, as in DEAP's sortNondominated (which groups by fitness).  Two
+    objectives: O(N log N) on the host.  More: the GPU sort when a backend is set."""
     n = w.shape[0]
+    if w.shape[1] != 2 and _fronts_backend is not None and n > 256:
+        return np.asarray(_fronts_backend(w), dtype=np.int64)
     front = np.full(n, -1, dtype=np.int64)
     # work on unique fitness rows
     uniq, inv = np.unique(w, axis=0, return_inverse=True)
@@ -456,6 +469,7 @@ def launch(cfg, device=0, seed=None):
         _, bits = eng.rmsd_matrix(coords, threshold=threshold, values=False)
         return eng.similar_lists(bits, len(coords))
 
+    set_fronts_backend(batch.engines[0][0].nondominated_fronts)
     ga = TensorGA(spec, cfg.weights, evaluate, similarity, threshold=cfg.similarity.args[1], seed=seed)
     n = cfg.ga.population
     pop = ga.random_population(n)

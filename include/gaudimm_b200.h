@@ -190,6 +190,13 @@ int gmm_express_is_tree(gmm_ctx* ctx);
 int gmm_similar_lists(gmm_ctx* ctx, int N, int row0, int row1, const uint32_t* bits_d, int32_t* counts_d,
                       const int64_t* ptr_d, int32_t* idx_d, void* stream);
 
+/* Non-dominated sorting for the selection step (gaudi/algorithms.py:160 -> DEAP selNSGA2 ->
+ * sortNondominated).  w_sorted_d: [n, m] fp64 weighted fitness values (larger is better in every
+ * column, DEAP's wvalues), rows sorted lexicographically in DESCENDING order (checked; GMM_EINVAL
+ * otherwise), m <= 8.  front_d[i] = index of the front row i belongs to (0 = non-dominated);
+ * equal rows share a front.  Synchronises the stream once (the order check). */
+int gmm_nondominated_fronts(gmm_ctx* ctx, int n, int m, const double* w_sorted_d, int32_t* front_d, void* stream);
+
 /* HOST function: the greedy pass of gaudi/algorithms.py:139-155 over HOST partner lists
  * (ptr_h int64 [N+1], idx_h int32) and the candidates' lexicographic fitness ranks (rank_h,
  * larger = fitter, as ``i.fitness <= n_i.fitness`` compares wvalues): visit candidates in order;

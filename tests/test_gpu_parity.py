@@ -293,6 +293,41 @@ def test_rmsd_matrix(small_system, torch_cuda):
     assert float(o.diagonal().abs().max()) == 0.0
 
 
+def test_nondominated_fronts_on_device(small_system, torch_cuda):
+    """gmm_nondominated_fronts against the definition (peel the non-dominated layer, repeat) for
+    2-5 objectives with plenty of ties and duplicates, and against the O(N log N) two-objective
+    host sort at a size where peeling is out of reach."""
+    from gaudi_b200 import tensor_ga as TG, _lib
+    lig, rec, params, eng = small_system
+    rng = np.random.default_rng(21)
+
+    def peel(w):
+        level = np.full(len(w), -1)
+        rem, lv = np.arange(len(w)), 0
+        while len(rem):
+            sub = w[rem]
+            dom = np.zeros(len(sub), bool)
+            for s0 in range(0, len(sub), 256):
+                blk = sub[s0:s0 + 256]
+                dom[s0:s0 + 256] = ((sub[None] >= blk[:, None]).all(2) & (sub[None] > blk[:, None]).any(2)).any(1)
+            level[rem[~dom]] = lv
+            rem, lv = rem[dom], lv + 1
+        return level
+
+    for n, m in ((1, 3), (2, 2), (511, 3), (512, 4), (513, 3), (1700, 3), (1300, 5), (900, 1)):
+        w = np.round(rng.normal(size=(n, m)), 1)              # one decimal: ties in every column
+        w[n // 2:n // 2 + 5] = w[0]                            # exact duplicates of one row
+        assert np.array_equal(eng.nondominated_fronts(w), peel(w)), (n, m)
+    w = np.round(np.stack([rng.exponential(50, 70000), -rng.exponential(30, 70000)], 1), 3)
+    assert np.array_equal(eng.nondominated_fronts(w), TG.nondominated_fronts(w))
+    # rows that are not sorted are refused, not mis-sorted
+    bad = torch_cuda.as_tensor(np.array([[0.0, 1.0], [1.0, 0.0], [0.5, 0.5]])).cuda()
+    out = torch_cuda.empty(3, dtype=torch_cuda.int32, device="cuda")
+    import ctypes as C
+    rc = eng._L.gmm_nondominated_fronts(eng._h, 3, 2, C.c_void_p(bad.data_ptr()), C.c_void_p(out.data_ptr()), None)
+    assert rc == _lib.GMM_EINVAL
+
+
 def test_similarity_bitmask_tensor_core_path_edges(small_system, torch_cuda):
     """The tensor-core bitmask kernel decides most pairs from an fp16 product and re-decides the rest
     exactly; the cases here push everything through the re-decision machinery: every pair at the
