@@ -57,6 +57,7 @@ nds_block_kernel(int b0, int nb, const double* __restrict__ w, int32_t* __restri
     for (int q = 0; q < kNdsBlock / 32; ++q) {
         uint32_t word = 0u;
         if (t < nb && (q << 5) + 31 > t) {
+#pragma unroll 1
             for (int bit = 0; bit < 32; ++bit) {
                 const int i = (q << 5) + bit;
                 if (i > t && i < nb && dominates<M>(mine, &sw[i * M])) word |= 1u << bit;
@@ -68,6 +69,7 @@ nds_block_kernel(int b0, int nb, const double* __restrict__ w, int32_t* __restri
 #pragma unroll
     for (int q = 0; q < kNdsBlock / 32; ++q) {
         if ((q << 5) >= nb) break;
+#pragma unroll 1
         for (int bit = 0; bit < 32; ++bit) {
             const int s = (q << 5) + bit;
             if (s >= nb) break;

@@ -461,6 +461,10 @@ def launch(cfg, device=0, seed=None):
                 xyz = coords
             for i, col in members:
                 out[:, i] = py_round(scores[:, col], objectives[i].precision)
+        if batch.geometry:                                   # Distance / Angle restraints (gmm_geometry)
+            geo = batch.engines[0][0].geometry(xyz).cpu().numpy()
+            for col, (i, o) in enumerate(batch.geometry):
+                out[:, i] = py_round(geo[:, col], o.precision)
         return out, np.ascontiguousarray(xyz[:, batch.lig_slice])
 
     def similarity(coords, threshold):

@@ -120,3 +120,47 @@ def test_distance_and_angle_plugins(built_lib):
                                                             weight=-1.0), abs=2e-3)
         assert got[3] == pytest.approx(O.angle_objective([x[r] for r in rows], "planar"), abs=2e-3)
     assert len(batch.engines) == 1
+
+
+@pytest.mark.gpu
+def test_three_objective_array_ga(built_lib):
+    """Clashes + Contacts + Distance through the array GA: the restraint column comes from
+    gmm_geometry, selection from the device non-dominated sort (three objectives)."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from gaudi_b200 import parse, tensor_ga
+    prot, lig = G.load("5er1_protein_mol2"), G.load("5er1_ligand_mol2")
+    s_lig, s_prot = int(lig.serial[0]), int(prot.serial[100])
+    cfg = parse.Settings({
+        "output": {"verbose": False, "precision": 3},
+        "ga": {"population": 600, "generations": 2, "mu": 1.0, "lambda_": 1.0},
+        "genes": [
+            {"name": "Protein", "module": "gaudi_b200.genes.molecule", "path": "p.mol2", "mol": prot},
+            {"name": "Ligand", "module": "gaudi_b200.genes.molecule", "path": "l.mol2", "mol": lig},
+            {"name": "Torsion", "module": "gaudi_b200.genes.torsion", "target": "Ligand", "flexibility": 360},
+            {"name": "Search", "module": "gaudi_b200.genes.search", "target": "Ligand/1", "radius": 3.0, "rotate": True},
+        ],
+        "objectives": [
+            {"name": "Clashes", "module": "gaudi_b200.objectives.contacts", "which": "clashes",
+             "probes": ["Ligand"], "radius": 5.0, "weight": -1.0},
+            {"name": "Contacts", "module": "gaudi_b200.objectives.contacts", "which": "hydrophobic",
+             "probes": ["Ligand"], "radius": 5.0, "weight": -1.0},
+            {"name": "Dist", "module": "gaudi_b200.objectives.distance", "probes": [["Ligand", s_lig]],
+             "target": ["Protein", s_prot], "threshold": 3.0, "weight": -1.0},
+        ],
+        "similarity": {"module": "gaudi_b200.similarity.rmsd", "args": [["Ligand"], 2.5], "kwargs": {}},
+    })
+    pop, log, batch = tensor_ga.launch(cfg, seed=11)
+    fit = pop["fitness"]
+    assert fit.shape == (600, 3) and np.isfinite(fit).all()
+    row = int(np.flatnonzero(lig.serial == s_lig)[0])
+    world = pop["coords"].astype(np.float64) + batch.centre
+    for p in range(0, 600, 37):
+        want = O.distance_objective(world[p, [row]], prot.xyz[100], 3.0)
+        assert fit[p, 2] == pytest.approx(want, abs=2e-3)
+    # the selected population starts with the non-dominated front of what it was selected from
+    w = fit * np.array([-1.0, -1.0, -1.0])
+    fronts = batch.engines[0][0].nondominated_fronts(w)
+    assert (fronts == 0).sum() >= 1 and fronts.max() >= 1
+    tensor_ga.set_fronts_backend(None)
