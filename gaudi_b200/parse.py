@@ -31,6 +31,30 @@ DEFAULTS = {
 }
 
 
+# A job written for the reference names its plugins ``gaudi.genes.torsion`` etc.  The ones that have a
+# B200 mirror are redirected; anything else of the reference's is refused by name, so that a job
+# never silently runs with a gene or objective missing.
+B200_MODULES = {
+    "gaudi.genes.molecule": "gaudi_b200.genes.molecule",
+    "gaudi.genes.torsion": "gaudi_b200.genes.torsion",
+    "gaudi.genes.search": "gaudi_b200.genes.search",
+    "gaudi.genes.rotamers": "gaudi_b200.genes.rotamers",
+    "gaudi.objectives.contacts": "gaudi_b200.objectives.contacts",
+    "gaudi.objectives.distance": "gaudi_b200.objectives.distance",
+    "gaudi.objectives.angle": "gaudi_b200.objectives.angle",
+    "gaudi.similarity.rmsd": "gaudi_b200.similarity.rmsd",
+}
+
+
+def b200_module(name):
+    """Module path on the B200 path for a plugin named in a reference job file."""
+    if name in B200_MODULES:
+        return B200_MODULES[name]
+    if name.startswith("gaudi."):
+        raise NotImplementedError("%s has no B200 counterpart (available: %s)" % (name, ", ".join(sorted(B200_MODULES))))
+    return name
+
+
 class Settings(Param):
     def __init__(self, source=None, **kw):
         Param.__init__(self)
@@ -60,6 +84,9 @@ class Settings(Param):
                 g["path"] = os.path.normpath(os.path.join(base, g["path"]))
         for o in self["objectives"]:
             o.setdefault("weight", -1.0)
+        for plugin in self["genes"] + self["objectives"]:
+            plugin["module"] = b200_module(plugin["module"])
+        self["similarity"]["module"] = b200_module(self["similarity"]["module"])
 
     @property
     def weights(self):

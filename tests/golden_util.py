@@ -35,3 +35,17 @@ def ligand_3pk2():
     ty = dict(zip(lm.name, lm.sybyl))
     lp.sybyl = [ty.get(n, lp.element[i].title()) for i, n in enumerate(lp.name)]
     return lp
+
+
+def write_mol2(mol, path):
+    """A minimal Tripos mol2 of a fixture molecule (what gaudi_b200.molio.read_mol2 reads back):
+    lets the tests hand the plugin layer real files, as a job file would."""
+    with open(path, "w") as fh:
+        fh.write("@<TRIPOS>MOLECULE\nfixture\n%d %d 1\nSMALL\nNO_CHARGES\n\n@<TRIPOS>ATOM\n" % (mol.n_atoms, len(mol.bonds)))
+        for i in range(mol.n_atoms):
+            fh.write("%7d %-8s %12.6f %12.6f %12.6f %-6s %5d %s%d 0.0000\n" % (
+                int(mol.serial[i]), mol.name[i], mol.xyz[i, 0], mol.xyz[i, 1], mol.xyz[i, 2], mol.sybyl[i],
+                int(mol.resseq[i]), mol.resname[i], int(mol.resseq[i])))
+        fh.write("@<TRIPOS>BOND\n")
+        for k, (a, b) in enumerate(mol.bonds):
+            fh.write("%6d %6d %6d 1\n" % (k + 1, int(mol.serial[a]), int(mol.serial[b])))

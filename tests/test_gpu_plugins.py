@@ -196,3 +196,34 @@ def test_expressed_coordinates_of_every_molecule(cuda):
     assert any((np.abs(i.find_molecule("Protein")._expressed_coordinates - prot.xyz) > 1e-4).any() for i in pop)
     assert similarity.rmsd(pop[0], pop[0], ["Ligand", "Protein"], 0.5)
     assert pop[0].similar(pop[0])
+
+
+def test_reference_yaml_job_runs(cuda, tmp_path):
+    """A YAML job with the reference's own module names and structure files on disk, run through
+    ``algorithms.launch``: the drop-in the plugin API promises."""
+    from gaudi_b200 import algorithms
+    G.write_mol2(G.load("5er1_protein_mol2"), str(tmp_path / "protein.mol2"))
+    G.write_mol2(G.load("5er1_ligand_mol2"), str(tmp_path / "ligand.mol2"))
+    job = tmp_path / "job.yaml"
+    job.write_text("""
+output: {verbose: false, precision: 3}
+ga: {population: 30, generations: 2, mu: 1.0, lambda_: 1.0}
+similarity: {module: gaudi.similarity.rmsd, args: [[Ligand], 2.5], kwargs: {}}
+genes:
+  - {name: Protein, module: gaudi.genes.molecule, path: protein.mol2}
+  - {name: Ligand, module: gaudi.genes.molecule, path: ligand.mol2}
+  - {name: Torsion, module: gaudi.genes.torsion, target: Ligand, flexibility: 360}
+  - {name: Search, module: gaudi.genes.search, target: Ligand/1, radius: 3.0, rotate: true}
+objectives:
+  - {name: Clashes, module: gaudi.objectives.contacts, which: clashes, probes: [Ligand], radius: 5.0, weight: -1.0}
+  - {name: Contacts, module: gaudi.objectives.contacts, which: hydrophobic, probes: [Ligand], radius: 5.0, weight: -1.0}
+""")
+    cfg = parse.Settings(str(job))
+    pop, log, elite = algorithms.launch(cfg, seed=3)
+    assert len(pop) == 30 and len(log) == 3 and all(ind.fitness.valid for ind in pop)
+    batch = cfg._environment.batch
+    for ind in pop[::7]:
+        res, xyz = oracle_scores(batch, ind)
+        got = ind.fitness.values
+        assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash)
+        assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro)

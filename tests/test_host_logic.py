@@ -237,3 +237,33 @@ def test_tensor_variation_properties():
     r = TG.random_rotations(50, np.random.default_rng(0))
     assert np.allclose(TG.slerp(r, r, 0.3), r, atol=1e-9)
     assert np.allclose(TG.quat_to_matrix(TG.matrix_to_quat(r)), r, atol=1e-9)
+
+
+def test_reference_job_file_is_redirected(tmp_path):
+    """A job file written for the reference (``module: gaudi.genes.torsion`` ...) resolves to the
+    B200 mirrors; plugins without a mirror are refused by name."""
+    from gaudi_b200 import parse
+    job = tmp_path / "job.yaml"
+    job.write_text("""
+ga: {population: 12, generations: 1}
+similarity: {module: gaudi.similarity.rmsd, args: [[Ligand], 2.5], kwargs: {}}
+genes:
+  - {name: Protein, module: gaudi.genes.molecule, path: p.mol2}
+  - {name: Ligand, module: gaudi.genes.molecule, path: sub/l.mol2}
+  - {name: Torsion, module: gaudi.genes.torsion, target: Ligand, flexibility: 360}
+  - {name: Search, module: gaudi.genes.search, target: Ligand/1, radius: 3.0, rotate: true}
+objectives:
+  - {name: Clashes, module: gaudi.objectives.contacts, which: clashes, probes: [Ligand], radius: 5.0, weight: -1.0}
+  - {name: Near, module: gaudi.objectives.distance, probes: [Ligand/1], target: Protein/2, threshold: 3.0, weight: -1.0}
+""")
+    cfg = parse.Settings(str(job))
+    assert [g.module for g in cfg.genes] == ["gaudi_b200.genes.molecule"] * 2 + ["gaudi_b200.genes.torsion",
+                                                                                  "gaudi_b200.genes.search"]
+    assert [o.module for o in cfg.objectives] == ["gaudi_b200.objectives.contacts", "gaudi_b200.objectives.distance"]
+    assert cfg.similarity.module == "gaudi_b200.similarity.rmsd"
+    assert cfg.genes[1].path == str(tmp_path / "sub" / "l.mol2")          # relative to the job file
+    assert cfg.ga.mu == 1 and cfg.ga.cx_eta == 5                           # reference defaults (parse.py:254-284)
+    bad = tmp_path / "bad.yaml"
+    bad.write_text("genes:\n  - {name: M, module: gaudi.genes.mutamers, residues: [Protein/1]}\n")
+    with pytest.raises(NotImplementedError, match="gaudi.genes.mutamers"):
+        parse.Settings(str(bad))
