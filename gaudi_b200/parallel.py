@@ -7,7 +7,6 @@ Works with the ``nccl`` backend on GPUs and with ``gloo`` on CPU tensors (used b
 world-size-2 tests, where the per-shard compute is supplied by the test)."""
 from __future__ import annotations
 
-import numpy as np
 import torch
 import torch.distributed as dist
 

@@ -427,7 +427,6 @@ def launch(cfg, device=0, seed=None):
     per-individual Python objects.  Returns ``(population dict, logbook, BatchEvaluator)``."""
     import random
     from . import base, plugin
-    from .engine import bits_to_bool
     if seed is not None:
         random.seed(seed)
     plugin.import_plugins(*cfg.genes)

@@ -24,7 +24,6 @@ fixes its semantics.
 from __future__ import annotations
 
 import math
-from collections import deque
 
 import numpy as np
 
