@@ -620,7 +620,8 @@ int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const doub
         constexpr int kChunks = 2;
         if (!c->copy_stream) {
             GMM_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-            for (int k = 0; k <= kChunks; ++k) GMM_CUDA(cudaEventCreateWithFlags(&c->ev_copy[k], cudaEventDisableTiming));
+            for (int k = 0; k <= kChunks; ++k)
+                if (!c->ev_copy[k]) GMM_CUDA(cudaEventCreateWithFlags(&c->ev_copy[k], cudaEventDisableTiming));
         }
         if ((rc = ensure_scratch(c, contacts_scratch_bytes(c, P)))) return rc;   // before anything is queued
         GMM_CUDA(cudaEventRecord(c->ev_copy[kChunks], s));
@@ -653,24 +654,54 @@ int gmm_evaluate_host(gmm_ctx* c, int P, const double* torsion_deg_h, const doub
         GMM_CUDA(cudaStreamSynchronize(s));
         return GMM_OK;
     }
-    if ((rc = h2d(o_t, torsion_deg_h, nt))) return rc;
-    if ((rc = h2d(o_x, xform_h, nx))) return rc;
-    if ((rc = h2d(o_r, rot_allele_h, nr))) return rc;
-    rc = gmm_evaluate(c, P, nt ? (const double*)(dp + o_t) : nullptr, nx ? (const double*)(dp + o_x) : nullptr,
-                      nr ? (const double*)(dp + o_r) : nullptr, nxyz ? (float*)(dp + o_xyz) : nullptr,
-                      (double*)(dp + o_s), (int32_t*)(dp + o_c), stream);
-    if (rc) return rc;
-    struct Out { void* dst; size_t off, n; bool direct; };
-    Out outs[3] = {{out_scores_h, o_s, ns, false}, {out_counts_h, o_c, out_counts_h ? nc : 0, false},
-                   {out_xyz_h, o_xyz, nxyz, false}};
-    for (auto& o : outs) {
-        if (!o.n) continue;
-        o.direct = pinned(o.dst);
-        GMM_CUDA(cudaMemcpyAsync(o.direct ? o.dst : (void*)(hp + o.off), dp + o.off, o.n, cudaMemcpyDeviceToHost, s));
+    // General path (some buffer is pageable, or the population is small).  Large populations go in
+    // four equal chunks: while the GPU works on chunk k the host is already copying chunk k + 1's
+    // pageable rows into the pinned staging area, and chunk k - 1's results out of it — the host
+    // memcpy of 11.5 MB of alleles costs about as much as the kernels, so hiding it matters.
+    const int n_chunks = (P >= 32768) ? 4 : 1;
+    if ((rc = ensure_scratch(c, contacts_scratch_bytes(c, P)))) return rc;       // before anything is queued
+    if (n_chunks > 1)
+        for (int k = 0; k < n_chunks; ++k)
+            if (!c->ev_copy[k]) GMM_CUDA(cudaEventCreateWithFlags(&c->ev_copy[k], cudaEventDisableTiming));
+    const size_t st = (size_t)c->n_allele_tors * sizeof(double), sx = nx ? 12 * sizeof(double) : 0,
+                 sr = nr ? (size_t)c->n_res * sizeof(double) : 0, sxyz = nxyz ? (size_t)c->M * 3 * sizeof(float) : 0;
+    const bool scores_direct = pinned(out_scores_h), counts_direct = out_counts_h && pinned(out_counts_h),
+               xyz_direct = out_xyz_h && pinned(out_xyz_h);
+    int bounds[5];
+    for (int k = 0; k <= n_chunks; ++k) bounds[k] = (int)(((long long)P * k / n_chunks) & ~3LL);
+    bounds[n_chunks] = P;
+    for (int k = 0; k < n_chunks; ++k) {
+        const size_t a0 = bounds[k], n = bounds[k + 1] - bounds[k];
+        if (n == 0) continue;
+        if (nt && (rc = h2d(o_t + a0 * st, (const char*)torsion_deg_h + a0 * st, n * st))) return rc;
+        if (nx && (rc = h2d(o_x + a0 * sx, (const char*)xform_h + a0 * sx, n * sx))) return rc;
+        if (nr && (rc = h2d(o_r + a0 * sr, (const char*)rot_allele_h + a0 * sr, n * sr))) return rc;
+        rc = gmm_evaluate(c, (int)n, nt ? (const double*)(dp + o_t + a0 * st) : nullptr,
+                          nx ? (const double*)(dp + o_x + a0 * sx) : nullptr,
+                          nr ? (const double*)(dp + o_r + a0 * sr) : nullptr,
+                          nxyz ? (float*)(dp + o_xyz + a0 * sxyz) : nullptr,
+                          (double*)(dp + o_s) + 2 * a0, (int32_t*)(dp + o_c) + 2 * a0, stream);
+        if (rc) return rc;
+        const size_t os = o_s + a0 * 2 * sizeof(double), oc = o_c + a0 * 2 * sizeof(int32_t), ox = o_xyz + a0 * sxyz;
+        GMM_CUDA(cudaMemcpyAsync(scores_direct ? (void*)(out_scores_h + 2 * a0) : (void*)(hp + os), dp + os,
+                                 n * 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (out_counts_h)
+            GMM_CUDA(cudaMemcpyAsync(counts_direct ? (void*)(out_counts_h + 2 * a0) : (void*)(hp + oc), dp + oc,
+                                     n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+        if (nxyz)
+            GMM_CUDA(cudaMemcpyAsync(xyz_direct ? (void*)((char*)out_xyz_h + a0 * sxyz) : (void*)(hp + ox), dp + ox,
+                                     n * sxyz, cudaMemcpyDeviceToHost, s));
+        if (n_chunks > 1) GMM_CUDA(cudaEventRecord(c->ev_copy[k], s));
     }
-    GMM_CUDA(cudaStreamSynchronize(s));
-    for (auto& o : outs)
-        if (o.n && !o.direct) memcpy(o.dst, hp + o.off, o.n);
+    for (int k = 0; k < n_chunks; ++k) {
+        const size_t a0 = bounds[k], n = bounds[k + 1] - bounds[k];
+        if (n == 0) continue;
+        if (n_chunks > 1) GMM_CUDA(cudaEventSynchronize(c->ev_copy[k]));
+        else GMM_CUDA(cudaStreamSynchronize(s));
+        if (!scores_direct) memcpy(out_scores_h + 2 * a0, hp + o_s + a0 * 2 * sizeof(double), n * 2 * sizeof(double));
+        if (out_counts_h && !counts_direct) memcpy(out_counts_h + 2 * a0, hp + o_c + a0 * 2 * sizeof(int32_t), n * 2 * sizeof(int32_t));
+        if (nxyz && !xyz_direct) memcpy((char*)out_xyz_h + a0 * sxyz, hp + o_xyz + a0 * sxyz, n * sxyz);
+    }
     return GMM_OK;
 }
 
