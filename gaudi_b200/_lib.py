@@ -39,6 +39,7 @@ SIGNATURES = {
     "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),
     "gmm_similar_lists": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "gmm_niching_host": (_i, [_i, _vp, _vp, _vp, _vp]),
+    "gmm_fronts2_host": (_i, [_i, _vp, _vp]),
     "gmm_nondominated_fronts": (_i, [_vp, _i, _i, _vp, _vp, _vp]),
     "gmm_contacts_pairs": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, C.POINTER(_i), _vp]),
     "gmm_measure_fp32_peak": (_i, [_i, C.POINTER(_d)]),

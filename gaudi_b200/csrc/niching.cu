@@ -107,3 +107,33 @@ extern "C" int gmm_niching_host(int N, const int64_t* ptr_h, const int32_t* idx_
     }
     return GMM_OK;
 }
+
+// Host: fronts of TWO-objective rows sorted best first (column 0 descending, ties column 1
+// descending): every dominator of a row stands before it, front f remembers the largest second
+// objective it holds (non-increasing in f), and a row joins the first front whose best is strictly
+// below its own second objective (binary search): O(N log N), the host-side counterpart of
+// gmm_nondominated_fronts for the common two-objective job.  Equal rows share a front.
+extern "C" int gmm_fronts2_host(int N, const double* w_sorted_h, int32_t* front_h) {
+    if (N < 0 || (N > 0 && (!w_sorted_h || !front_h))) { gmm::set_error("gmm_fronts2_host: bad argument"); return GMM_EINVAL; }
+    std::vector<double> best;            // best[f], non-increasing
+    for (int i = 0; i < N; ++i) {
+        const double x = w_sorted_h[2 * (size_t)i], y = w_sorted_h[2 * (size_t)i + 1];
+        if (i > 0) {
+            const double px = w_sorted_h[2 * (size_t)i - 2], py = w_sorted_h[2 * (size_t)i - 1];
+            if (px < x || (px == x && py < y) || x != x || y != y) {
+                gmm::set_error("gmm_fronts2_host: rows are not sorted best first (or hold NaN)");
+                return GMM_EINVAL;
+            }
+            if (px == x && py == y) { front_h[i] = front_h[i - 1]; continue; }
+        }
+        // first f with best[f] < y
+        size_t lo = 0, hi = best.size();
+        while (lo < hi) {
+            const size_t mid = (lo + hi) / 2;
+            if (best[mid] < y) hi = mid; else lo = mid + 1;
+        }
+        if (lo == best.size()) best.push_back(y); else best[lo] = y;
+        front_h[i] = (int32_t)lo;
+    }
+    return GMM_OK;
+}

@@ -27,13 +27,6 @@ import numpy as np
 
 
 # ---- NSGA-II on arrays ---------------------------------------------------------------------
-def _first_below(neg_best, y):
-    """First front whose best second objective is < y; ``neg_best`` holds -best, ascending."""
-    from bisect import bisect_right
-    # best[f] < y  <=>  -best[f] > -y : first index with neg_best > -y
-    return bisect_right(neg_best, -y)
-
-
 _fronts_backend = None      # set by launch(): Engine.nondominated_fronts (GPU) for three or more objectives
 
 
@@ -51,43 +44,40 @@ def nondominated_fronts(w):
     n = w.shape[0]
     if w.shape[1] != 2 and _fronts_backend is not None and n > 256:
         return np.asarray(_fronts_backend(w), dtype=np.int64)
+    if w.shape[1] == 2 and n > 0:
+        # O(N log N) for two objectives (gmm_fronts2_host): rows visited by first objective
+        # descending, ties by second descending, so every dominator of a row comes before it; front
+        # f keeps the largest second objective it holds, and a row joins the first front whose best
+        # is strictly below its own second objective.
+        import ctypes as C
+        from . import _lib
+        order = np.lexsort((-w[:, 1], -w[:, 0]))
+        ws = np.ascontiguousarray(w[order], dtype=np.float64)
+        lev = np.empty(n, dtype=np.int32)
+        _lib.check(_lib.lib().gmm_fronts2_host(int(n), ws.ctypes.data_as(C.c_void_p), lev.ctypes.data_as(C.c_void_p)))
+        front = np.empty(n, dtype=np.int64)
+        front[order] = lev
+        return front
     front = np.full(n, -1, dtype=np.int64)
-    # work on unique fitness rows
+    # any other number of objectives, on the host: peel the non-dominated layer of the unique rows
+    # (O(N^2) per layer: small populations only; launch() installs the device sort)
     uniq, inv = np.unique(w, axis=0, return_inverse=True)
     inv = inv.reshape(-1)
     u = uniq.shape[0]
     ufront = np.full(u, -1, dtype=np.int64)
-    if uniq.shape[1] == 2:
-        # O(n log n) for two objectives: visit the unique points by first objective descending
-        # (ties: second descending), so every dominator of a point comes before it; front f keeps
-        # the largest second objective it holds (non-increasing in f), and a point joins the first
-        # front whose best is strictly below its own second objective.
-        order = np.lexsort((-uniq[:, 1], -uniq[:, 0]))
-        neg_best = []                      # -best[f], ascending
-        y = uniq[order, 1].tolist()
-        lev = [0] * u
-        for k in range(u):
-            f = _first_below(neg_best, y[k])
-            if f == len(neg_best):
-                neg_best.append(-y[k])
-            else:
-                neg_best[f] = -y[k]
-            lev[k] = f
-        ufront[order] = lev
-    else:
-        remaining = np.arange(u)
-        level = 0
-        while len(remaining):
-            sub = uniq[remaining]
-            nd = np.ones(len(sub), dtype=bool)
-            for s in range(0, len(sub), 512):          # chunked O(n^2) dominance test
-                blk = sub[s:s + 512]
-                ge = (sub[None, :, :] >= blk[:, None, :]).all(axis=2)
-                gt = (sub[None, :, :] > blk[:, None, :]).any(axis=2)
-                nd[s:s + 512] = ~(ge & gt).any(axis=1)
-            ufront[remaining[nd]] = level
-            remaining = remaining[~nd]
-            level += 1
+    remaining = np.arange(u)
+    level = 0
+    while len(remaining):
+        sub = uniq[remaining]
+        nd = np.ones(len(sub), dtype=bool)
+        for s in range(0, len(sub), 512):          # chunked O(n^2) dominance test
+            blk = sub[s:s + 512]
+            ge = (sub[None, :, :] >= blk[:, None, :]).all(axis=2)
+            gt = (sub[None, :, :] > blk[:, None, :]).any(axis=2)
+            nd[s:s + 512] = ~(ge & gt).any(axis=1)
+        ufront[remaining[nd]] = level
+        remaining = remaining[~nd]
+        level += 1
     front[:] = ufront[inv]
     return front
 
@@ -115,18 +105,23 @@ def sel_nsga2(values, weights, k):
     by decreasing crowding distance."""
     w = values * np.asarray(weights)[None, :]
     front = nondominated_fronts(w)
-    chosen = []
-    for level in range(front.max() + 1):
-        idx = np.flatnonzero(front == level)
-        if len(chosen) + len(idx) <= k:
-            chosen.extend(idx.tolist())
-            if len(chosen) == k:
-                break
+    n = len(front)
+    if k >= n:
+        return np.argsort(front, kind="stable")
+    order = np.argsort(front, kind="stable")           # whole fronts first, original order inside a front
+    counts = np.bincount(front)
+    ends = np.cumsum(counts)
+    last = int(np.searchsorted(ends, k, side="left"))  # the front that crosses k (or ends exactly at it)
+    start = int(ends[last - 1]) if last > 0 else 0
+    chosen = order[:start]
+    if start < k:
+        idx = order[start:ends[last]]
+        if ends[last] == k:
+            chosen = order[:k]
         else:
             cd = crowding_distance(values[idx])
-            order = np.argsort(-cd, kind="stable")
-            chosen.extend(idx[order[:k - len(chosen)]].tolist())
-            break
+            pick = np.argsort(-cd, kind="stable")[:k - start]
+            chosen = np.concatenate([chosen, idx[pick]])
     return np.asarray(chosen, dtype=np.int64)
 
 

@@ -197,6 +197,11 @@ int gmm_similar_lists(gmm_ctx* ctx, int N, int row0, int row1, const uint32_t* b
  * equal rows share a front.  Synchronises the stream once (the order check). */
 int gmm_nondominated_fronts(gmm_ctx* ctx, int n, int m, const double* w_sorted_d, int32_t* front_d, void* stream);
 
+/* HOST function: gmm_nondominated_fronts for the common two-objective job, O(N log N) on the host.
+ * w_sorted_h [N, 2] fp64 weighted values, rows sorted by column 0 descending, ties by column 1
+ * descending (checked); front_h [N] int32 out.  Equal rows share a front. */
+int gmm_fronts2_host(int N, const double* w_sorted_h, int32_t* front_h);
+
 /* HOST function: the greedy pass of gaudi/algorithms.py:139-155 over HOST partner lists
  * (ptr_h int64 [N+1], idx_h int32) and the candidates' lexicographic fitness ranks (rank_h,
  * larger = fitter, as ``i.fitness <= n_i.fitness`` compares wvalues): visit candidates in order;
