@@ -122,7 +122,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:
                 pass
-            time.sleep(0.01)
+            time.sleep(0.001)
 
     def stop(self):
         self._halt.set()
