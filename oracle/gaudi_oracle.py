@@ -352,6 +352,9 @@ def greedy_niching(order, similar, not_better):
 
 # --------------------------------------------------------------------------------------
 # Geometric restraint objectives ("next" row of the scope)
+# Parity status of this section: UNPINNED.  The reference has no test for its Distance and Angle
+# objectives, so there is no golden value to reproduce; the two functions below follow the
+# reference's own lines (cited) and are checked on hand-computable geometry only.
 # --------------------------------------------------------------------------------------
 def distance_objective(probe_xyz, target_xyz, threshold, tolerance=None, weight=1.0):
     """gaudi/objectives/distance.py:102-129 (``evaluate_distances``): mean absolute deviation of
