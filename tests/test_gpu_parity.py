@@ -293,6 +293,25 @@ def test_rmsd_matrix(small_system, torch_cuda):
     assert float(o.diagonal().abs().max()) == 0.0
 
 
+def test_large_receptor(torch_cuda):
+    """120,000 receptor atoms (a solvated complex): per-individual leaf lists and zone words of the
+    one-kernel path are then 22 KB of shared memory per pose; warp-per-individual and
+    CTA-per-individual variants against the tiled two-kernel path, bit for bit."""
+    from gaudi_b200.engine import Engine
+    params = M.ContactParams()
+    lig = synth.make_ligand(40, 10, seed=1)
+    rec = synth.make_receptor(120000, seed=2, params=params)
+    fused = Engine(lig, rec, params, device=0)
+    tiled = Engine(lig, rec, M.ContactParams(tiled=True), device=0)
+    for pop in (300, 3000):
+        tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=pop, radius=20.0)
+        s1, c1, _ = fused.evaluate(tors, xf)
+        s2, c2, _ = tiled.evaluate(tors, xf)
+        assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
+        assert int((c1.sum(dim=1) > 0).sum()) > pop // 2          # poses do touch the receptor
+    fused.close(); tiled.close()
+
+
 def test_nondominated_fronts_on_device(small_system, torch_cuda):
     """gmm_nondominated_fronts against the definition (peel the non-dominated layer, repeat) for
     2-5 objectives with plenty of ties and duplicates, and against the O(N log N) two-objective
