@@ -5,6 +5,7 @@
 set -e
 cd "$(dirname "$0")/.."
 POPS="${@:-8192 65536}"
+if git diff --quiet; then echo "working tree equals HEAD: nothing to compare"; exit 1; fi
 git stash -q
 python __graft_entry__.py build >/dev/null 2>&1 && cp gaudi_b200/libgaudimm_b200.so gaudi_b200/libA.bin
 git stash pop -q
