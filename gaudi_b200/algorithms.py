@@ -72,9 +72,18 @@ def ea_mu_plus_lambda(population, toolbox, mu, lambda_, cxpb, mutpb, ngen, cfg=N
         for ind, fit in zip(invalid, toolbox.map(toolbox.evaluate, invalid)):
             ind.fitness.values = fit
         candidates = population + offspring
-        if batch is not None and sim_args is not None:
-            batch.similarity_matrix(candidates, sim_args[0], sim_args[1])   # one GPU call per generation
-        new_population = niching(candidates, toolbox.similarity)
+        if batch is not None and sim_args is not None and getattr(toolbox, "array_niching", False):
+            # one GPU call per generation; the greedy pass runs over the partner lists it leaves
+            # (gmm_niching_host), same result as the pairwise loop below
+            import numpy as np
+            from . import tensor_ga
+            lists = batch.similarity_lists(candidates, sim_args[0], sim_args[1])
+            w = np.array([ind.fitness.wvalues for ind in candidates], dtype=np.float64)
+            new_population = [candidates[i] for i in tensor_ga.niching(lists, w)]
+        else:
+            if batch is not None and sim_args is not None:
+                batch.similarity_matrix(candidates, sim_args[0], sim_args[1])
+            new_population = niching(candidates, toolbox.similarity)
         while len(new_population) < mu:
             new_population.append(random.choice(candidates))
         if halloffame is not None:
@@ -106,7 +115,21 @@ def launch(cfg, device=0, seed=None):
     toolbox.register("mate", lambda a, b: a.mate(b))
     toolbox.register("mutate", lambda ind, indpb: ind.mutate(indpb), indpb=cfg.ga.mut_indpb)
     toolbox.register("similarity", lambda a, b: a.similar(b))
-    toolbox.register("select", deaplite.sel_nsga2)
+    if cfg.similarity.module == "gaudi_b200.similarity.rmsd":
+        # the stock similarity: niching and selection work on arrays (partner lists from the
+        # device, fronts by gmm_fronts2_host / gmm_nondominated_fronts) instead of O(N^2)
+        # Python-level calls; any other similarity function keeps the reference's pairwise loop
+        toolbox.array_niching = True
+        from . import tensor_ga
+        import numpy as np
+        tensor_ga.set_fronts_backend(environment.batch.engines[0][0].nondominated_fronts)
+
+        def select(individuals, k):
+            values = np.array([ind.fitness.values for ind in individuals], dtype=np.float64)
+            return [individuals[i] for i in tensor_ga.sel_nsga2(values, np.asarray(cfg.weights, float), k)]
+        toolbox.register("select", select)
+    else:
+        toolbox.register("select", deaplite.sel_nsga2)
     toolbox.register("map", BatchedMap(environment, toolbox.evaluate))
     if cfg.output.pareto:
         elite = deaplite.ParetoFront(toolbox.similarity)

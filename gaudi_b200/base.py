@@ -393,34 +393,52 @@ class BatchEvaluator(object):
         return self.evaluate([individual])[0][idx]
 
     # ---- batched similarity -----------------------------------------------------------------
-    def similarity_matrix(self, individuals, subjects, threshold):
-        """One ``gmm_rmsd_matrix`` call for every pair among ``individuals``; afterwards
-        ``gaudi_b200.similarity.rmsd`` answers from the bitmask."""
-        from .engine import bits_to_bool
-        conf = np.stack([np.asarray(ind._molecules[subjects[0]]._expressed_coordinates - self.centre, np.float32)
-                         for ind in individuals])
+    def _similarity_bits(self, individuals, subjects, threshold):
+        """Device bitmask (N, ceil(N/32)) int32: pairs similar in EVERY subject molecule."""
         eng = self.engines[0][0]
-        _, bits = eng.rmsd_matrix(conf, threshold=threshold, values=False)
-        sim = bits_to_bool(bits, len(individuals))
-        for s in subjects[1:]:
+        bits = None
+        for s in subjects:
             conf = np.stack([np.asarray(ind._molecules[s]._expressed_coordinates - self.centre, np.float32)
                              for ind in individuals])
-            _, bits = eng.rmsd_matrix(conf, threshold=threshold, values=False)
-            sim &= bits_to_bool(bits, len(individuals))
-        # keyed by identity: the tuple keeps the individuals alive so that no later individual can
+            _, b = eng.rmsd_matrix(conf, threshold=threshold, values=False)
+            bits = b if bits is None else bits & b
+        return bits
+
+    def similarity_matrix(self, individuals, subjects, threshold):
+        """One ``gmm_rmsd_matrix`` call per subject for every pair among ``individuals``; afterwards
+        ``gaudi_b200.similarity.rmsd`` answers from the result.  Returns the (N, N) bool matrix."""
+        from .engine import bits_to_bool
+        bits = self._similarity_bits(individuals, subjects, threshold)
+        ptr, idx = self.engines[0][0].similar_lists(bits, len(individuals))
+        self._remember(individuals, ptr, idx, subjects, threshold)
+        return bits_to_bool(bits, len(individuals))
+
+    def similarity_lists(self, individuals, subjects, threshold):
+        """As ``similarity_matrix`` but only the partner lists leave the device: ``(ptr, idx)`` CSR
+        over ``individuals`` (self excluded), what the niching pass consumes."""
+        bits = self._similarity_bits(individuals, subjects, threshold)
+        ptr, idx = self.engines[0][0].similar_lists(bits, len(individuals))
+        self._remember(individuals, ptr, idx, subjects, threshold)
+        return ptr, idx
+
+    def _remember(self, individuals, ptr, idx, subjects, threshold):
+        # keyed by identity: the entry keeps the individuals alive so that no later individual can
         # be handed the id of one of these and read its row by mistake
-        self._sim = ({id(ind): k for k, ind in enumerate(individuals)}, sim, tuple(subjects), float(threshold),
+        self._sim = ({id(ind): k for k, ind in enumerate(individuals)}, ptr, idx, tuple(subjects), float(threshold),
                      list(individuals))
-        return sim
 
     def lookup_similarity(self, ind1, ind2, subjects, threshold):
         if self._sim is None:
             return None
-        index, sim, subj, thr, _alive = self._sim
+        index, ptr, idx, subj, thr, _alive = self._sim
         a, b = index.get(id(ind1)), index.get(id(ind2))
         if a is None or b is None or subj != tuple(subjects) or thr != float(threshold):
             return None
-        return bool(sim[a, b])
+        if a == b:
+            return True
+        row = idx[ptr[a]:ptr[a + 1]]                       # partners of a, ascending
+        k = int(np.searchsorted(row, b))
+        return bool(k < len(row) and row[k] == b)
 
     def close(self):
         for eng, _ in self.engines:
