@@ -47,6 +47,7 @@ __device__ __forceinline__ void team_sync() {
     if (S == 1) __syncwarp(); else __syncthreads();
 }
 
+template <bool PLAIN>
 __device__ __forceinline__ void fused_drain_pairs(const SweepArgs& a, uint32_t* pq, int& npq, const float4* ligx,
                                                   Acc& acc, int lane) {
     for (int base = 0; base < npq; base += 32) {
@@ -54,7 +55,7 @@ __device__ __forceinline__ void fused_drain_pairs(const SweepArgs& a, uint32_t* 
         if (e < npq) {
             const uint32_t pr = pq[e];
             const int s = pr >> 22, j = pr & 0x3fffff;
-            if (!ms_excluded(a.ms_ptr, a.ms_idx, s, j)) {
+            if (PLAIN || !ms_excluded(a.ms_ptr, a.ms_idx, s, j)) {
                 const float4 m = ligx[s];
                 const float4 r = a.rec4[j];
                 const PairScore ps = score_pair(m.x, m.y, m.z, m.w, a.mflags[s], r.x, r.y, r.z, r.w, a.rflags[j], a.prm);
@@ -75,6 +76,7 @@ __device__ __forceinline__ void fused_drain_pairs(const SweepArgs& a, uint32_t* 
 // bit per mobile atom and the set bits of all lanes are then compacted into the pair queue one
 // ballot per round (rounds = the largest hit count of any lane, a handful) instead of one ballot
 // per mobile atom.
+template <bool PLAIN>
 __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint32_t* cq, int& ncq, uint32_t* pq,
                                                        int& npq, const float4* ligx, const float4* ligc,
                                                        const float4 sph, const uint32_t* zm, Acc& acc, int lane) {
@@ -103,11 +105,11 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
             for (int k = 0; k < n; ++k) {
                 const int s = s0 + k;
                 const float4 m = ligc[s];
-                const float t = ligx[s].w + ((s < a.n_hseed || s >= a.n_seed) ? cr_h : cr_c);
+                const float t = ligx[s].w + ((s < a.n_hseed || (!PLAIN && s >= a.n_seed)) ? cr_h : cr_c);
                 const float dot = fmaf(ax, m.x, fmaf(ay, m.y, fmaf(az, m.z, m.w)));
                 if (dot <= fmaf(t * 1.000004f, t, slack)) hits |= 1u << k;
             }
-            hits &= zm[s0 >> 5];
+            if (!PLAIN) hits &= zm[s0 >> 5];
             unsigned live = __ballot_sync(0xffffffffu, hits != 0u);
             while (live) {
                 if (hits) {
@@ -117,7 +119,7 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
                 }
                 npq += __popc(live);
                 __syncwarp();
-                if (npq > kPairQ - 32) fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+                if (npq > kPairQ - 32) fused_drain_pairs<PLAIN>(a, pq, npq, ligx, acc, lane);
                 live = __ballot_sync(0xffffffffu, hits != 0u);
             }
         }
@@ -129,8 +131,11 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
 // S: warps per individual.  CULL: leaves out of reach of the pose are skipped (the normal mode);
 // without it every leaf is swept (the dense mode the FP32 roofline is quoted for).  A template
 // parameter rather than a run-time flag: the kernel is sensitive to its instruction footprint
-// and each variant carries only its own code.
-template <int S, bool CULL>
+// and each variant carries only its own code.  PLAIN: the common docking job — every mobile atom is a
+// zone seed (a ligand, no flexible side chains), the receptor holds no seeds and no atom bonded to
+// the mobile set: the mobile-zone bits, the always-in-zone words, the non-seed sweep and the
+// exclusion lookups are compiled out.
+template <int S, bool CULL, bool PLAIN>
 __global__ void __launch_bounds__(128, 8)
 contacts_fused_kernel(const FusedArgs f) {
     const SweepArgs& a = f.s;
@@ -207,6 +212,7 @@ contacts_fused_kernel(const FusedArgs f) {
     const bool internal = a.prm.options & GMM_OPT_ONLY_INTERNAL;
     // mobile atoms in the zone: seeds always, the others (flexible side chains) iff within radius
     // of a seed; one atom per lane, 32 atoms = one word per ballot
+    if (!PLAIN)
     for (int base = wt * 32; base < a.MW * 32; base += TL) {
         const int s = base + lane;
         bool in = s < a.n_seed;
@@ -257,7 +263,7 @@ contacts_fused_kernel(const FusedArgs f) {
         ligc[s] = make_float4(x, y, z, fmaf(z, z, fmaf(y, y, x * x)));
     }
     // always-in-zone receptor atoms exist only when the receptor holds zone seeds (n_sseed > 0)
-    const bool has_always = a.n_sseed > 0;
+    const bool has_always = !PLAIN && a.n_sseed > 0;
     for (int st = tlane; st <= f.NST; st += TL) zone[st] = has_always ? a.always[st] : 0u;
 
     Acc acc; acc.cfx = 0; acc.hfx = 0; acc.nc = 0; acc.nh = 0;
@@ -412,7 +418,7 @@ contacts_fused_kernel(const FusedArgs f) {
             // one call site for the expansion keeps the kernel's code (and its instruction-cache
             // footprint) small: queue nearly full, or nothing left to sweep
             if (gi >= ngroups || ncq > kCandQ - 128) {
-                fused_drain_candidates(a, cq, ncq, pq, npq, ligx, ligc, sph, zm, acc, lane);
+                fused_drain_candidates<PLAIN>(a, cq, ncq, pq, npq, ligx, ligc, sph, zm, acc, lane);
                 if (gi >= ngroups) break;
             }
             const uint2 st4 = *reinterpret_cast<const uint2*>(list + 4 * gi);
@@ -465,10 +471,11 @@ contacts_fused_kernel(const FusedArgs f) {
                 bool near = false;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) near = near || (ms[k] <= fmaf(near_m, nr[k], near_c));
-                if (a.n_sseed > 0) near = near || ((zone[stv[0]] | zone[stv[1]] | zone[stv[2]] | zone[stv[3]]) != 0u);
+                if (!PLAIN && a.n_sseed > 0) near = near || ((zone[stv[0]] | zone[stv[1]] | zone[stv[2]] | zone[stv[3]]) != 0u);
                 if (!__any_sync(0xffffffffu, near)) continue;
             }
             float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
+            if (!PLAIN) {
 #pragma unroll 2
             for (s = a.n_seed; s + 1 < a.M; s += 2) {      // mobile atoms that are not zone seeds
                 const float4 m = ligc[s], q = ligc[s + 1];
@@ -483,11 +490,12 @@ contacts_fused_kernel(const FusedArgs f) {
                 for (int k = 0; k < 4; ++k)
                     ma[k] = fminf(ma[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
             }
+            }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float margin = 2e-4f + 1e-6f * (nr[k] + wmax);
                 const float dz = ms[k] + nr[k];
-                bool in = ((zone[stv[k]] >> lane) & 1u) || dz <= a.rad2 - margin;
+                bool in = (!PLAIN && ((zone[stv[k]] >> lane) & 1u)) || dz <= a.rad2 - margin;
                 const bool band = !in && dz <= a.rad2 + margin;
                 if (__any_sync(0xffffffffu, band)) {
                     if (band) {     // re-decide with exact differences (same arithmetic as the dump kernel)
@@ -512,7 +520,7 @@ contacts_fused_kernel(const FusedArgs f) {
             }
             __syncwarp();
         }
-        fused_drain_pairs(a, pq, npq, ligx, acc, lane);
+        fused_drain_pairs<PLAIN>(a, pq, npq, ligx, acc, lane);
         team_sync<S>();
 
         // ---- 3. static-static pairs with both atoms in the zone ------------------------------
@@ -560,7 +568,7 @@ contacts_fused_kernel(const FusedArgs f) {
         const uint32_t pr = f.mm_pairs[e];
         const float c2 = f.mm_c2[e];                   // (r_a + r_b - cutoff)^2, fixed per pair
         const int sa = pr & 0xffff, sb = pr >> 16;
-        if (!a.all_seed && (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u))) continue;
+        if (!PLAIN && !a.all_seed && (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u))) continue;
         const float4 A = ligx[sa], B = ligx[sb];
         if (dist2f(A.x, A.y, A.z, B.x, B.y, B.z) > c2) continue;
         const PairScore ps = score_pair(A.x, A.y, A.z, A.w, a.mflags[sa], B.x, B.y, B.z, B.w, a.mflags[sb], a.prm);
@@ -643,8 +651,13 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
     GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));
     const bool cull = f.s.cull != 0;
-    void (*kernel)(const FusedArgs) = S == 1 ? (cull ? contacts_fused_kernel<1, true> : contacts_fused_kernel<1, false>)
-                                             : (cull ? contacts_fused_kernel<4, true> : contacts_fused_kernel<4, false>);
+    const bool plain = c->all_seed && c->n_sseed == 0 && c->ms_nnz == 0 && !(c->prm.options & GMM_OPT_ONLY_INTERNAL);
+    void (*const variants[8])(const FusedArgs) = {
+        contacts_fused_kernel<1, false, false>, contacts_fused_kernel<1, false, true>,
+        contacts_fused_kernel<1, true, false>, contacts_fused_kernel<1, true, true>,
+        contacts_fused_kernel<4, false, false>, contacts_fused_kernel<4, false, true>,
+        contacts_fused_kernel<4, true, false>, contacts_fused_kernel<4, true, true>};
+    void (*kernel)(const FusedArgs) = variants[(S == 1 ? 0 : 4) + (cull ? 2 : 0) + (plain ? 1 : 0)];
     { const int rc = allow_dynamic_smem((const void*)kernel, c->device, limit); if (rc) return rc; }
     if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
     kernel<<<S == 1 ? (P + 3) / 4 : P, 128, smem, s>>>(f);
