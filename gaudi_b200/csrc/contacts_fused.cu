@@ -42,6 +42,26 @@ struct FusedArgs {
 
 struct Acc { long long cfx, hfx; int nc, nh; };
 
+// Warp reductions on the REDUX unit (one instruction per 32-bit word) instead of five rounds of
+// shuffles: floats through the usual order-preserving map to unsigned integers, 64-bit sums in
+// three pieces of at most 24 bits so that 32 lanes cannot overflow a word.
+__device__ __forceinline__ unsigned float_key(float v) {
+    const unsigned b = __float_as_uint(v);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+__device__ __forceinline__ float warp_min(float v) { return key_float(__reduce_min_sync(0xffffffffu, float_key(v))); }
+__device__ __forceinline__ float warp_max(float v) { return key_float(__reduce_max_sync(0xffffffffu, float_key(v))); }
+__device__ __forceinline__ long long warp_sum(long long v) {
+    const unsigned long long u = (unsigned long long)v;
+    const unsigned long long a = __reduce_add_sync(0xffffffffu, (unsigned)(u & 0xffffffu));
+    const unsigned long long b = __reduce_add_sync(0xffffffffu, (unsigned)((u >> 24) & 0xffffffu));
+    const unsigned long long c = __reduce_add_sync(0xffffffffu, (unsigned)(u >> 48));
+    return (long long)(a + (b << 24) + (c << 48));          // modulo 2^64, as the lane-wise sum would be
+}
+
 template <int S>
 __device__ __forceinline__ void team_sync() {
     if (S == 1) __syncwarp(); else __syncthreads();
@@ -230,6 +250,7 @@ contacts_fused_kernel(const FusedArgs f) {
     }
     if (wt == 0) {                                     // bounding box and sphere of the pose
         float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+#pragma unroll 1
         for (int s = lane; s < a.M; s += 32) {
             const float4 m = ligx[s];
             lo[0] = fminf(lo[0], m.x); hi[0] = fmaxf(hi[0], m.x);
@@ -237,17 +258,12 @@ contacts_fused_kernel(const FusedArgs f) {
             lo[2] = fminf(lo[2], m.z); hi[2] = fmaxf(hi[2], m.z);
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
-                hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
-            }
+        for (int k = 0; k < 3; ++k) { lo[k] = warp_min(lo[k]); hi[k] = warp_max(hi[k]); }
         const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
         float r2 = 0.f;
+#pragma unroll 1
         for (int s = lane; s < a.M; s += 32) r2 = fmaxf(r2, dist2f(ligx[s].x, ligx[s].y, ligx[s].z, cx, cy, cz));
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, o));
+        r2 = warp_max(r2);
         if (lane == 0) {
             misc[0] = make_float4(cx, cy, cz, r2);
             misc[1] = make_float4(lo[0], lo[1], lo[2], 0.f);
@@ -257,6 +273,7 @@ contacts_fused_kernel(const FusedArgs f) {
     team_sync<S>();
     const float4 sph = misc[0];
     const float wmax = sph.w;
+#pragma unroll 1
     for (int s = tlane; s < a.Mp; s += TL) {
         const float4 m = ligx[s];
         const float x = m.x - sph.x, y = m.y - sph.y, z = m.z - sph.z;
@@ -264,6 +281,7 @@ contacts_fused_kernel(const FusedArgs f) {
     }
     // always-in-zone receptor atoms exist only when the receptor holds zone seeds (n_sseed > 0)
     const bool has_always = !PLAIN && a.n_sseed > 0;
+#pragma unroll 2
     for (int st = tlane; st <= f.NST; st += TL) zone[st] = has_always ? a.always[st] : 0u;
 
     Acc acc; acc.cfx = 0; acc.hfx = 0; acc.nc = 0; acc.nh = 0;
@@ -577,12 +595,8 @@ contacts_fused_kernel(const FusedArgs f) {
     }
 
     // ---- 5. finish ---------------------------------------------------------------------------
-    long long cfx = acc.cfx, hfx = acc.hfx, nc = acc.nc, nh = acc.nh;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        cfx += __shfl_xor_sync(0xffffffffu, cfx, o); hfx += __shfl_xor_sync(0xffffffffu, hfx, o);
-        nc += __shfl_xor_sync(0xffffffffu, nc, o); nh += __shfl_xor_sync(0xffffffffu, nh, o);
-    }
+    long long cfx = warp_sum(acc.cfx), hfx = warp_sum(acc.hfx);
+    long long nc = __reduce_add_sync(0xffffffffu, acc.nc), nh = __reduce_add_sync(0xffffffffu, acc.nh);
     if (S > 1) {
         if (lane == 0) {
             atomicAdd((unsigned long long*)&accs[0], (unsigned long long)cfx);
