@@ -509,25 +509,38 @@ contacts_fused_kernel(const FusedArgs f) {
                     ma[k] = fminf(ma[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
             }
             }
+            bool in[4], band[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float margin = 2e-4f + 1e-6f * (nr[k] + wmax);
                 const float dz = ms[k] + nr[k];
-                bool in = (!PLAIN && ((zone[stv[k]] >> lane) & 1u)) || dz <= a.rad2 - margin;
-                const bool band = !in && dz <= a.rad2 + margin;
-                if (__any_sync(0xffffffffu, band)) {
-                    if (band) {     // re-decide with exact differences (same arithmetic as the dump kernel)
-                        const float4 r = a.rec4[stv[k] * kSubTile + lane];
-                        float e = 3e38f;
+                in[k] = (!PLAIN && ((zone[stv[k]] >> lane) & 1u)) || dz <= a.rad2 - margin;
+                band[k] = !in[k] && dz <= a.rad2 + margin;
+            }
+            if (__any_sync(0xffffffffu, band[0] || band[1] || band[2] || band[3])) {
+                // rare (a handful of atoms per thousand): re-decide with exact differences, the same
+                // arithmetic as the dump kernel.  One rolled copy of the loop for the four leaves.
+#pragma unroll 1
+                for (int k = 0; k < 4; ++k) {
+                    const bool bk = k == 0 ? band[0] : k == 1 ? band[1] : k == 2 ? band[2] : band[3];
+                    if (!bk) continue;
+                    const uint32_t st = k == 0 ? stv[0] : k == 1 ? stv[1] : k == 2 ? stv[2] : stv[3];
+                    const float4 r = a.rec4[st * kSubTile + lane];
+                    float e = 3e38f;
 #pragma unroll 2
-                        for (int s = 0; s < a.n_seed; ++s)
-                            e = fminf(e, dist2f(r.x, r.y, r.z, ligx[s].x, ligx[s].y, ligx[s].z));
-                        in = e <= a.rad2;
-                    }
+                    for (int s = 0; s < a.n_seed; ++s)
+                        e = fminf(e, dist2f(r.x, r.y, r.z, ligx[s].x, ligx[s].y, ligx[s].z));
+                    const bool res = e <= a.rad2;
+                    in[0] = k == 0 ? res : in[0]; in[1] = k == 1 ? res : in[1];
+                    in[2] = k == 2 ? res : in[2]; in[3] = k == 3 ? res : in[3];
                 }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float margin = 2e-4f + 1e-6f * (nr[k] + wmax);
                 const float c = rw[k] + a.rmax_mobile;
-                const bool cand = in && (ma[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin);
-                const unsigned zb = __ballot_sync(0xffffffffu, in);
+                const bool cand = in[k] && (ma[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin);
+                const unsigned zb = __ballot_sync(0xffffffffu, in[k]);
                 const unsigned cb = __ballot_sync(0xffffffffu, cand);
                 __syncwarp();
                 if (lane == 0 && stv[k] < (uint32_t)f.NST) zone[stv[k]] = zb;
