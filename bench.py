@@ -370,12 +370,12 @@ def run_b200(args):
                          "traffic": 31.76e6 if (name == "c3" and world == 1) else None,
                          "algorithmic_bytes_per_launch": shard * (L * 12 + 16 + 8),
                          "hbm": hbm_check(shard * (L * 12 + 16 + 8), sweep),
-                         "note": "culled run: the pair-test flop count credits only the sweep (about a fifth of "
+                         "note": "culled run: the pair-test flop count credits only the sweep (about a third of "
                                  "the issued instructions); culling, candidate expansion, pair scoring and the "
                                  "static-pair walk are per-individual bookkeeping. The dense run of the same "
                                  "kernel (key 'dense') is the sweep-dominated regime the FP32 roofline models. "
                                  "ncu of this kernel: profiles/ncu_contacts_fused_culled_r01.txt (issue slots "
-                                 "~65 % busy, latency-bound)",
+                                 "~79 % busy, issue-bound)",
                          "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
                          "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
                          "kernel_ms": sweep, "express_ms": float(np.mean(expr_ms)), "finalize_ms": float(np.mean(fin_ms)),
