@@ -37,6 +37,7 @@ struct FusedArgs {
     const uint32_t* mm_pairs; const float* mm_c2; int n_mm;
     double* scores; int32_t* counts;
     int ind_bytes;
+    int count_tests;  // 1: tally the executed pair tests (gmm_last_pair_tests); on while profiling is enabled
     int tma_pose;     // 1: stage each pose with one TMA bulk copy (size and alignment permit)
 };
 
@@ -620,9 +621,9 @@ contacts_fused_kernel(const FusedArgs f) {
         team_sync<S>();
         cfx = accs[0]; hfx = accs[1]; nc = accs[2]; nh = accs[3];
     }
-    if (lane == 0 && swept_leaves) atomicAdd(a.counters, (unsigned long long)swept_leaves * kSubTile * a.M);
+    if (f.count_tests && lane == 0 && swept_leaves) atomicAdd(a.counters, (unsigned long long)swept_leaves * kSubTile * a.M);
     if (tlane == 0) {
-        if (f.n_mm) atomicAdd(a.counters, (unsigned long long)f.n_mm);
+        if (f.count_tests && f.n_mm) atomicAdd(a.counters, (unsigned long long)f.n_mm);
         double clash = 2.0 * ((double)cfx / kFxScale);          // contacts.py:176-177
         const double hydro = 2.0 * ((double)hfx / kFxScale);
         if (a.prm.cutoff != 0.0 && clash > a.prm.cutoff) clash = -1000.0 * a.prm.weight;   // contacts.py:132-133
@@ -663,6 +664,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.rr_ptr = c->rr_nnz ? c->d_rr_ptr : nullptr; f.edge = c->d_edge;
     f.mm_pairs = c->d_mm_pairs; f.mm_c2 = c->d_mm_c2; f.n_mm = c->n_mm;
     f.scores = scores; f.counts = counts;
+    f.count_tests = c->prof ? 1 : 0;
     const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
     const size_t pose_bytes = (size_t)c->M * 3 * sizeof(float);

@@ -238,7 +238,9 @@ int gmm_contacts_pairs(gmm_ctx* ctx, const float* xyz_one_d, int max_pairs,
  * MEASURED_PEAKS.json does not carry).  Synchronises. */
 int gmm_measure_fp32_peak(int device, double* tflops_out);
 /* Pair tests executed by the last gmm_contacts/gmm_evaluate on this context (receptor
- * tiles that survived culling x mobile atoms + intra-mobile pairs).  Synchronises. */
+ * tiles that survived culling x mobile atoms + intra-mobile pairs).  The one-kernel Contacts path
+ * keeps this tally only while profiling is on (gmm_set_profiling(ctx, 1)): it is instrumentation,
+ * one global atomic per individual, and costs 1 % of the kernel.  Synchronises. */
 int gmm_last_pair_tests(gmm_ctx* ctx, unsigned long long* n_out);
 /* Per-kernel timing for roofline reports: when on, CUDA events are recorded around the
  * express, Contacts-sweep and Contacts-finalize kernels on the caller's stream;

@@ -165,12 +165,14 @@ def test_contacts_invariances(small_system, torch_cuda):
     lig, rec, params, eng = small_system
     dense = Engine(lig, rec, M.ContactParams(cull=False), device=0)
     tors, xf = synth.make_alleles(4096, lig.n_allele_torsions, seed=3)
+    eng.set_profiling(True); dense.set_profiling(True)        # the pair-test tally is kept while profiling
     s1, c1, _ = eng.evaluate(tors, xf)
     s2, c2, _ = dense.evaluate(tors, xf)
     assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
+    assert 0 < eng.last_pair_tests() < dense.last_pair_tests()
+    eng.set_profiling(False)
     parts = [eng.evaluate(tors[a:b], xf[a:b])[0] for a, b in ((0, 1000), (1000, 1003), (1003, 4096))]
     assert torch_cuda.equal(torch_cuda.cat(parts), s1)
-    assert eng.last_pair_tests() < dense.last_pair_tests()
 
 
 @pytest.mark.parametrize("pop", [4096, 100, 1])
@@ -452,10 +454,12 @@ def test_full_size_baseline_config(torch_cuda):
     tors, xf = synth.make_alleles(65536, 10, seed=3)
     eng = Engine(lig, rec, params, device=0)
     dense = Engine(lig, rec, M.ContactParams(cull=False), device=0)
+    eng.set_profiling(True); dense.set_profiling(True)
     s1, c1, x1 = eng.evaluate(tors, xf, want_xyz=True)
     s2, c2 = dense.contacts(x1)
     assert torch_cuda.equal(s1, s2) and torch_cuda.equal(c1, c2)
-    assert eng.last_pair_tests() * 10 < dense.last_pair_tests()
+    assert 0 < eng.last_pair_tests() * 10 < dense.last_pair_tests()
+    eng.set_profiling(False)
     parts = [eng.evaluate(tors[k * 8192:(k + 1) * 8192], xf[k * 8192:(k + 1) * 8192])[0] for k in range(8)]
     assert torch_cuda.equal(torch_cuda.cat(parts), s1)
     s = s1.cpu().numpy(); x = x1.cpu().numpy().astype(np.float64) + eng.centre
