@@ -286,6 +286,8 @@ class Engine(object):
         return {"express": ms[0], "sweep": ms[1], "finalize": ms[2]}
 
     def last_pair_tests(self):
+        """Pair tests executed by the last Contacts call; the one-kernel path keeps the tally only
+        while ``set_profiling(True)`` is in effect (``gmm_last_pair_tests``)."""
         n = C.c_ulonglong(0)
         _lib.check(self._L.gmm_last_pair_tests(self._h, C.byref(n)))
         return int(n.value)
