@@ -24,6 +24,7 @@ SIGNATURES = {
     "gmm_last_error": (C.c_char_p, []),
     "gmm_version": (_i, []),
     "gmm_reserve": (_i, [_vp, _i]),
+    "gmm_reserve_rmsd": (_i, [_vp, _i, _i]),
     "gmm_set_mobile": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i]),
     "gmm_set_rotamers": (_i, [_vp, _i, _vp, _vp]),
     "gmm_set_receptor": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -522,6 +522,13 @@ int gmm_reserve(gmm_ctx* c, int max_pop) {
     return ensure_scratch(c, need);
 }
 
+int gmm_reserve_rmsd(gmm_ctx* c, int max_n, int atoms) {
+    REQUIRE(c, GMM_EINVAL, "gmm_reserve_rmsd: ctx is NULL");
+    REQUIRE(max_n >= 0 && atoms >= 1, GMM_EINVAL, "gmm_reserve_rmsd: max_n=%d atoms=%d invalid", max_n, atoms);
+    DeviceGuard g(c->device);
+    return reserve_rmsd_workspace(c, max_n, atoms);
+}
+
 static int check_ready(gmm_ctx* c, int P, const char* fn) {
     REQUIRE(c, GMM_EINVAL, "%s: ctx is NULL", fn);
     REQUIRE(c->has_mobile, GMM_ESTATE, "%s: gmm_set_mobile has not been called", fn);

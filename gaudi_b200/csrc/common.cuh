@@ -230,6 +230,7 @@ int launch_geometry(gmm_ctx* c, int P, const float* xyz, double* out, cudaStream
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);
+int reserve_rmsd_workspace(gmm_ctx* c, int N, int A);
 int launch_pairs_dump(gmm_ctx* c, const float* xyz_one, int max_pairs, int32_t* pairs_h,
                       int32_t* kind_h, double* ov_h, double* val_h, int* n_out, cudaStream_t s);
 int ensure_scratch(gmm_ctx* c, size_t bytes);

@@ -23,8 +23,6 @@
 //   4  intra    pairs inside the mobile set (exclusions pre-removed);
 //   5  finish   fixed-point sums -> doubles, x2 (contacts.py:176-177), cutoff penalty
 //               (contacts.py:132-133).
-#include <cstdlib>
-
 #include "contacts_common.cuh"
 
 namespace gmm {
@@ -203,12 +201,31 @@ contacts_fused_kernel(const FusedArgs f) {
                          ::"r"((unsigned)__cvta_generic_to_shared(raw)), "l"(a.xyz + (size_t)p * a.M * 3),
                            "r"(bytes), "r"(mbar_s) : "memory");
         }
-        unsigned done = 0;
-        for (int spin = 0; !done; ++spin) {
+        // The wait is bounded by TIME (two seconds of the global timer, looked at every 4,096 polls),
+        // not by a poll count: under a debugger, a profiler's replay or time-slicing a healthy copy can
+        // take arbitrarily many polls.  A copy that has still not landed then is given up on without
+        // taking the context down: the individual's scores become NaN and d_counters[1] counts it.
+        unsigned done = 0, expired = 0;
+        unsigned long long t_start = 0;
+        for (int spin = 0; !done && !expired; ++spin) {
             asm volatile("{\n\t.reg .pred q;\n\t"
                          "mbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0;\n\t"
                          "selp.u32 %0, 1, 0, q;\n\t}" : "=r"(done) : "r"(mbar_s) : "memory");
-            if (spin > (1 << 24)) __trap();          // never hang the GPU on a lost copy
+            if (!done && (spin & 4095) == 4095) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t_start == 0) t_start = now;
+                else if (now - t_start > 2000000000ull) expired = 1;
+            }
+        }
+        if (S == 1 ? __any_sync(0xffffffffu, expired) : __syncthreads_or((int)expired)) {
+            if (tlane == 0) {
+                atomicAdd(a.counters + 1, 1ull);
+                f.scores[2 * (size_t)p] = __longlong_as_double(0x7ff8000000000000ll);
+                f.scores[2 * (size_t)p + 1] = __longlong_as_double(0x7ff8000000000000ll);
+                if (f.counts) { f.counts[2 * (size_t)p] = -1; f.counts[2 * (size_t)p + 1] = -1; }
+            }
+            return;
         }
         for (int s = tlane; s < a.Mp; s += TL) {
             const int atom = a.slot2atom[s];
@@ -673,12 +690,12 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     const size_t queues = kFusedQueues;
     const size_t limit = kFusedSmemLimit;
     // warp-per-individual from this population on; below it a CTA per individual fills the GPU better
-    static const int team_switch = getenv("GMM_TEAM_SWITCH") ? atoi(getenv("GMM_TEAM_SWITCH")) : 148 * 18;
-    int S = (P >= team_switch) ? 1 : 4;
+    constexpr int kTeamSwitch = 148 * 18;       // measured: tools/latency_small_pop.py
+    int S = (P >= kTeamSwitch) ? 1 : 4;
     if (S == 1 && 4 * ind + queues > limit) S = 4;
     if (ind + queues > limit) return GMM_OK;    // not handled
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
-    GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));
+    if (c->prof) GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));   // the pair-test tally
     const bool cull = f.s.cull != 0;
     const bool plain = c->all_seed && c->n_sseed == 0 && c->ms_nnz == 0 && !(c->prm.options & GMM_OPT_ONLY_INTERNAL);
     void (*const variants[8])(const FusedArgs) = {

@@ -16,6 +16,8 @@
 // For them the scratch lives in a fixed array inside the library image itself.  Every GPU
 // that loads libgaudimm_b200.so carries these kStaticScratchBytes until the process exits,
 // which is why the size is modest and populations that need more are refused.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -30,6 +32,7 @@ static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBy
 
 constexpr int kMaxDevices = 64;
 void* g_scratch_addr[kMaxDevices] = {nullptr};
+std::mutex g_scratch_mu;      // host threads making their first call on a device at the same time
 
 // Device address of g_static_scratch on `device` (which must be the current device).
 int static_scratch_address(int device, void** out) {
@@ -37,6 +40,7 @@ int static_scratch_address(int device, void** out) {
         gmm::set_error("gmm_evaluate_static: device %d outside [0,%d)", device, kMaxDevices);
         return GMM_ELIMIT;
     }
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
     if (g_scratch_addr[device] == nullptr) {
         void* ptr = nullptr;
         cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);

@@ -413,8 +413,9 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
     }
 }
 
-static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, uint32_t* out_bits,
-                           double thr, cudaStream_t s) {
+// Workspace of the bitmask path: re-centred fp16 conformers, their squared norms, column sums, flag.
+// Grown on demand (device-wide synchronisation + cudaMalloc); gmm_reserve_rmsd() pre-sizes it.
+int reserve_rmsd_workspace(gmm_ctx* c, int N, int A) {
     const int K = 3 * A, Kp = (K + 15) & ~15;
     const size_t xc_bytes = ((size_t)N * Kp * sizeof(__half) + 255) / 256 * 256;
     const size_t need = xc_bytes + ((size_t)N + Kp + 64) * sizeof(float);
@@ -423,6 +424,14 @@ static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0,
         GMM_CUDA(cudaMalloc(&c->d_rmsd_ws, need));
         c->rmsd_ws_bytes = need;
     }
+    return GMM_OK;
+}
+
+static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, uint32_t* out_bits,
+                           double thr, cudaStream_t s) {
+    const int K = 3 * A, Kp = (K + 15) & ~15;
+    const size_t xc_bytes = ((size_t)N * Kp * sizeof(__half) + 255) / 256 * 256;
+    { const int rc = reserve_rmsd_workspace(c, N, A); if (rc) return rc; }
     __half* xc = static_cast<__half*>(c->d_rmsd_ws);
     float* norm = reinterpret_cast<float*>(static_cast<unsigned char*>(c->d_rmsd_ws) + xc_bytes);
     float* colsum = norm + N;

@@ -2,6 +2,12 @@
 gaudi/cli/gaudi_run.py:69-134, gaudi/genes/torsion.py:173-195), restated from DEAP's
 published algorithms because DEAP is not installable here.  All of it is host-side GA
 bookkeeping ("next" row 1); none of it is on the CUDA path.
+
+Attribution: ``cx_simulated_binary_bounded``, ``mut_polynomial_bounded``, ``cx_two_point``,
+``var_or``, ``sort_nondominated``, ``assign_crowding_dist``, ``sel_nsga2``, ``HallOfFame`` and
+``ParetoFront`` follow the corresponding functions of DEAP (Distributed Evolutionary Algorithms in
+Python, https://github.com/DEAP/deap, (c) the DEAP authors, GNU LGPL v3), operation for operation,
+so that a GA run varies and selects alleles exactly as the reference's DEAP calls do.
 """
 from __future__ import annotations
 
@@ -237,7 +243,10 @@ class ParetoFront(HallOfFame):
             for i in reversed(to_remove):
                 del self.items[i]
             if not is_dominated and not has_twin:
+                # DEAP's HallOfFame.insert keeps the items sorted best first; the reference writes its
+                # results in that order, so result numbering follows it
                 self.items.append(deepcopy(ind))
+                self.items.sort(key=attrgetter("fitness"), reverse=True)
 
 
 # ---- variation operators ----------------------------------------------------------------

@@ -103,6 +103,10 @@ class Engine(object):
     def reserve(self, max_pop):
         _lib.check(self._L.gmm_reserve(self._h, int(max_pop)))
 
+    def reserve_rmsd(self, max_n, atoms):
+        """Pre-size the workspace of bitmask-only ``rmsd_matrix`` calls (``gmm_reserve_rmsd``)."""
+        _lib.check(self._L.gmm_reserve_rmsd(self._h, int(max_n), int(atoms)))
+
     # -- hot path ----------------------------------------------------------------------
     def express(self, torsions=None, xforms=None, rot_alleles=None, out=None):
         """(P, M, 3) float32 device-frame coordinates (add ``self.centre`` for world frame)."""

@@ -8,18 +8,25 @@ from __future__ import annotations
 
 import numpy as np
 
-_engine_for_pairs = None
+_engines_for_pairs = {}
 
 
-def _pair_engine():
-    """A context with a dummy one-atom model, only used for stand-alone RMSD calls."""
-    global _engine_for_pairs
-    if _engine_for_pairs is None:
+def _pair_engine(batch=None, device=None):
+    """The context stand-alone RMSD calls run on: the job's own (first) engine when there is one,
+    else a context with a dummy one-atom model on ``device`` (default: the current CUDA device, so
+    that under one-process-per-GPU launches no rank touches another rank's GPU)."""
+    if batch is not None and batch.engines:
+        return batch.engines[0][0]
+    if device is None:
+        import torch
+        device = torch.cuda.current_device()
+    device = int(device)
+    if device not in _engines_for_pairs:
         from . import model as M
         from .engine import Engine
         mob = M.build_mobile(np.zeros((1, 3)), np.ones(1), np.array([M.F_SEED], np.uint8), np.zeros((0, 2)), [])
-        _engine_for_pairs = Engine(mob, M.empty_receptor(), M.ContactParams(only_internal=True))
-    return _engine_for_pairs
+        _engines_for_pairs[device] = Engine(mob, M.empty_receptor(), M.ContactParams(only_internal=True), device=device)
+    return _engines_for_pairs[device]
 
 
 def rmsd(ind1, ind2, subjects, threshold, *args, **kwargs):
@@ -39,7 +46,7 @@ def rmsd(ind1, ind2, subjects, threshold, *args, **kwargs):
             return False                       # similarity.py:65-66
         centre = c1.mean(axis=0)
         conf = np.stack([c1 - centre, c2 - centre]).astype(np.float32)
-        _, bits = _pair_engine().rmsd_matrix(conf, threshold=threshold, values=False)
+        _, bits = _pair_engine(batch, getattr(env, "device", None)).rmsd_matrix(conf, threshold=threshold, values=False)
         if not bits_to_bool(bits, 2)[0, 1]:
             return False
     return True

@@ -275,8 +275,14 @@ class TensorGA(object):
         return out[:n] + c
 
     @staticmethod
-    def xforms(pop):
-        return np.concatenate([pop["rot"], pop["trans"][:, :, None]], axis=2).reshape(-1, 12)
+    def xforms(pop, precision=0):
+        """(N, 12) products ``T . R`` for ``gmm_express``; with ``Search.precision > 0`` both allele
+        matrices are rounded to that many decimals first (search.py:207-210)."""
+        rot, trans = pop["rot"], pop["trans"]
+        prec = int(precision)
+        if prec > 0:
+            rot, trans = np.around(rot, prec), np.around(trans, prec)
+        return np.concatenate([rot, trans[:, :, None]], axis=2).reshape(-1, 12)
 
     @staticmethod
     def take(pop, idx):
@@ -291,7 +297,7 @@ class TensorGA(object):
         if len(idx) == 0:
             return 0
         sub = self.take(pop, idx)
-        scores, coords = self.evaluate(sub["torsions"], self.xforms(sub), sub["rotamers"])
+        scores, coords = self.evaluate(sub["torsions"], self.xforms(sub, self.spec.get("search_precision", 0)), sub["rotamers"])
         pop["fitness"][idx] = scores
         if pop["coords"] is None:
             pop["coords"] = np.zeros((len(pop["fitness"]),) + coords.shape[1:], dtype=np.float32)
@@ -332,7 +338,7 @@ class TensorGA(object):
             t_poly = np.round(self._poly(t, s["mut_eta"], -half, half, s["mut_indpb"]), s["precision"])
             t_new = np.round(rng.uniform(-half, half, size=t.shape), s["precision"])
             child["torsions"][k] = np.where(poly[:, None], t_poly, t_new)
-            hit = rng.random(len(k)) < s["mut_indpb"]                    # search.py:236
+            hit = rng.random(len(k)) < s.get("search_indpb", s["mut_indpb"])   # search.py:236
             if hit.any():
                 kk = k[hit]
                 f = s.get("interpolation", 0.5)
@@ -342,7 +348,7 @@ class TensorGA(object):
                 child["trans"][kk] = child["trans"][kk] + f * (tgt_t - child["trans"][kk])
             if child["rotamers"].shape[1]:
                 r = child["rotamers"][k]
-                resample = rng.random(r.shape) < s["mut_indpb"]          # rotamers.py:163
+                resample = rng.random(r.shape) < s.get("rotamers_indpb", s["mut_indpb"])   # rotamers.py:163
                 child["rotamers"][k] = np.where(resample, rng.random(r.shape), r)
             child["fitness"][k] = np.nan
         return child
@@ -437,7 +443,15 @@ def launch(cfg, device=0, seed=None):
         "n_torsions": batch.n_torsions,
         "flexibility": tors.flexibility if tors is not None else 360.0,
         "precision": tors.precision if tors is not None else 1,
-        "cx_eta": float(cfg.ga.cx_eta), "mut_eta": float(cfg.ga.mut_eta), "mut_indpb": float(cfg.ga.mut_indpb),
+        # the gene instances carry the job-wide ga.* values unless their own YAML block overrides them
+        # (plugin.load_plugins passes both; gaudi/genes/__init__.py:70-80)
+        "cx_eta": tors.cxeta if tors is not None else float(cfg.ga.cx_eta),
+        "mut_eta": tors.mteta if tors is not None else float(cfg.ga.mut_eta),
+        "mut_indpb": tors.indpb if tors is not None else float(cfg.ga.mut_indpb),
+        "search_indpb": search.indpb if search is not None else float(cfg.ga.mut_indpb),
+        "rotamers_indpb": (template.genes[batch.rotamer_name].indpb if batch.rotamer_name
+                           else float(cfg.ga.mut_indpb)),
+        "search_precision": search.precision if search is not None else 0,
         "search_center": search.center if search is not None else batch.centre,
         "search_radius": search.radius if search is not None else 0.0,
         "rotate": search.rotate if search is not None else False,

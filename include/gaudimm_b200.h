@@ -69,6 +69,11 @@ int         gmm_version(void);
 /* Pre-size the context's scratch for populations up to max_pop (optional). */
 int         gmm_reserve(gmm_ctx* ctx, int max_pop);
 
+/* Pre-size the workspace of bitmask-only gmm_rmsd_matrix calls (re-centred fp16 copies of the
+ * conformers and their norms) for up to max_n conformers of `atoms` atoms (optional).  Without it
+ * the first such call at a larger size synchronises the device and allocates, like the scratch. */
+int         gmm_reserve_rmsd(gmm_ctx* ctx, int max_n, int atoms);
+
 /* Static model (host pointers, uploaded once) ------------------------------------ */
 
 /* The atoms whose coordinates depend on the genome.  Replaces the live chimera.Molecule
@@ -134,7 +139,9 @@ int gmm_express(gmm_ctx* ctx, int P, const double* torsion_deg_d, const double* 
  * expressed individuals.
  *   xyz_d        [P, M, 3] fp32 device-frame coordinates of the mobile atoms
  *   out_scores_d [P, 2] fp64 = (clashes, hydrophobic), before the caller's round()
- *   out_counts_d [P, 2] int32 = unique (clash, hydrophobic) pairs counted, or NULL */
+ *   out_counts_d [P, 2] int32 = unique (clash, hydrophobic) pairs counted, or NULL
+ * A pose whose staging copy has not landed after two seconds (never seen; the wait is bounded so
+ * that a fault cannot hang the GPU) gets NaN scores and counts of -1 instead of stopping the context. */
 int gmm_contacts(gmm_ctx* ctx, int P, const float* xyz_d, double* out_scores_d,
                  int32_t* out_counts_d, void* stream);
 

@@ -23,41 +23,52 @@ def test_static_scratch_evaluate_matches_regular_evaluate(built_lib):
     from gaudi_b200 import _lib
     from gaudi_b200.engine import Engine
 
-    params = M.ContactParams()
     lig = synth.make_ligand(40, 10, seed=1)
-    rec = synth.make_receptor(3000, seed=2, params=params)
-    eng = Engine(lig, rec, params, device=0)
-    dev = eng.torch_device
-    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    dev = torch.device("cuda", 0)
 
-    def static_eval(tors, xf):
-        t = torch.as_tensor(tors).to(dev)
-        x = torch.as_tensor(xf).to(dev)
-        scores = torch.full((t.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
-        counts = torch.full((t.shape[0], 2), -1, dtype=torch.int32, device=dev)
-        _lib.check(built_lib.gmm_evaluate_static(eng._h, t.shape[0], C.c_void_p(t.data_ptr()),
-                                                 C.c_void_p(x.data_ptr()), None,
-                                                 C.c_void_p(scores.data_ptr()), C.c_void_p(counts.data_ptr()),
-                                                 stream))
+    def free_bytes():
         torch.cuda.synchronize()
-        return scores.cpu().numpy(), counts.cpu().numpy()
+        return torch.cuda.mem_get_info(dev)[0]
 
-    for seed, pop in ((31, 1500), (32, 700)):          # two calls in a row, second one smaller
-        tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=seed)
-        want_s, want_c, _ = eng.evaluate(tors, xf)
-        got_s, got_c = static_eval(tors, xf)
-        want_s = want_s.cpu().numpy()
-        # same tolerance as tests/test_gpu_parity.py (the sums are integer, so in fact equal)
-        assert np.all(np.abs(got_s - want_s) <= 1e-4 * np.maximum(1.0, np.abs(want_s)))
-        assert np.array_equal(got_c, want_c.cpu().numpy())
-        assert np.isfinite(got_s).all() and (np.abs(got_s).sum() > 0)
+    # Two Contacts paths use the built-in array differently: the default one-kernel path parks only
+    # the expressed coordinates there, the tiled path (GMM_OPT_TILED) also its per-individual zone
+    # bitmask and partial sums.  Both are checked, each on two calls in a row with different
+    # populations, so that data left behind by the first cannot pass for the second.
+    for params, n_rec, pops, too_big in ((M.ContactParams(), 3000, ((31, 1500), (32, 700)), 200000),
+                                         (M.ContactParams(tiled=True), 5000, ((33, 4096), (34, 1000)), 20000)):
+        rec = synth.make_receptor(n_rec, seed=2, params=params)
+        eng = Engine(lig, rec, params, device=0)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for seed, pop in pops:
+            tors, xf = synth.make_alleles(pop, lig.n_allele_torsions, seed=seed)
+            want_s, want_c, _ = eng.evaluate(tors, xf)
+            # inputs and outputs are the caller's: allocate them first, then watch the driver's
+            # free-memory figure across the call itself (torch's caching allocator does not
+            # return memory to the driver in between, so any drop would be the library's)
+            t = torch.as_tensor(tors).to(dev)
+            x = torch.as_tensor(xf).to(dev)
+            scores = torch.full((pop, 2), float("nan"), dtype=torch.float64, device=dev)
+            counts = torch.full((pop, 2), -1, dtype=torch.int32, device=dev)
+            before = free_bytes()
+            _lib.check(built_lib.gmm_evaluate_static(eng._h, pop, C.c_void_p(t.data_ptr()), C.c_void_p(x.data_ptr()),
+                                                     None, C.c_void_p(scores.data_ptr()), C.c_void_p(counts.data_ptr()),
+                                                     stream))
+            assert free_bytes() == before, "gmm_evaluate_static changed the amount of free device memory"
+            got_s, got_c = scores.cpu().numpy(), counts.cpu().numpy()
+            want_s = want_s.cpu().numpy()
+            # same tolerance as tests/test_gpu_parity.py (the sums are integer, so in fact equal)
+            assert np.all(np.abs(got_s - want_s) <= 1e-4 * np.maximum(1.0, np.abs(want_s)))
+            assert np.array_equal(got_c, want_c.cpu().numpy())
+            assert np.isfinite(got_s).all() and (np.abs(got_s).sum() > 0)
 
-    # a population that does not fit the built-in 16 MiB is refused, loudly, without allocating
-    big = 200000
-    t = torch.zeros((big, lig.n_allele_torsions), dtype=torch.float64, device=dev)
-    x = torch.zeros((big, 12), dtype=torch.float64, device=dev)
-    s = torch.zeros((big, 2), dtype=torch.float64, device=dev)
-    rc = built_lib.gmm_evaluate_static(eng._h, big, C.c_void_p(t.data_ptr()), C.c_void_p(x.data_ptr()), None,
-                                       C.c_void_p(s.data_ptr()), None, stream)
-    assert rc == _lib.GMM_ELIMIT
-    assert b"built-in buffer" in built_lib.gmm_last_error()
+        # a population that does not fit the built-in 16 MiB is refused, loudly, without allocating
+        t = torch.zeros((too_big, lig.n_allele_torsions), dtype=torch.float64, device=dev)
+        x = torch.zeros((too_big, 12), dtype=torch.float64, device=dev)
+        s = torch.zeros((too_big, 2), dtype=torch.float64, device=dev)
+        before = free_bytes()
+        rc = built_lib.gmm_evaluate_static(eng._h, too_big, C.c_void_p(t.data_ptr()), C.c_void_p(x.data_ptr()), None,
+                                           C.c_void_p(s.data_ptr()), None, stream)
+        assert rc == _lib.GMM_ELIMIT
+        assert b"built-in buffer" in built_lib.gmm_last_error()
+        assert free_bytes() == before
+        eng.close()
