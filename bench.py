@@ -517,43 +517,16 @@ def rotamers_measurement(torch, dev, timed):
     (the reference takes them from Chimera's Dunbrack library, which is not available here)."""
     import random
     import golden_util as G
-    from gaudi_b200 import base, parse
-    rng = np.random.default_rng(5)
-    prot, lig = G.load("5er1_protein_mol2"), G.load("5er1_ligand_mol2")
-    d = np.linalg.norm(prot.xyz[:, None, :] - lig.xyz[None, ::4, :], axis=2).min(axis=1)
-    near = []
-    for a in np.argsort(d):
-        r, nm = int(prot.resseq[a]), prot.resname[a][:3].upper()
-        if nm not in ("ALA", "GLY", "PRO") and r not in near:
-            near.append(r)
-        if len(near) == 12:
-            break
-    library = {nm: rng.uniform(-180, 180, size=(int(rng.integers(3, 82)), 4)).tolist()
-               for nm in set(prot.resname[a][:3].upper() for a in range(prot.n_atoms))}
-    cfg = parse.Settings({
-        "output": {"verbose": False},
-        "genes": [{"name": "Protein", "module": "gaudi_b200.genes.molecule", "path": "5er1_protein.mol2", "mol": prot},
-                  {"name": "Ligand", "module": "gaudi_b200.genes.molecule", "path": "5er1_ligand.mol2", "mol": lig},
-                  {"name": "Rotamers", "module": "gaudi_b200.genes.rotamers",
-                   "residues": [("Protein", str(r)) for r in near], "library": library},
-                  {"name": "Torsion", "module": "gaudi_b200.genes.torsion", "target": "Ligand"},
-                  {"name": "Search", "module": "gaudi_b200.genes.search", "target": "Ligand/1", "radius": 3.0}],
-        "objectives": [{"name": "Clashes", "module": "gaudi_b200.objectives.contacts", "which": "clashes",
-                        "probes": ["Ligand"], "radius": 5.0, "weight": -1.0},
-                       {"name": "Contacts", "module": "gaudi_b200.objectives.contacts", "which": "hydrophobic",
-                        "probes": ["Ligand"], "radius": 5.0, "weight": -1.0}]})
+    from gaudi_b200 import base
+    cfg, _ = G.configs4_job(12, seed=5)
+    lig = cfg.genes[1]["mol"]
     random.seed(5)
     template = base.MolecularIndividual(cfg)
     env = base.Environment(cfg, device=dev.index or 0)
     batch = env.attach(template)
     eng = batch.engines[0][0]
     pop = 32768
-    tors = np.round(rng.uniform(-180, 180, size=(pop, batch.n_torsions)), 1)
-    from gaudi_b200 import synth
-    centre = np.asarray(template.genes["Search"].center)
-    xf = np.concatenate([synth.random_rotations(pop, rng),
-                         synth.random_points_in_sphere(pop, centre, 3.0, rng)[:, :, None]], axis=2).reshape(pop, 12)
-    rot = rng.random((pop, batch.n_rot_res))
+    tors, xf, rot = G.configs4_alleles(batch, template, pop, seed=5)
     t_d, x_d, r_d = (torch.as_tensor(v).to(dev) for v in (tors, xf, rot))
     eng.set_profiling(True)
     ms = timed(lambda: eng.evaluate(t_d, x_d, r_d), 10)

@@ -166,8 +166,11 @@ int gmm_evaluate_host(gmm_ctx* ctx, int P, const double* torsion_deg_h, const do
  * context's cudaMalloc'ed buffer: the call never calls cudaMalloc/cudaFree.
  *   - populations whose scratch need exceeds 16 MiB are refused with GMM_ELIMIT (the message
  *     states both sizes); split them into smaller batches;
- *   - the first call on each device looks the array's device address up (one-time set-up);
- *     make that first call before starting any stream capture;
+ *   - the first call on each device looks the array's device address up (one-time set-up, guarded
+ *     by a lock so that host threads may race to it); with CUDA's lazy module loading that is also
+ *     the moment the driver places the 16 MiB array on that GPU, so free device memory drops by
+ *     about that much once, there, and never afterwards; make that first call before starting
+ *     any stream capture;
  *   - all calls, from every context on that device, share the one array: calls that overlap on
  *     the GPU (different streams) race with each other; on one stream they are safe.  Nothing
  *     in it has to be zero on entry (every word is written before it is read). */

@@ -30,6 +30,8 @@ def test_static_scratch_evaluate_matches_regular_evaluate(built_lib):
         torch.cuda.synchronize()
         return torch.cuda.mem_get_info(dev)[0]
 
+    first_call_on_device = True
+
     # Two Contacts paths use the built-in array differently: the default one-kernel path parks only
     # the expressed coordinates there, the tiled path (GMM_OPT_TILED) also its per-individual zone
     # bitmask and partial sums.  Both are checked, each on two calls in a row with different
@@ -53,7 +55,16 @@ def test_static_scratch_evaluate_matches_regular_evaluate(built_lib):
             _lib.check(built_lib.gmm_evaluate_static(eng._h, pop, C.c_void_p(t.data_ptr()), C.c_void_p(x.data_ptr()),
                                                      None, C.c_void_p(scores.data_ptr()), C.c_void_p(counts.data_ptr()),
                                                      stream))
-            assert free_bytes() == before, "gmm_evaluate_static changed the amount of free device memory"
+            drop = before - free_bytes()
+            if first_call_on_device:
+                # the one-time set-up: with CUDA's lazy module loading the driver places the library's
+                # built-in array on the GPU when it is first touched (its 16 MiB plus the module's
+                # code, never more than a few MiB); this is the cost the header says every GPU
+                # that uses the library carries, paid once
+                assert 0 <= drop <= (16 << 20) + (8 << 20), drop
+                first_call_on_device = False
+            else:
+                assert drop == 0, "gmm_evaluate_static changed the amount of free device memory by %d bytes" % drop
             got_s, got_c = scores.cpu().numpy(), counts.cpu().numpy()
             want_s = want_s.cpu().numpy()
             # same tolerance as tests/test_gpu_parity.py (the sums are integer, so in fact equal)
