@@ -98,19 +98,33 @@ def ea_mu_plus_lambda(population, toolbox, mu, lambda_, cxpb, mutpb, ngen, cfg=N
     return population, logbook
 
 
-def launch(cfg, device=0, seed=None):
+def launch(cfg, device=0, seed=None, group=None):
     """gaudi/cli/gaudi_run.py:69-134 for the B200 path: build population and environment,
-    register the DEAP-style aliases plus the batched ``map``, run the loop."""
-    from . import base, plugin
+    register the DEAP-style aliases plus the batched ``map``, run the loop.
+
+    Several GPUs: start one process per GPU (``torchrun``), initialise ``torch.distributed`` and call
+    ``launch`` in every process with its own ``device``.  Rank 0 runs the GA and returns
+    ``(population, logbook, elite)``; the other ranks evaluate their share of every
+    ``toolbox.map(toolbox.evaluate, ...)`` call and return ``(None, None, None)`` when rank 0 is done.
+    Results are identical to a single-GPU run with the same seed."""
+    from . import base, parallel, plugin
     if seed is not None:
         random.seed(seed)
     plugin.import_plugins(*cfg.genes)
     plugin.import_plugins(*cfg.objectives)
     toolbox = deaplite.Toolbox()
-    population = [base.MolecularIndividual(cfg) for _ in range(cfg.ga.population)]
-    environment = base.Environment(cfg, device=device)
+    world, rank = parallel._world(group) if group is not False else (1, 0)
+    environment = base.Environment(cfg, device=device, group=group)
     cfg._environment = environment
+    if rank != 0:
+        environment.attach(base.MolecularIndividual(cfg))
+        environment.batch.enable_sharding(cfg.ga.population + int(cfg.ga.lambda_ * cfg.ga.population))
+        environment.batch.serve()
+        environment.batch.close()
+        return None, None, None
+    population = [base.MolecularIndividual(cfg) for _ in range(cfg.ga.population)]
     environment.attach(population[0])
+    environment.batch.enable_sharding(cfg.ga.population + int(cfg.ga.lambda_ * cfg.ga.population))
     toolbox.register("evaluate", environment.evaluate)
     toolbox.register("mate", lambda a, b: a.mate(b))
     toolbox.register("mutate", lambda ind, indpb: ind.mutate(indpb), indpb=cfg.ga.mut_indpb)
@@ -140,4 +154,5 @@ def launch(cfg, device=0, seed=None):
     population, log = ea_mu_plus_lambda(population, toolbox, mu=mu, lambda_=lambda_, cxpb=cfg.ga.cx_pb,
                                         mutpb=cfg.ga.mut_pb, ngen=cfg.ga.generations, cfg=cfg,
                                         halloffame=elite, verbose=cfg.output.verbose, environment=environment)
+    environment.batch.shutdown()
     return population, log, elite

@@ -130,10 +130,16 @@ def expressed(*individuals):
 
 
 class Environment(object):
-    def __init__(self, cfg=None, device=0, **kwargs):
+    """``device``: the GPU of this process.  Under a one-process-per-GPU launch (``torchrun``;
+    ``torch.distributed`` initialised with more than one rank) the batched evaluate is sharded by
+    individual over the ranks (``gaudi_b200.parallel.HostSharded``): the GA runs on rank 0, the other
+    ranks sit in ``BatchEvaluator.serve()``; pass ``group=False`` to keep a process on its own."""
+
+    def __init__(self, cfg=None, device=0, group=None, **kwargs):
         self.objectives = OrderedDict()
         self.cfg = cfg
         self.device = device
+        self.group = group
         self.batch = None
         if cfg is not None:
             self.weights = cfg.weights
@@ -142,7 +148,7 @@ class Environment(object):
 
     def attach(self, template):
         """Build the GPU model from one (template) individual; called once per job."""
-        self.batch = BatchEvaluator(template, self, device=self.device)
+        self.batch = BatchEvaluator(template, self, device=self.device, group=self.group)
         return self.batch
 
     def evaluate(self, individual):
@@ -162,10 +168,12 @@ class Environment(object):
 class BatchEvaluator(object):
     """Static model + GPU context(s) for one job, and the batched evaluate."""
 
-    def __init__(self, template, environment, device=0):
+    def __init__(self, template, environment, device=0, group=None):
         from .engine import Engine
         self.environment = environment
         self.device = device
+        self.group = group
+        self.sharded = None
         genes = template.genes
         self.torsion_name = next((n for n, g in genes.items() if g.__class__.__name__ == "Torsion"), None)
         self.search_name = next((n for n, g in genes.items() if g.__class__.__name__ == "Search"), None)
@@ -348,6 +356,73 @@ class BatchEvaluator(object):
                 rot[p] = ind.genes[self.rotamer_name].allele
         return tors, xf, rot
 
+    # ---- scoring of allele arrays ----------------------------------------------------------
+    def score_arrays(self, tors, xf, rot):
+        """This process's GPU: raw objective columns ``(P, n_obj)`` fp64 (before the caller's
+        ``round``) and device-frame coordinates ``(P, M, 3)`` float32 for allele arrays."""
+        P = len(tors)
+        objectives = list(self.environment.objectives.values())
+        raw = np.zeros((P, len(objectives)))
+        xyz = None
+        for eng, members in self.engines:
+            scores, _, coords = eng.evaluate_host(tors if self.n_torsions else np.zeros((P, 0)),
+                                                  xf if self.search_name else None,
+                                                  rot if self.n_rot_res else None, want_xyz=xyz is None)
+            if coords is not None:
+                xyz = coords
+            for i, col in members:
+                raw[:, i] = scores[:, col]
+        if self.geometry:
+            geo = self.engines[0][0].geometry(xyz).cpu().numpy()
+            for col, (i, o) in enumerate(self.geometry):
+                raw[:, i] = geo[:, col]
+        return raw, xyz
+
+    def enable_sharding(self, max_pop):
+        """One-process-per-GPU launches: build the shared, page-locked population table (collective:
+        every rank calls it with the same ``max_pop``).  No-op on a single process."""
+        from . import parallel
+        world, _ = parallel._world(self.group) if self.group is not False else (1, 0)
+        if world == 1 or self.sharded is not None:
+            return
+        spec = OrderedDict()
+        spec["tors"] = ((self.n_torsions,), np.float64)
+        spec["xforms"] = ((12,), np.float64)
+        spec["rot"] = ((self.n_rot_res,), np.float64)
+        spec["raw"] = ((len(self.environment.objectives),), np.float64)
+        spec["xyz"] = ((self.mobile.n_atoms, 3), np.float32)
+        self.sharded = parallel.HostSharded(spec, max_pop, self.group)
+
+    def _score_block(self, lo, hi):
+        a = self.sharded.arrays
+        raw, xyz = self.score_arrays(a["tors"][lo:hi], a["xforms"][lo:hi], a["rot"][lo:hi])
+        a["raw"][lo:hi] = raw
+        a["xyz"][lo:hi] = xyz
+
+    def score_population(self, tors, xf, rot):
+        """``score_arrays`` over every GPU of the job (rank 0 calls this, the others ``serve``)."""
+        if self.sharded is None:
+            return self.score_arrays(tors, xf, rot)
+        a, P = self.sharded.arrays, len(tors)
+        if P > self.sharded.max_rows:
+            raise ValueError("population of %d exceeds the sharded table (%d rows)" % (P, self.sharded.max_rows))
+        if self.n_torsions:
+            a["tors"][:P] = tors
+        if xf is not None:
+            a["xforms"][:P] = xf
+        if rot is not None and self.n_rot_res:
+            a["rot"][:P] = rot
+        self.sharded.run(P, self._score_block)
+        return a["raw"][:P], a["xyz"][:P]
+
+    def serve(self):
+        """Ranks other than 0: evaluate blocks of rank 0's populations until it shuts the job down."""
+        self.sharded.serve(self._score_block)
+
+    def shutdown(self):
+        if self.sharded is not None:
+            self.sharded.shutdown()
+
     def evaluate(self, individuals):
         """Batched ``Environment.evaluate``: list of rounded score lists, in objective order
         (``round(score, obj.precision)``, gaudi/base.py:361)."""
@@ -355,21 +430,9 @@ class BatchEvaluator(object):
             return []
         tors, xf, rot = self.pack(individuals)
         objectives = list(self.environment.objectives.values())
-        out = [[None] * len(objectives) for _ in individuals]
-        xyz = None
-        for eng, members in self.engines:
-            scores, _, coords = eng.evaluate_host(tors if self.n_torsions else np.zeros((len(individuals), 0)),
-                                                  xf, rot, want_xyz=xyz is None)
-            if coords is not None:
-                xyz = coords
-            for p in range(len(individuals)):
-                for i, col in members:
-                    out[p][i] = round(float(scores[p, col]), objectives[i].precision)
-        if self.geometry:
-            geo = self.engines[0][0].geometry(xyz).cpu().numpy()
-            for p in range(len(individuals)):
-                for col, (i, o) in enumerate(self.geometry):
-                    out[p][i] = round(float(geo[p, col]), o.precision)
+        raw, xyz = self.score_population(tors, xf, rot)
+        out = [[round(float(raw[p, i]), objectives[i].precision) for i in range(len(objectives))]
+               for p in range(len(individuals))]
         # post_express (gaudi/base.py:301-303): every Molecule gene gets its expressed, world-frame
         # coordinates.  Molecules without mobile atoms share one array (the reference copies the
         # whole protein on every evaluation); molecules with flexible side chains get a copy with
@@ -441,5 +504,8 @@ class BatchEvaluator(object):
         return bool(k < len(row) and row[k] == b)
 
     def close(self):
+        if self.sharded is not None:
+            self.sharded.close()
+            self.sharded = None
         for eng, _ in self.engines:
             eng.close()

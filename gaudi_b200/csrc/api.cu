@@ -97,6 +97,7 @@ int gmm_create(gmm_ctx** out, int device) {
 
 int gmm_destroy(gmm_ctx* c) {
     if (!c) return GMM_OK;
+    gmm_exchange_destroy(c);
     DeviceGuard g(c->device);
     cudaDeviceSynchronize();
     release(c->d_xyz0); release(c->d_mflags_atom); release(c->d_tfixed); release(c->d_tmoving);

@@ -214,6 +214,7 @@ struct gmm_ctx {
     void* h_pin = nullptr; size_t pin_bytes = 0;
     void* d_stage = nullptr; size_t stage_bytes = 0;
     void* d_rmsd_ws = nullptr; size_t rmsd_ws_bytes = 0;   // centred conformers + norms (rmsd.cu, bitmask path)
+    void* exchange = nullptr;        // gmm::Exchange (exchange.cu): fitness exchange with the other ranks' GPUs
 };
 
 namespace gmm {

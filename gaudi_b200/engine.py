@@ -149,12 +149,13 @@ class Engine(object):
         return scores, cnt, xyz
 
     def evaluate_host(self, torsions=None, xforms=None, rot_alleles=None, want_xyz=False,
-                      scores_out=None, counts_out=None):
+                      scores_out=None, counts_out=None, xyz_out=None):
         """Host buffers in, host buffers out (H2D + kernels + D2H inside the call).
 
         Inputs may be numpy arrays or CPU torch tensors; page-locked ones
         (``torch.empty(..., pin_memory=True)``) are copied from directly, pageable ones are
-        staged.  ``scores_out`` / ``counts_out``: optional preallocated (pinned) CPU tensors."""
+        staged.  ``scores_out`` / ``counts_out`` / ``xyz_out``: optional preallocated (pinned) CPU
+        tensors or numpy arrays (for instance rows of a ``parallel.HostSharded`` table)."""
         def host(a):
             if a is None:
                 return None, None
@@ -173,8 +174,9 @@ class Engine(object):
             counts_out = np.empty((P, 2), np.int32)
         sp = C.c_void_p(scores_out.data_ptr()) if isinstance(scores_out, torch.Tensor) else _np_ptr(scores_out)
         cp = C.c_void_p(counts_out.data_ptr()) if isinstance(counts_out, torch.Tensor) else _np_ptr(counts_out)
-        xyz = np.empty((P, self.mobile.n_atoms, 3), np.float32) if want_xyz else None
-        _lib.check(self._L.gmm_evaluate_host(self._h, P, tp, xp, rp, _np_ptr(xyz), sp, cp, self._stream()))
+        xyz = xyz_out if xyz_out is not None else (np.empty((P, self.mobile.n_atoms, 3), np.float32) if want_xyz else None)
+        xyzp = C.c_void_p(xyz.data_ptr()) if isinstance(xyz, torch.Tensor) else _np_ptr(xyz)
+        _lib.check(self._L.gmm_evaluate_host(self._h, P, tp, xp, rp, xyzp, sp, cp, self._stream()))
         return scores_out, counts_out, xyz
 
     def rmsd_matrix(self, xyz, row0=0, row1=None, threshold=2.5, values=True, bits=True):

@@ -89,3 +89,278 @@ def sharded_rmsd_bits(rmsd_rows, coords, group=None, counts=None):
     if even:
         return allb
     return torch.cat([allb[r * m:r * m + counts[r]] for r in range(world)])
+
+
+# ---------------------------------------------------------------------------------------------
+# Fitness exchange through peer memory (gmm_exchange_*): the all-gather without a collective
+# ---------------------------------------------------------------------------------------------
+def _world(group=None):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group), dist.get_rank(group)
+    return 1, 0
+
+
+def tensor_from_pointer(ptr, shape, dtype, device):
+    """Zero-copy torch view of device memory owned by the library (``__cuda_array_interface__``)."""
+    typestr = {torch.float64: "<f8", torch.int32: "<i4", torch.float32: "<f4"}[dtype]
+    holder = type("DevicePointer", (), {})()
+    holder.__cuda_array_interface__ = {"shape": tuple(int(s) for s in shape), "typestr": typestr,
+                                       "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(holder, device=device)
+
+
+class FitnessExchange(object):
+    """Every rank's ``[n, 2]`` score rows (and pair counts) land in every rank's copy of the
+    ``[max_rows, 2]`` fitness table: one small kernel per step that stores through CUDA-IPC peer
+    mappings, publishes an epoch flag and waits for the other ranks' flags (csrc/exchange.cu).  The
+    process group is used once, at construction, to pass the IPC handles around; a step contains no
+    collective call and can be replayed from a CUDA graph."""
+
+    def __init__(self, engine, max_rows, group=None):
+        import ctypes as C
+        from . import _lib
+        self.engine, self.group, self.max_rows = engine, group, int(max_rows)
+        self.world, self.rank = _world(group)
+        self._L, self._C = _lib.lib(), C
+        handle = (C.c_ubyte * 64)()
+        _lib.check(self._L.gmm_exchange_create(engine._h, self.world, self.rank, self.max_rows, handle))
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle), group=group)
+            blob = (C.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(handles))
+            _lib.check(self._L.gmm_exchange_connect(engine._h, blob))
+            dist.barrier(group=group)           # every rank has mapped every block before anyone publishes
+
+    def _views(self, ps, pc):
+        dev = self.engine.torch_device
+        return (tensor_from_pointer(ps.value, (self.max_rows, 2), torch.float64, dev),
+                tensor_from_pointer(pc.value, (self.max_rows, 2), torch.int32, dev))
+
+    def publish(self, scores, counts, row0):
+        """Enqueue the exchange of this rank's rows on torch's current stream; returns the
+        ``(scores [max_rows, 2], counts [max_rows, 2])`` views that hold every rank's rows once the
+        kernel has run (valid until this rank's publish after next)."""
+        from . import _lib
+        C = self._C
+        ps, pc = C.c_void_p(), C.c_void_p()
+        _lib.check(self._L.gmm_exchange_publish(
+            self.engine._h, C.c_void_p(scores.data_ptr()), C.c_void_p(counts.data_ptr()) if counts is not None else None,
+            int(row0), int(scores.shape[0]), C.byref(ps), C.byref(pc), self.engine._stream()))
+        return self._views(ps, pc)
+
+    def state(self):
+        """Synchronise; ``(epochs completed, timed_out, scores view, counts view)`` of the last epoch."""
+        from . import _lib
+        C = self._C
+        epoch, err, ps, pc = C.c_uint(0), C.c_int(0), C.c_void_p(), C.c_void_p()
+        _lib.check(self._L.gmm_exchange_state(self.engine._h, C.byref(epoch), C.byref(err), C.byref(ps), C.byref(pc)))
+        s, c = self._views(ps, pc)
+        return int(epoch.value), bool(err.value), s, c
+
+    def close(self):
+        self._L.gmm_exchange_destroy(self.engine._h)
+
+
+class ShardedEvaluator(object):
+    """Population sharded by individual over the ranks of one node, device-resident alleles:
+    rank r evaluates rows ``[bounds[r], bounds[r + 1])`` of the population and every rank ends up
+    with the whole ``[P, 2]`` fitness table (rank 0 runs NSGA-II selection,
+    gaudi/algorithms.py:160).  ``exchange``: ``"peer"`` (default: stores through peer memory,
+    :class:`FitnessExchange`) or ``"nccl"`` (``all_gather_into_tensor``; the cross-check)."""
+
+    def __init__(self, engine, population, group=None, exchange="peer"):
+        self.engine, self.group, self.population = engine, group, int(population)
+        self.world, self.rank = _world(group)
+        self.bounds = shard_bounds(self.population, self.world)
+        self.lo, self.hi = self.bounds[self.rank], self.bounds[self.rank + 1]
+        self.max_shard = max_shard(self.population, self.world)
+        dev = engine.torch_device
+        self.scores = torch.zeros((self.max_shard, 2), dtype=torch.float64, device=dev)
+        self.counts = torch.zeros((self.max_shard, 2), dtype=torch.int32, device=dev)
+        engine.reserve(self.max_shard)
+        self.kind = exchange if self.world > 1 else "none"
+        self.exchange = FitnessExchange(engine, self.population, group) if self.kind == "peer" else None
+        if self.kind == "nccl":
+            self._gs = torch.empty((self.world * self.max_shard, 2), dtype=torch.float64, device=dev)
+            self._gc = torch.empty((self.world * self.max_shard, 2), dtype=torch.int32, device=dev)
+
+    def shard(self, a):
+        """This rank's rows of a population-sized array (or None)."""
+        return None if a is None else a[self.lo:self.hi]
+
+    def evaluate(self, torsions=None, xforms=None, rot_alleles=None):
+        """``torsions / xforms / rot_alleles``: THIS rank's rows, on the device.  Returns
+        ``(scores [P, 2] fp64, counts [P, 2] int32)`` with every rank's rows, on every rank."""
+        n = self.hi - self.lo
+        s, c = self.scores[:n], self.counts[:n]
+        self.engine.evaluate(torsions, xforms, rot_alleles, scores_out=s, counts_out=c)
+        if self.kind == "none":
+            return s, c
+        if self.kind == "peer":
+            gs, gc = self.exchange.publish(s, c, self.lo)
+            return gs[:self.population], gc[:self.population]
+        dist.all_gather_into_tensor(self._gs, self.scores, group=self.group)
+        dist.all_gather_into_tensor(self._gc, self.counts, group=self.group)
+        m, b = self.max_shard, self.bounds
+        if all(b[r + 1] - b[r] == m for r in range(self.world)):
+            return self._gs, self._gc
+        return (torch.cat([self._gs[r * m:r * m + b[r + 1] - b[r]] for r in range(self.world)]),
+                torch.cat([self._gc[r * m:r * m + b[r + 1] - b[r]] for r in range(self.world)]))
+
+    def close(self):
+        if self.exchange is not None:
+            self.exchange.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# Host-resident populations on several GPUs: one page-locked table shared by the ranks
+# ---------------------------------------------------------------------------------------------
+class HostSharded(object):
+    """The GA lives in ONE process (rank 0: DEAP-style selection, variation and niching are
+    sequential host code, gaudi/algorithms.py:54-202); its allele and fitness tables live in a
+    shared-memory segment that every rank maps and page-locks (``cudaHostRegister``).  A step is
+    then: rank 0 raises the epoch; every rank copies ITS rows host-to-device over its own PCIe
+    link, evaluates them, and copies its results device-to-host into the same table; rank 0 waits
+    for the ranks' done marks and reads the whole table.  No allele or score crosses NVLink, and
+    the upload runs on ``world`` PCIe links in parallel instead of through rank 0's.
+
+    ``spec``: ordered ``name -> (trailing shape, numpy dtype)``; ``self.arrays[name]`` is the
+    ``[max_rows, ...]`` table.  ``run(n_rows, fn)`` is collective: every rank calls it (ranks other
+    than 0 usually through ``serve``), and ``fn(lo, hi)`` runs on each rank with a non-empty block.
+    The process group is used at construction only (segment name, barrier)."""
+
+    HEADER = 64     # int64 slots: 0 epoch, 1 n_rows, 2 shutdown, 8 + r: last epoch rank r has finished
+
+    def __init__(self, spec, max_rows, group=None, register=True, timeout=120.0):
+        import os
+        import uuid
+        import numpy as np
+        self.group, self.max_rows, self.timeout = group, int(max_rows), float(timeout)
+        self.world, self.rank = _world(group)
+        offsets, at = {}, self.HEADER * 8
+        for name, (shape, dtype) in spec.items():
+            nbytes = int(np.prod((self.max_rows,) + tuple(shape))) * np.dtype(dtype).itemsize
+            offsets[name] = at
+            at += (nbytes + 255) // 256 * 256
+        self.nbytes = max(at, 4096)
+        path = [None]
+        if self.rank == 0:
+            path[0] = "/dev/shm/gaudimm_b200_%s" % uuid.uuid4().hex
+            with open(path[0], "wb") as fh:
+                fh.truncate(self.nbytes)
+        if self.world > 1:
+            dist.broadcast_object_list(path, src=0, group=group)
+        self.path = path[0]
+        self._map = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(self.nbytes,))
+        self.header = self._map[:self.HEADER * 8].view(np.int64)
+        self.arrays = {}
+        for name, (shape, dtype) in spec.items():
+            n = int(np.prod((self.max_rows,) + tuple(shape))) * np.dtype(dtype).itemsize
+            self.arrays[name] = self._map[offsets[name]:offsets[name] + n].view(dtype).reshape((self.max_rows,) + tuple(shape))
+        self._registered = False
+        if register and torch.cuda.is_available():
+            rc = torch.cuda.cudart().cudaHostRegister(self._map.ctypes.data, self.nbytes, 0)
+            if int(rc) != 0:
+                raise RuntimeError("cudaHostRegister of the shared population table failed with code %d" % int(rc))
+            self._registered = True
+        self._seen = 0
+        if self.world > 1:
+            dist.barrier(group=group)
+        if self.rank == 0:
+            os.unlink(self.path)          # the mappings keep the segment alive; nothing is left behind on a crash
+
+    def _wait(self, cond, what):
+        import time
+        t0 = time.perf_counter()
+        spins = 0
+        while not cond():
+            spins += 1
+            if (spins & 0xfff) == 0 and time.perf_counter() - t0 > self.timeout:
+                raise RuntimeError("HostSharded: rank %d waited more than %.0f s for %s" % (self.rank, self.timeout, what))
+
+    def run(self, n_rows, fn):
+        """Collective.  Rank 0's ``n_rows`` counts; returns the row bounds used."""
+        h = self.header
+        if self.rank == 0:
+            if n_rows > self.max_rows:
+                raise ValueError("population of %d rows exceeds the table's %d" % (n_rows, self.max_rows))
+            h[1] = int(n_rows)
+            h[0] = self._seen + 1
+        self._wait(lambda: h[0] > self._seen or h[2] != 0, "rank 0 to start a step")
+        if h[2] != 0:
+            return None
+        self._seen = int(h[0])
+        b = shard_bounds(int(h[1]), self.world)
+        lo, hi = b[self.rank], b[self.rank + 1]
+        if hi > lo:
+            fn(lo, hi)
+        h[8 + self.rank] = self._seen
+        if self.rank == 0:
+            for r in range(1, self.world):
+                self._wait(lambda r=r: h[8 + r] >= self._seen, "rank %d to finish its block" % r)
+        return b
+
+    def serve(self, fn):
+        """Ranks other than 0: take part in rank 0's steps until it calls ``shutdown``."""
+        while self.run(0, fn) is not None:
+            pass
+
+    def shutdown(self):
+        if self.rank == 0:
+            self.header[2] = 1
+
+    def close(self):
+        if self._registered:
+            torch.cuda.synchronize()
+            torch.cuda.cudart().cudaHostUnregister(self._map.ctypes.data)
+            self._registered = False
+
+
+class HostShardedEvaluator(object):
+    """``gmm_evaluate_host`` on several GPUs for a population that lives in rank 0's host memory
+    (the ``toolbox.map(toolbox.evaluate, population)`` seam, gaudi/algorithms.py:99-102): the allele
+    and fitness tables are the page-locked shared tables of :class:`HostSharded`; each rank's
+    ``gmm_evaluate_host`` copies its rows straight out of and into them.
+
+    Rank 0 fills ``tors / xforms / rot`` (numpy views, ``[max_pop, ...]``) and calls
+    ``evaluate(P)``; the other ranks call ``serve()`` (or ``evaluate()`` once per step).  After the
+    call rank 0 reads ``scores[:P]`` / ``counts[:P]`` (and ``xyz[:P]`` when ``want_xyz``)."""
+
+    def __init__(self, engine, max_pop, group=None, want_xyz=False):
+        from collections import OrderedDict
+        import numpy as np
+        m = engine.mobile
+        self.engine, self.want_xyz = engine, bool(want_xyz)
+        spec = OrderedDict()
+        spec["tors"] = ((m.n_allele_torsions,), np.float64)
+        spec["xforms"] = ((12,), np.float64)
+        spec["rot"] = ((m.n_rotamer_residues,), np.float64)
+        spec["scores"] = ((2,), np.float64)
+        spec["counts"] = ((2,), np.int32)
+        if want_xyz:
+            spec["xyz"] = ((m.n_atoms, 3), np.float32)
+        self.table = HostSharded(spec, max_pop, group)
+        for name, arr in self.table.arrays.items():
+            setattr(self, name, arr)
+        self.world, self.rank = self.table.world, self.table.rank
+        engine.reserve(max_shard(int(max_pop), self.world))
+        self.use_xforms = True
+
+    def _block(self, lo, hi):
+        a = self.table.arrays
+        self.engine.evaluate_host(a["tors"][lo:hi], a["xforms"][lo:hi] if self.use_xforms else None,
+                                  a["rot"][lo:hi] if a["rot"].shape[1] else None,
+                                  scores_out=a["scores"][lo:hi], counts_out=a["counts"][lo:hi],
+                                  xyz_out=a["xyz"][lo:hi] if self.want_xyz else None)
+
+    def evaluate(self, n_rows=0):
+        return self.table.run(n_rows, self._block)
+
+    def serve(self):
+        self.table.serve(self._block)
+
+    def shutdown(self):
+        self.table.shutdown()
+
+    def close(self):
+        self.table.close()

@@ -422,20 +422,27 @@ def py_round(a, ndigits):
     return np.array([round(float(v), ndigits) for v in flat]).reshape(np.shape(a))
 
 
-def launch(cfg, device=0, seed=None):
+def launch(cfg, device=0, seed=None, group=None):
     """``gaudi_b200.algorithms.launch`` with the population held as arrays.  Same job description;
     one template individual is instantiated to discover the topology, then the GA never touches
-    per-individual Python objects.  Returns ``(population dict, logbook, BatchEvaluator)``."""
+    per-individual Python objects.  Returns ``(population dict, logbook, BatchEvaluator)``.  Under a
+    one-process-per-GPU launch rank 0 runs the GA, the other ranks evaluate their blocks and return
+    ``(None, None, batch)``, as in ``gaudi_b200.algorithms.launch``."""
     import random
-    from . import base, plugin
+    from . import base, parallel, plugin
     if seed is not None:
         random.seed(seed)
     plugin.import_plugins(*cfg.genes)
     plugin.import_plugins(*cfg.objectives)
     template = base.MolecularIndividual(cfg)
-    env = base.Environment(cfg, device=device)
+    env = base.Environment(cfg, device=device, group=group)
     cfg._environment = env
     batch = env.attach(template)
+    n_pop = cfg.ga.population
+    batch.enable_sharding(n_pop + int(cfg.ga.lambda_ * n_pop))
+    if (parallel._world(group)[1] if group is not False else 0) != 0:
+        batch.serve()
+        return None, None, batch
     tors = template.genes.get(batch.torsion_name) if batch.torsion_name else None
     search = template.genes.get(batch.search_name) if batch.search_name else None
     objectives = list(env.objectives.values())
@@ -460,19 +467,11 @@ def launch(cfg, device=0, seed=None):
     }
 
     def evaluate(t, xf, r):
+        # every GPU of the job when launched one process per GPU (BatchEvaluator.score_population)
+        raw, xyz = batch.score_population(t, xf if search is not None else None, r if batch.n_rot_res else None)
         out = np.empty((len(t), len(objectives)))
-        xyz = None
-        for eng, members in batch.engines:
-            scores, _, coords = eng.evaluate_host(t, xf if search is not None else None,
-                                                  r if batch.n_rot_res else None, want_xyz=xyz is None)
-            if coords is not None:
-                xyz = coords
-            for i, col in members:
-                out[:, i] = py_round(scores[:, col], objectives[i].precision)
-        if batch.geometry:                                   # Distance / Angle restraints (gmm_geometry)
-            geo = batch.engines[0][0].geometry(xyz).cpu().numpy()
-            for col, (i, o) in enumerate(batch.geometry):
-                out[:, i] = py_round(geo[:, col], o.precision)
+        for i, o in enumerate(objectives):
+            out[:, i] = py_round(raw[:, i], o.precision)
         return out, np.ascontiguousarray(xyz[:, batch.lig_slice])
 
     def similarity(coords, threshold):
@@ -487,4 +486,5 @@ def launch(cfg, device=0, seed=None):
     pop = ga.random_population(n)
     mu, lambda_ = int(cfg.ga.mu * n), int(cfg.ga.lambda_ * n)
     pop, log = ga.run(pop, mu, lambda_, cfg.ga.cx_pb, cfg.ga.mut_pb, cfg.ga.generations)
+    batch.shutdown()
     return pop, log, batch

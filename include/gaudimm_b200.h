@@ -56,6 +56,8 @@ extern "C" {
                                      * (the reference's own order of operations) even when the model allows the
                                      * faster kinematic-tree form; results agree to fp64 rounding */
 
+#define GMM_MAX_PEERS          16    /* ranks (GPUs of one node) in a fitness exchange */
+#define GMM_IPC_HANDLE_BYTES   64    /* sizeof(cudaIpcMemHandle_t) */
 #define GMM_MAX_MOBILE_ATOMS   1024
 #define GMM_MAX_TORSIONS       1024
 
@@ -185,6 +187,36 @@ int gmm_evaluate_static(gmm_ctx* ctx, int P, const double* torsion_deg_d, const 
  *   out_similar_d    [row1-row0, ceil(N/32)] uint32 bitmask of NOT(rmsd^2 > thr^2), or NULL */
 int gmm_rmsd_matrix(gmm_ctx* ctx, int N, int A, const float* xyz_d, int row0, int row1,
                     float* out_rmsd_d, uint32_t* out_similar_d, double threshold, void* stream);
+
+/* Multi-GPU: fitness exchange between the GPUs of one node, one process per GPU ------------------
+ * The reference's seam is toolbox.map(toolbox.evaluate, invalid_ind) (gaudi/algorithms.py:99-102,
+ * 133-137; gaudi/cli/gaudi_run.py:97-99, where a multiprocessing pool was once meant to go): the
+ * population is split by individual, every rank scores its block with gmm_evaluate, and the rows
+ * are gathered so that the rank running selection (gaudi/algorithms.py:160) holds them all.
+ *   gmm_exchange_create   allocates this rank's block (room for max_rows = the whole population,
+ *                         twice: two buffers alternate) and returns its CUDA IPC handle;
+ *   gmm_exchange_connect  maps the other ranks' blocks: handles_h = the world handles in rank
+ *                         order, exchanged by the caller (any transport: torch.distributed, MPI,
+ *                         a file); ranks may share one GPU;
+ *   gmm_exchange_publish  enqueues ONE kernel on `stream` that stores this rank's rows
+ *                         [row0, row0 + n_rows) into every rank's block with plain stores through the
+ *                         peer mappings, publishes the epoch and waits (on the GPU, at most 10 s)
+ *                         for every other rank's publish of the same epoch.  No host
+ *                         synchronisation, no allocation: capturable in a CUDA graph.  Every rank
+ *                         must publish the same number of times.  *gathered_*_out: where the rows
+ *                         of THIS call will be once the kernel has run ([max_rows, 2] fp64 scores,
+ *                         [max_rows, 2] int32 counts); valid until this rank's publish after next;
+ *   gmm_exchange_state    synchronises the device; returns the epochs completed, whether a wait
+ *                         ever timed out, and the buffers holding the LAST completed epoch (use it
+ *                         after replaying publishes from a CUDA graph, which the host-side epoch
+ *                         count behind gmm_exchange_publish's out pointers does not see). */
+int gmm_exchange_create(gmm_ctx* ctx, int world, int rank, int max_rows, unsigned char* handle_out /*[64]*/);
+int gmm_exchange_connect(gmm_ctx* ctx, const unsigned char* handles_h /*[world, 64]*/);
+int gmm_exchange_publish(gmm_ctx* ctx, const double* scores_d, const int32_t* counts_d, int row0, int n_rows,
+                         double** gathered_scores_out, int32_t** gathered_counts_out, void* stream);
+int gmm_exchange_state(gmm_ctx* ctx, unsigned* epoch_out, int* error_out, double** gathered_scores_out,
+                       int32_t** gathered_counts_out);
+int gmm_exchange_destroy(gmm_ctx* ctx);
 
 /* 1 when gmm_express / gmm_evaluate use the kinematic-tree form for this model (moving sets nested
  * or disjoint, verified numerically in gmm_set_mobile), 0 when they apply the bond rotations one

@@ -147,6 +147,53 @@ def test_sharded_gather_world2_gloo(tmp_path):
     assert res[1] == 0.0          # row-block sharded similarity bitmask == full matrix
 
 
+def _host_sharded_worker(rank, world, port, out):
+    import torch.distributed as dist
+    from collections import OrderedDict
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    spec = OrderedDict([("x", ((3,), np.float64)), ("y", ((2,), np.float64)), ("who", ((), np.int32))])
+    table = parallel.HostSharded(spec, 50, timeout=30.0)
+    a = table.arrays
+
+    def block(lo, hi):          # stands in for this rank's GPU: a function of its rows only
+        a["y"][lo:hi, 0] = a["x"][lo:hi].sum(axis=1)
+        a["y"][lo:hi, 1] = a["x"][lo:hi, 0] * 2.0
+        a["who"][lo:hi] = rank
+
+    if rank == 0:
+        rng = np.random.default_rng(3)
+        worst, owners = 0.0, []
+        for n in (50, 7, 1, 0, 33):                      # full table, ragged, fewer rows than ranks, empty
+            a["x"][:n] = rng.normal(size=(n, 3))
+            a["y"][:] = np.nan
+            b = table.run(n, block)
+            assert b == parallel.shard_bounds(n, world)
+            want = np.stack([a["x"][:n].sum(axis=1), a["x"][:n, 0] * 2.0], axis=1) if n else np.zeros((0, 2))
+            worst = max(worst, float(np.abs(a["y"][:n] - want).max()) if n else 0.0)
+            owners.append([int(np.sum(a["who"][:n] == r)) for r in range(world)])
+        table.shutdown()
+        np.save(out, np.array([worst] + [float(v) for row in owners for v in row]))
+    else:
+        table.serve(block)                               # returns when rank 0 shuts the job down
+    table.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_host_sharded_table_world2_gloo(tmp_path):
+    """The shared population table behind multi-GPU ``toolbox.map``: rank 0 drives steps, the other
+    rank serves until shutdown; every row is computed by the rank that owns it."""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "hs.npy")
+    port = 31500 + random.randint(0, 2000)
+    mp.spawn(_host_sharded_worker, args=(2, port, out), nprocs=2, join=True)
+    res = np.load(out)
+    assert res[0] == 0.0
+    assert res[1:].reshape(-1, 2).tolist() == [[25, 25], [3, 4], [0, 1], [0, 0], [16, 17]]
+
+
 # ---- tensorised GA bookkeeping (gaudi_b200/tensor_ga.py) against the per-object versions ----------
 def test_tensor_nsga2_matches_deaplite():
     from gaudi_b200 import tensor_ga as TG
