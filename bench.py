@@ -1,20 +1,27 @@
 #!/usr/bin/env python
 """Benchmark of the GaudiMM hot path on B200: individuals scored / s for
-express (Torsion + Search) + Contacts (clashes and hydrophobic), plus RMSD pairs / s.
+express (Torsion + Search [+ Rotamers]) + Contacts (clashes and hydrophobic), plus RMSD pairs / s.
 
     python bench.py --gpus N --steps K --warmup W              # the B200 path (this repo)
     python bench.py --impl reference --gpus N --steps K ...    # the reference's CPU path
+    (N > 1: python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...)
 
-One "step" = one batched evaluate of the whole population (BASELINE.json configs[2]:
-65,536 poses of a 40-atom / 10-torsion ligand against a 20,000-atom receptor box; with N
-GPUs the population is sharded by individual and the fitness vectors are all-gathered).
-Prints ONE JSON line on rank 0.  See DESIGN.md section "Measurement" for every field.
+One "step" = one batched evaluate of the whole population (BASELINE.json configs[2]: 65,536
+poses of a 40-atom / 10-torsion ligand against a 20,000-atom receptor box).  With N GPUs the
+population is sharded by individual through the product's own multi-GPU layer
+(gaudi_b200.parallel.ShardedEvaluator: every rank scores its block, the fitness rows are gathered
+into every rank's table by stores through peer memory — no collective call in the step, the step
+is one CUDA graph at every N; --exchange nccl selects an NCCL all_gather instead).  Prints ONE
+JSON line on rank 0.  Side objects of the same line, at every N: "rmsd" (configs[3], row blocks
+over the ranks, only the partner lists travel) and "configs4" (Rotamers on 12 side chains,
+population 32,768, sharded by individual).  See DESIGN.md section 5 for every field.
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import re
 import sys
 import threading
 import time
@@ -30,9 +37,18 @@ WORKLOADS = {
     "c3": (65536, 40, 10, 20000),   # BASELINE.json configs[2] -- the headline
     "c2": (4096, 40, 10, 5000),     # BASELINE.json configs[1]
 }
-RMSD_N, RMSD_A = 16384, 60          # BASELINE.json configs[3]
+RMSD_N, RMSD_A, RMSD_THR = 16384, 60, 2.5   # BASELINE.json configs[3]; threshold of gaudi/parse.py:279
+C5_POP, C5_RES = 32768, 12          # BASELINE.json configs[4]
 FLOPS_PER_PAIR_TEST = 10
 FLOPS_PER_RMSD_PAIR = 9 * RMSD_A    # 3A FADD + 3A FFMA
+L2_FLUSH_BYTES = 192 * 1024 * 1024  # > 126 MB L2
+
+C3_TEXT = ("configs[2]: pop %d x (%d-atom, %d-torsion ligand) vs %d-atom receptor box, "
+           "Torsion+Search express + Contacts(clashes, hydrophobic)" % WORKLOADS["c3"])
+RMSD_TEXT = ("configs[3]: similarity (gaudi/similarity.py:36-75) of all pairs of %d conformers x %d atoms, threshold %.1f A"
+             % (RMSD_N, RMSD_A, RMSD_THR))
+C5_TEXT = ("configs[4]: Rotamers gene on %d flexible side chains + Torsion + Search + Contacts(clashes, hydrophobic), "
+           "pop %d, 5er1 test complex" % (C5_RES, C5_POP))
 
 
 def build_system(name):
@@ -45,49 +61,18 @@ def build_system(name):
     return params, lig, rec, tors, xf
 
 
-# ------------------------------------------------------------------------------------
-# CPU baseline: the oracle (a numpy/scipy port of the reference's CPU path) on host cores
-# ------------------------------------------------------------------------------------
-_W = {}
-
-
-def _cpu_init(name):
-    import oracle_adapter as OA
-    params, lig, rec, tors, xf = build_system(name)
-    _W.update(OA=OA, params=params, lig=lig, rec=rec, tors=tors, xf=xf)
-
-
-def _cpu_eval(rng):
-    OA, lig = _W["OA"], _W["lig"]
-    out = []
-    for p in range(rng[0], rng[1]):
-        x = OA.express(lig, _W["tors"][p], _W["xf"][p])
-        r = OA.contacts(lig, _W["rec"], _W["params"], x, with_slack=False)
-        out.append((r.clash, r.hydro))
-    return out
-
-
-class CpuPool(object):
-    def __init__(self, name, cores):
-        import multiprocessing as mp
-        self.cores = cores
-        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
-            os.environ.setdefault(var, "1")      # one process per core, no nested BLAS threads
-        # spawn: the parent may hold a CUDA context, which must not be forked
-        self.pool = mp.get_context("spawn").Pool(cores, initializer=_cpu_init, initargs=(name,))
-        self.pool.map(_cpu_eval, [(0, 1)] * cores)       # warm every worker
-
-    def run(self, start, count):
-        per = max(1, count // (self.cores * 4))
-        chunks = [(a, min(a + per, start + count)) for a in range(start, start + count, per)]
-        t0 = time.perf_counter()
-        res = self.pool.map(_cpu_eval, chunks)
-        dt = time.perf_counter() - t0
-        return dt, [s for c in res for s in c]
-
-    def close(self):
-        self.pool.close()
-        self.pool.join()
+def build_c5(device):
+    """configs[4] through the plugin layer's model builder (tests/golden_util.configs4_job)."""
+    import random
+    import golden_util as G
+    from gaudi_b200 import base
+    cfg, _ = G.configs4_job(C5_RES, seed=5)
+    random.seed(5)
+    template = base.MolecularIndividual(cfg)
+    env = base.Environment(cfg, device=device, group=False)
+    batch = env.attach(template)
+    tors, xf, rot = G.configs4_alleles(batch, template, C5_POP, seed=5)
+    return batch, tors, xf, rot
 
 
 # ------------------------------------------------------------------------------------
@@ -133,448 +118,574 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------
-# B200 arm
+# small helpers
 # ------------------------------------------------------------------------------------
-def run_rmsd(args):
-    """BASELINE.json configs[3]: similarity bitmask of 16,384 conformers x 60 atoms, row blocks over
-    the ranks; coordinates are all-gathered first (each rank starts with its own block, as after a
-    sharded evaluate), every rank computes its rows, the bitmask rows are all-gathered to rank 0."""
-    import torch
-    import torch.distributed as dist
-    from gaudi_b200 import model as M, parallel, synth
-    from gaudi_b200.engine import Engine, measure_fp32_peak, launch_count
-    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    lig = synth.make_ligand(12, 2, seed=1)
-    eng = Engine(lig, M.empty_receptor(), M.ContactParams(only_internal=True), device=local)
-    conf = synth.make_conformers(RMSD_N, RMSD_A, seed=4).astype(np.float32)
-    b = parallel.shard_bounds(RMSD_N, world)
-    mine = torch.as_tensor(conf[b[rank]:b[rank + 1]]).to(dev)
-    flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)
+class Ctx(object):
+    """Process-wide state of one bench run: ranks, device, L2 flush buffer, timing."""
 
-    def rows(allc, r0, r1):
-        return eng.rmsd_matrix(allc, row0=r0, row1=r1, threshold=2.5, values=False)[1]
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=self.dev)
 
-    def step():
-        return parallel.sharded_rmsd_bits(rows, mine, counts=[b[r + 1] - b[r] for r in range(world)])
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    for _ in range(max(3, args.warmup)):
-        bits = step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    peak32 = measure_fp32_peak(local)
-    l0 = launch_count()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    for k in range(args.steps):
-        flush.fill_(k & 0xff)
-        ev[k][0].record(); step(); ev[k][1].record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t = torch.tensor([sum(a.elapsed_time(c) for a, c in ev) / args.steps], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    if rank == 0:
-        print(json.dumps({
-            "metric": "RMSD pairs/s", "value": (RMSD_N * (RMSD_N - 1) // 2) / (ms * 1e-3), "unit": "unique pairs/s",
-            "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[3]: similarity bitmask of %d conformers x %d atoms, threshold 2.5 A, "
-                                   "row-block sharded; fp16 tensor-core pre-filter, every pair inside its error bound "
-                                   "re-decided by the exact f32 sum (bits identical to the f32 kernel)" % (RMSD_N, RMSD_A),
-                       "l2": "192 MiB buffer written between timed iterations"},
-            "roofline": dict(rmsd_roofline(((RMSD_N + 127) // 128) * (((RMSD_N + 127) // 128) + 1) // 2 * 128 * 128, ms, peak32),
-                             step_note="step time includes the coordinate and bitmask all-gathers"),
-            "gpu_launches": int(launch_count() - l0)}), flush=True)
-    if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+    def max_over_ranks(self, values):
+        t = self.torch.tensor(list(values), dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.cpu().numpy()
+
+    def time_steps(self, fn, steps, warmup=3):
+        """Per-step device times (ms): L2 flushed before every step, CUDA events on the launching
+        stream, barrier + synchronize on both sides, per step the MAX over the ranks."""
+        torch = self.torch
+        for _ in range(warmup):
+            fn()
+        self.barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for k in range(steps):
+            self.flush.fill_(k & 0xff)
+            ev[k][0].record()
+            fn()
+            ev[k][1].record()
+        self.barrier()
+        return self.max_over_ranks(a.elapsed_time(b) for a, b in ev)
 
 
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
-    from gaudi_b200 import model as M
-    from gaudi_b200.engine import Engine, measure_fp32_peak, launch_count
-    from gaudi_b200 import synth
+def spread(ms):
+    return {"ms_per_step_min": float(np.min(ms)), "ms_per_step_median": float(np.median(ms)),
+            "ms_per_step_max": float(np.max(ms))}
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    name = args.workload
-    pop, L, T, R = WORKLOADS[name]
-    params, lig, rec, tors, xf = build_system(name)
-    # shard by individual: contiguous blocks, the last ranks may hold one fewer
-    bounds = [(pop * r) // world for r in range(world + 1)]
-    lo, hi = bounds[rank], bounds[rank + 1]
-    shard = hi - lo
-    max_shard = max(bounds[r + 1] - bounds[r] for r in range(world))
 
-    eng = Engine(lig, rec, params, device=local)
-    eng.reserve(max_shard)
-    eng.set_profiling(True)
-    t_d = torch.as_tensor(tors[lo:hi]).to(dev)
-    x_d = torch.as_tensor(xf[lo:hi]).to(dev)
-    scores = torch.empty((max_shard, 2), dtype=torch.float64, device=dev)
-    counts = torch.empty((max_shard, 2), dtype=torch.int32, device=dev)
-    gathered = torch.empty((world * max_shard, 2), dtype=torch.float64, device=dev) if world > 1 else None
-    flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
-    # page-locked host buffers of the end-to-end leg (allocated up front, as an application would)
-    th = torch.as_tensor(np.ascontiguousarray(tors[lo:hi])).pin_memory()
-    xh = torch.as_tensor(np.ascontiguousarray(xf[lo:hi])).pin_memory()
-    s_pin = torch.empty((shard, 2), dtype=torch.float64).pin_memory()
-    c_pin = torch.empty((shard, 2), dtype=torch.int32).pin_memory()
-
-    def step():
-        eng.evaluate(t_d, x_d, counts=True, scores_out=scores[:shard], counts_out=counts[:shard])
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, scores)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    barrier()
-    peak32 = measure_fp32_peak(local)          # FP32 roofline denominator, measured here
-
-    # Single GPU: the step (memset + express + Contacts) is captured once into a CUDA graph and
-    # replayed (about 1 % at this size: the step is not launch-bound).  Scratch is reserved and the
-    # kernels have run, so the captured calls neither allocate nor synchronise.  With several
-    # ranks the step is launched eagerly: the NCCL all_gather follows the kernels on the same
-    # stream and its enqueue is hidden behind them; capturing the collective bought nothing and
-    # a two-rank trial of it did not complete.  --no-graph launches eagerly at N=1 too.
-    graph, launches_per_step = None, None
-    if not args.no_graph and world == 1:
-        eng.set_profiling(False)               # event timing is for the eager passes below
-        try:
-            side = torch.cuda.Stream(device=dev)
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                step()
-            torch.cuda.current_stream().wait_stream(side)
-            barrier()
-            graph = torch.cuda.CUDAGraph()
-            n0 = launch_count()
-            with torch.cuda.graph(graph):
-                step()
-            launches_per_step = launch_count() - n0
-            graph.replay()
-            barrier()
-        except Exception as exc:               # capture unsupported (e.g. by the NCCL build): run eagerly
-            sys.stderr.write("bench: CUDA graph capture failed (%s); launching eagerly\n" % exc)
-            graph = None
-            barrier()
-    run_step = graph.replay if graph is not None else step
-    eng.set_profiling(False)                   # no instrumentation inside the timed region
-    for _ in range(3):
-        run_step()
-    sampler = ClockSampler(local)
-    sampler.start()
-    launches0 = launch_count()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    sweep_ms, expr_ms, fin_ms = [], [], []
-    barrier()
-    for k in range(args.steps):
-        flush.fill_(k & 0xff)                  # evict L2 between timed iterations
-        ev[k][0].record()
-        run_step()
-        ev[k][1].record()
-    barrier()
-    launches = launches_per_step * args.steps if graph is not None else launch_count() - launches0
-    clocks = sampler.stop()
-    # per-kernel durations (roofline numerator) and the executed pair tests from eager, profiled
-    # launches of the same step, each kernel bracketed by CUDA events on the launching stream, L2
-    # flushed as in the timed loop
-    eng.set_profiling(True)
-    for k in range(min(args.steps, 10)):
-        flush.fill_(k & 0xff)
-        step()
-        kt = eng.kernel_times()
-        sweep_ms.append(kt["sweep"]); expr_ms.append(kt["express"]); fin_ms.append(kt["finalize"])
-    barrier()
-    total_ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    value = pop / (ms_per_step * 1e-3)
-
-    # roofline of the dominant kernel (contacts sweep), executed pair tests
-    tests = eng.last_pair_tests()
-    sweep = float(np.mean(sweep_ms))
-    achieved = tests * FLOPS_PER_PAIR_TEST / (sweep * 1e-3) / 1e12
-    dense_flops_per_ind = FLOPS_PER_PAIR_TEST * (L * R + L * (L - 1) // 2)
-
-    # e2e: host buffers through the C ABI (H2D alleles, kernels, D2H scores) per step
-    eng.set_profiling(False)
-    for _ in range(max(3, args.warmup)):       # same warm-up as the device loop (also wakes the PCIe link)
-        eng.evaluate_host(th, xh, scores_out=s_pin, counts_out=c_pin)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n_e2e = max(3, args.steps)
-    e0.record()
-    for _ in range(n_e2e):
-        s_h, c_h, _ = eng.evaluate_host(th, xh, scores_out=s_pin, counts_out=c_pin)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, scores)
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1) / n_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item())
-    h2d = int(th.numel() * th.element_size() + xh.numel() * xh.element_size())
-    d2h = int(s_h.numel() * s_h.element_size() + c_h.numel() * c_h.element_size())
-    assert torch.equal(s_pin.to(dev), scores[:shard]), "e2e path disagrees with the device path"
-
-    extra = {}
-    if rank == 0 and world == 1 and not args.quick:
-        extra = side_measurements(eng, torch, dev, peak32)
-
-    out = None
-    if rank == 0:
-        out = {
-            "metric": "individuals scored/sec (expr + Contacts)", "value": value, "unit": "individuals/s",
-            "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": "configs[2]: pop %d x (%d-atom, %d-torsion ligand) vs %d-atom receptor box, "
-                                   "Torsion+Search express + Contacts(clashes, hydrophobic)" % (pop, L, T, R),
-                       "sharding": "by individual, %d per GPU, NCCL all_gather of fitness" % max_shard if world > 1
-                       else "single GPU",
-                       "l2": "192 MiB buffer written between timed iterations",
-                       "launch": "step replayed from a CUDA graph" if graph is not None else "eager launches",
-                       "culling": "receptor tiles out of reach of a pose are skipped (results bit-identical to dense)"},
-            "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": achieved, "peak": peak32,
-                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of this kernel on this workload at
-                         # N=1, from the committed capture profiles/ncu_contacts_fused_r01j.txt (bytes/launch)
-                         "traffic": 31.76e6 if (name == "c3" and world == 1) else None,
-                         "algorithmic_bytes_per_launch": shard * (L * 12 + 16 + 8),
-                         "hbm": hbm_check(shard * (L * 12 + 16 + 8), sweep),
-                         "note": "culled run: the pair-test flop count credits only the sweep (about a third of "
-                                 "the issued instructions); culling, candidate expansion, pair scoring and the "
-                                 "static-pair walk are per-individual bookkeeping. The dense run of the same "
-                                 "kernel (key 'dense') is the sweep-dominated regime the FP32 roofline models. "
-                                 "ncu of this kernel: profiles/ncu_contacts_fused_culled_r01.txt (issue slots "
-                                 "~79 % busy, issue-bound)",
-                         "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
-                         "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
-                         "kernel_ms": sweep, "express_ms": float(np.mean(expr_ms)), "finalize_ms": float(np.mean(fin_ms)),
-                         "dense_flops_per_individual": dense_flops_per_ind,
-                         "executed_fraction_of_dense": tests * FLOPS_PER_PAIR_TEST / (dense_flops_per_ind * shard)},
-            "e2e": {"value": pop / (e2e_ms * 1e-3), "unit": "individuals/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
-            "gpu_launches": int(launches),
-            "clocks": clocks,
-        }
-        out.update(extra)
-    if rank == 0 and world == 1 and not args.no_cpu:
-        out["cpu_baseline"] = cpu_baseline(name, args.cpu_sample)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    if out is not None:
-        print(json.dumps(out), flush=True)
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh)
+    except Exception:
+        return {}
 
 
 def hbm_check(bytes_per_launch, kernel_ms):
     """HBM is not the bound of this path; say by how much, against the driver-measured copy bandwidth."""
-    peak = None
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
-            peak = float(json.load(fh)["hbm_gbs"])
-    except Exception:
-        peak = 6650.0          # fallback stated in B200_PROFILING.md
+    peak = float(measured_peaks().get("hbm_gbs", 6650.0))       # fallback stated in B200_PROFILING.md
     ach = bytes_per_launch / (kernel_ms * 1e-3) / 1e9
     return {"achieved_gbs": ach, "peak_gbs": peak, "frac": ach / peak}
 
 
 def tensor_peak():
-    """Dense fp16/bf16 tensor-core throughput to hold the HMMA work of the bitmask kernel against:
-    the driver-measured cuBLAS bf16 burst figure, else the nominal one of B200_PROFILING.md."""
+    pk = measured_peaks()
+    if "bf16_tflops" in pk:
+        return float(pk["bf16_tflops"]), "MEASURED_PEAKS.json bf16_tflops (cuBLAS burst)"
+    return 2250.0, "nominal dense fp16/bf16 of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+
+
+def committed_dram_traffic(kernel_tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, read at run time from
+    the newest committed ncu summary under profiles/ whose name holds ``kernel_tag``.  Returns
+    (bytes or None, file name or None)."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    best = None
+    pdir = os.path.join(ROOT, "profiles")
+    for fn in sorted(os.listdir(pdir)) if os.path.isdir(pdir) else []:
+        if kernel_tag in fn and fn.endswith(".txt"):
+            best = fn
+    if best is None:
+        return None, None
+    total, seen = 0.0, 0
+    for line in open(os.path.join(pdir, best)):
+        m = re.match(r"\s*dram__bytes_(read|write)\.sum\s+(\w+)\s+([0-9.,eE+-]+)", line)
+        if m and m.group(2) in unit:
+            total += float(m.group(3).replace(",", "")) * unit[m.group(2)]
+            seen += 1
+        if seen == 2:
+            break
+    return (total if seen == 2 else None), ("profiles/" + best)
+
+
+# ------------------------------------------------------------------------------------
+# CPU baselines (the oracle on the host cores; rank 0, N = 1 only)
+# ------------------------------------------------------------------------------------
+def c_oracle_module():
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import c_oracle
+    return c_oracle
+
+
+def cpu_contacts_baseline(co, alleles, budget_s=10.0, what=""):
+    """The oracle's C restatement (fp64, cell list, every host core) over the same population."""
+    n = len(alleles[0])
+    co.evaluate(*[a[:256] if a is not None else None for a in alleles])       # warm
+    reps, dt = 0, 0.0
+    while dt < budget_s and reps < 40:
+        t0 = time.perf_counter()
+        co.evaluate(*alleles)
+        dt += time.perf_counter() - t0
+        reps += 1
+    return {"value": n * reps / dt, "unit": "individuals/s", "cores": co.workers, "kind": "port",
+            "sample": "%d passes over %d individuals of the same population%s, C restatement of the reference's CPU path "
+                      "(oracle/gaudi_oracle.c: fp64 express + zone + DetectClash rule + scoring, cell list), "
+                      "%d host threads, %.1f s" % (reps, n, what, co.workers, dt)}
+
+
+def cpu_rmsd_baseline(budget_s=8.0):
+    """RMSD CPU baselines on a 1,024-conformer subsample of the same conformers (SURVEY.md 8d,
+    BASELINE.md 3): (a) the reference's formula called pair by pair from Python, as
+    gaudi/algorithms.py:141-155 calls ``similarity`` — the timed function is the oracle's
+    ``rmsd_squared``, which restates gaudi/similarity.py:73-75 line for line and is pinned to
+    recorded outputs of the reference's own module (tests/golden/similarity_reference.npz); the
+    reference's file itself cannot be read on this box; (b) the vectorised numpy form of the same
+    formula; (c) the C restatement on every host core."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import gaudi_oracle as O
+    from gaudi_b200 import synth
+    conf = synth.make_conformers(RMSD_N, RMSD_A, seed=4).astype(np.float32).astype(np.float64)
+    sub = conf[:1024]
+    thr2 = RMSD_THR * RMSD_THR
+    # (a) pairwise, python loop
+    t0, done, similar = time.perf_counter(), 0, 0
+    for i in range(len(sub)):
+        a = sub[i]
+        for j in range(i + 1, len(sub)):
+            similar += not (O.rmsd_squared(a, sub[j]) > thr2)
+        done += len(sub) - 1 - i
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt_a = time.perf_counter() - t0
+    # (b) vectorised numpy, one row against the subsample at a time
+    t0, done_b = time.perf_counter(), 0
+    while time.perf_counter() - t0 < budget_s / 2:
+        for i in range(0, len(sub), 8):
+            d = sub - sub[i]
+            _ = (d * d).sum(axis=(1, 2)) / RMSD_A > thr2
+            done_b += len(sub)
+    dt_b = time.perf_counter() - t0
+    out = {"value": done / dt_a, "unit": "pairs/s", "cores": 1, "kind": "port",
+           "sample": "%d pairs of a 1,024-conformer subsample of the same conformers, one Python call of the "
+                     "reference's formula per pair as gaudi/algorithms.py:141-155 makes them (oracle.rmsd_squared = "
+                     "gaudi/similarity.py:73-75, pinned to the reference module's recorded outputs), %.1f s"
+                     % (done, dt_a),
+           "numpy_vectorised": {"value": done_b / dt_b, "unit": "pairs/s", "cores": 1,
+                                "sample": "same formula broadcast over one row of the subsample at a time, %.1f s" % dt_b}}
     try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
-            return float(json.load(fh)["bf16_tflops"]), "MEASURED_PEAKS.json bf16_tflops (cuBLAS burst)"
-    except Exception:
-        return 2250.0, "nominal dense fp16/bf16 of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+        co = c_oracle_module()
+        lib = co._lib()
+        import ctypes as C
+        rows = 512
+        buf = np.empty((rows, RMSD_N))
+        nthreads = int(lib.go_num_threads())
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < budget_s / 2 or reps == 0:
+            lib.go_rmsd_matrix(C.c_int(RMSD_N), C.c_int(RMSD_A), conf.ctypes.data_as(C.c_void_p), C.c_int(0),
+                               C.c_int(rows), buf.ctypes.data_as(C.c_void_p))
+            reps += 1
+        dt_c = time.perf_counter() - t0
+        out["c_port_all_cores"] = {"value": rows * RMSD_N * reps / dt_c, "unit": "pairs/s", "cores": nthreads,
+                                   "sample": "%d passes over %d rows x %d columns, oracle/gaudi_oracle.c go_rmsd_matrix "
+                                             "(fp64, OpenMP), %.1f s" % (reps, rows, RMSD_N, dt_c)}
+    except Exception as exc:
+        out["c_port_all_cores"] = {"error": repr(exc)[:160]}
+    return out
 
 
-def rmsd_roofline(n_pairs_computed, ms, peak32):
-    """The bitmask kernel does its arithmetic on the tensor cores (2 * 192 flops of HMMA per pair for
-    60 atoms, K padded to 192) and is bounded by what follows the MMA: the per-pair decision, the
-    exact re-decision of the pairs inside the error bound, bit packing.  Reported: the HMMA rate
-    against the tensor peak, and the same pairs/s expressed in the FP32 kernel's flops (what the
-    reference's formula costs) against the FP32 peak."""
-    kp = (3 * RMSD_A + 15) // 16 * 16
-    peak_t, src = tensor_peak()
-    ach_t = n_pairs_computed * 2 * kp / (ms * 1e-3) / 1e12
-    ach_eq = n_pairs_computed * FLOPS_PER_RMSD_PAIR / (ms * 1e-3) / 1e12
-    return {"bound": "tensor", "kernel": "rmsd_bits_mma_kernel", "achieved": ach_t, "peak": peak_t, "unit": "TFLOP/s",
-            "frac": ach_t / peak_t, "peak_source": src, "flops_per_pair": 2 * kp, "traffic": None,
-            "fp32_equivalent": {"achieved": ach_eq, "peak": peak32, "frac": ach_eq / peak32 if peak32 else None,
-                                "flops_per_pair": FLOPS_PER_RMSD_PAIR,
-                                "note": "the FP32 direct-difference kernel (values requested, or GMM_OPT_RMSD_SIMT) "
-                                        "reaches about 0.5 of the FP32 peak on the same pairs"},
-            "note": "tensor pipe mostly idle by design: the MMA is a pre-filter, the kernel is bounded by the "
-                    "decision epilogue (profiles/ncu_rmsd_bits_mma_r01.txt)"}
+# ------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------
+def capture_graph(ctx, step):
+    """The step as one CUDA graph (no allocation, no host synchronisation, no collective call
+    inside).  Returns (graph or None, kernel launches per replay)."""
+    torch = ctx.torch
+    from gaudi_b200.engine import launch_count
+    try:
+        side = torch.cuda.Stream(device=ctx.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step()
+        torch.cuda.current_stream().wait_stream(side)
+        ctx.barrier()
+        graph = torch.cuda.CUDAGraph()
+        n0 = launch_count()
+        with torch.cuda.graph(graph):
+            step()
+        per = launch_count() - n0
+        graph.replay()
+        ctx.barrier()
+        return graph, per
+    except Exception as exc:
+        sys.stderr.write("bench: CUDA graph capture failed (%s); launching eagerly\n" % exc)
+        ctx.barrier()
+        return None, None
 
 
-def side_measurements(eng, torch, dev, peak32):
-    """Dense (no culling) figure on the same workload, configs[1], and the RMSD matrix of
-    configs[3]; reported next to the headline, same timing rules."""
-    from gaudi_b200 import model as M, synth
-    from gaudi_b200.engine import Engine
+def bench_c3(ctx):
+    torch, args = ctx.torch, ctx.args
+    from gaudi_b200 import parallel
+    from gaudi_b200.engine import Engine, measure_fp32_peak, launch_count
+    name = "c3"
+    pop, L, T, R = WORKLOADS[name]
+    params, lig, rec, tors, xf = build_system(name)
+    eng = Engine(lig, rec, params, device=ctx.local)
+    sh = parallel.ShardedEvaluator(eng, pop, exchange=args.exchange)
+    shard = sh.hi - sh.lo
+    t_d = torch.as_tensor(sh.shard(tors)).to(ctx.dev)
+    x_d = torch.as_tensor(sh.shard(xf)).to(ctx.dev)
+
+    def step():
+        return sh.evaluate(t_d, x_d)
+
+    warm = max(3, args.warmup)
+    for _ in range(warm):
+        step()
+    ctx.barrier()
+    peak32 = measure_fp32_peak(ctx.local)          # FP32 roofline denominator, measured here
+    graph, per_replay = (None, None)
+    if not args.no_graph and sh.kind != "nccl":
+        graph, per_replay = capture_graph(ctx, step)
+    run_step = graph.replay if graph is not None else step
+    sampler = ClockSampler(ctx.local)
+    sampler.start()
+    l0 = launch_count()
+    ms = ctx.time_steps(run_step, args.steps, warmup=3)
+    launches = per_replay * (args.steps + 3) if graph is not None else launch_count() - l0
+    clocks = sampler.stop()
+    ms_per_step = float(np.mean(ms))
+    value = pop / (ms_per_step * 1e-3)
+
+    # the gathered table every rank now holds equals the rows this rank computed itself
+    if sh.exchange is not None:
+        epoch, timed_out, g_s, g_c = sh.exchange.state()
+        assert not timed_out, "fitness exchange: a wait for another rank timed out"
+    else:
+        g_s, g_c = step()
+        torch.cuda.synchronize()
+    own_s, own_c, _ = eng.evaluate(t_d, x_d)
+    assert torch.equal(g_s[sh.lo:sh.hi], own_s) and torch.equal(g_c[sh.lo:sh.hi], own_c), "gathered rows differ"
+    total = float(g_s[:pop].sum().item())
+    checksum = ctx.max_over_ranks([total, -total])
+    assert checksum[0] == -checksum[1], "ranks hold different fitness tables"
+
+    # roofline of the dominant kernel: executed pair tests and kernel durations from eager, profiled
+    # launches of the same step (CUDA events around each kernel on the launching stream, L2 flushed)
+    eng.set_profiling(True)
+    sweep_ms, expr_ms = [], []
+    for k in range(min(args.steps, 10)):
+        ctx.flush.fill_(k & 0xff)
+        eng.evaluate(t_d, x_d, scores_out=sh.scores[:shard], counts_out=sh.counts[:shard])
+        kt = eng.kernel_times()
+        sweep_ms.append(kt["sweep"]); expr_ms.append(kt["express"])
+    tests = eng.last_pair_tests()
+    eng.set_profiling(False)
+    ctx.barrier()
+    sweep = float(np.mean(sweep_ms))
+    achieved = tests * FLOPS_PER_PAIR_TEST / (sweep * 1e-3) / 1e12
+    dense_flops_per_ind = FLOPS_PER_PAIR_TEST * (L * R + L * (L - 1) // 2)
+    traffic, traffic_file = committed_dram_traffic("contacts_fused_culled") if (ctx.world == 1) else (None, None)
+
+    e2e = bench_c3_e2e(ctx, eng, tors, xf, own_s, sh)
+
+    out = None
+    if ctx.rank == 0:
+        out = {
+            "metric": "individuals scored/sec (expr + Contacts)", "value": value, "unit": "individuals/s",
+            "n_gpus": ctx.world, "steps": args.steps, "warmup": warm, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": C3_TEXT,
+                       "sharding": ("by individual, %d per GPU; fitness rows gathered into every rank's table by %s"
+                                    % (sh.max_shard, "stores through peer memory + epoch flags (gmm_exchange_publish), no collective call"
+                                       if sh.kind == "peer" else "NCCL all_gather_into_tensor")) if ctx.world > 1 else "single GPU",
+                       "l2": "192 MiB buffer written between timed iterations",
+                       "launch": "step replayed from a CUDA graph" if graph is not None else "eager launches",
+                       "culling": "receptor tiles out of reach of a pose are skipped (results bit-identical to dense)"},
+            "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": achieved, "peak": peak32,
+                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None,
+                         "traffic": traffic, "traffic_source": traffic_file,
+                         "algorithmic_bytes_per_launch": shard * (L * 12 + 16 + 8),
+                         "hbm": hbm_check(shard * (L * 12 + 16 + 8), sweep),
+                         "note": "culled run: the pair-test flop count (SURVEY.md 8d: 10 flops per pair test) credits only "
+                                 "the sweep; culling, candidate expansion, pair scoring and the static-pair walk are "
+                                 "per-individual bookkeeping.  The dense run of the same kernel (key 'dense', N = 1) is "
+                                 "the sweep-dominated regime the FP32 roofline models; the kernel executes 7 flops per "
+                                 "pair test (3 FFMA + half a 3-input min), so by executed FP32 work the fractions are "
+                                 "0.7 x these",
+                         "peak_source": "measured here: dependent-free FFMA loop (MEASURED_PEAKS.json has no FP32 figure)",
+                         "pair_tests_per_launch": tests, "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
+                         "kernel_ms": sweep, "express_ms": float(np.mean(expr_ms)),
+                         "dense_flops_per_individual": dense_flops_per_ind,
+                         "executed_fraction_of_dense": tests * FLOPS_PER_PAIR_TEST / (dense_flops_per_ind * shard)},
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        out.update(spread(ms))
+    state = {"eng": eng, "sh": sh, "peak32": peak32, "lig": lig, "rec": rec, "params": params, "tors": tors, "xf": xf}
+    return out, state
+
+
+def bench_c3_e2e(ctx, eng, tors, xf, own_scores, sh):
+    """The same metric through the host-buffer API: the population's alleles start in page-locked
+    HOST memory of rank 0 (the process that runs the GA), the fitness table ends there.  N = 1:
+    gmm_evaluate_host.  N > 1: gaudi_b200.parallel.HostShardedEvaluator — the table is a
+    shared-memory segment page-locked by every rank, each rank's gmm_evaluate_host uploads its rows
+    over its own PCIe link and downloads its scores into the same table; rank 0 waits for every
+    rank's done mark.  Timed with the host clock on rank 0 around the whole collective call
+    (includes every copy and every wait), after a barrier."""
+    torch, args = ctx.torch, ctx.args
+    from gaudi_b200 import parallel
+    pop = len(tors)
+    hs = parallel.HostShardedEvaluator(eng, pop)
+    if ctx.rank == 0:
+        hs.tors[:pop] = tors
+        hs.xforms[:pop] = xf
+    n_e2e = max(5, args.steps)
+    warm = max(3, args.warmup)
+    times = []
+    for k in range(warm + n_e2e):
+        ctx.barrier()
+        t0 = time.perf_counter()
+        hs.evaluate(pop)
+        dt = time.perf_counter() - t0
+        if k >= warm:
+            times.append(dt * 1e3)
+    ctx.barrier()
+    out = None
+    if ctx.rank == 0:
+        got = torch.as_tensor(hs.scores[sh.lo:sh.hi].copy()).to(ctx.dev)
+        assert torch.equal(got, own_scores), "e2e path disagrees with the device path"
+        assert np.isfinite(hs.scores[:pop]).all()
+        e2e_ms = float(np.mean(times))
+        row_in = hs.tors.shape[1] * 8 + 12 * 8
+        out = {"value": pop / (e2e_ms * 1e-3), "unit": "individuals/s",
+               "h2d_bytes_per_step": int(pop * row_in), "d2h_bytes_per_step": int(pop * (16 + 8)),
+               "ms_per_step": e2e_ms, "ms_per_step_min": float(np.min(times)), "ms_per_step_max": float(np.max(times)),
+               "timed_with": "host clock on rank 0 around the collective call, barrier before each step",
+               "path": "gmm_evaluate_host" if ctx.world == 1 else
+                       "parallel.HostShardedEvaluator: shared page-locked table, %d PCIe links in parallel" % ctx.world}
+    hs.close()
+    return out
+
+
+def bench_rmsd(ctx, state, cpu=False):
+    """configs[3]: every rank holds its block of conformers (as after a sharded evaluate); a step =
+    all-gather of the conformers + this rank's rows of the similarity bitmask + compaction into
+    partner lists + gather of the lists (what the niching pass reads)."""
+    torch = ctx.torch
+    import ctypes as C
+    from gaudi_b200 import _lib
+    from gaudi_b200 import model as M, parallel, synth
+    from gaudi_b200.engine import Engine, launch_count
+    lig = synth.make_ligand(12, 2, seed=1)
+    eng = Engine(lig, M.empty_receptor(), M.ContactParams(only_internal=True), device=ctx.local)
+    eng.reserve_rmsd(RMSD_N, RMSD_A)
+    conf = synth.make_conformers(RMSD_N, RMSD_A, seed=4).astype(np.float32)
+    b = parallel.shard_bounds(RMSD_N, ctx.world)
+    counts = [b[r + 1] - b[r] for r in range(ctx.world)]
+    mine = torch.as_tensor(conf[b[ctx.rank]:b[ctx.rank + 1]]).to(ctx.dev)
+    allc = torch.as_tensor(conf).to(ctx.dev)
     res = {}
 
-    def timed(fn, reps):
-        fn(); fn(); fn()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(reps):
-            fn()
-        b.record()
-        torch.cuda.synchronize()
-        return a.elapsed_time(b) / reps
+    def step():
+        res["lists"] = parallel.sharded_similar_lists(eng, mine, counts, threshold=RMSD_THR)
 
-    # dense on the headline workload
-    pop, L, T, R = WORKLOADS["c3"]
-    dense = Engine(eng.mobile, eng.receptor, M.ContactParams(cull=False), device=eng.device)
-    dense.set_profiling(True)
-    tors, xf = synth.make_alleles(pop, T, seed=3)
-    t_d, x_d = torch.as_tensor(tors).to(dev), torch.as_tensor(xf).to(dev)
-    ms = timed(lambda: dense.evaluate(t_d, x_d), 3)
-    kt = dense.kernel_times()
-    tests = dense.last_pair_tests()
-    ach = tests * FLOPS_PER_PAIR_TEST / (kt["sweep"] * 1e-3) / 1e12
-    res["dense"] = {"value": pop / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms,
-                    "roofline": {"achieved": ach, "peak": peak32, "frac": ach / peak32, "unit": "TFLOP/s",
-                                 "kernel_ms": kt["sweep"], "pair_tests_per_launch": tests}}
-    dense.close()
-    # configs[1]
-    params, lig, rec, tors, xf = build_system("c2")
-    e2 = Engine(lig, rec, params, device=eng.device)
-    t_d, x_d = torch.as_tensor(tors).to(dev), torch.as_tensor(xf).to(dev)
-    ms = timed(lambda: e2.evaluate(t_d, x_d), 20)
-    res["configs1_pop4096_rec5k"] = {"value": tors.shape[0] / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms}
-    e2.close()
-    # configs[3]: RMSD matrix, bitmask output (what niching consumes)
-    conf = torch.as_tensor(synth.make_conformers(RMSD_N, RMSD_A, seed=4), dtype=torch.float32).to(dev)
-    bits = torch.empty((RMSD_N, RMSD_N // 32), dtype=torch.int32, device=dev)
-    from gaudi_b200 import _lib
-    import ctypes as C
+    l0 = launch_count()
+    ms = ctx.time_steps(step, 10, warmup=3)
+    launches = launch_count() - l0
+    # the bitmask kernel alone, this rank's rows (roofline numerator)
+    r0, r1 = b[ctx.rank], b[ctx.rank + 1]
+    bits = torch.empty((r1 - r0, (RMSD_N + 31) // 32), dtype=torch.int32, device=ctx.dev)
 
-    def rm():
-        _lib.check(eng._L.gmm_rmsd_matrix(eng._h, RMSD_N, RMSD_A, C.c_void_p(conf.data_ptr()), 0, RMSD_N, None,
-                                          C.c_void_p(bits.data_ptr()), 2.5, eng._stream()))
-    ms = timed(rm, 5)
+    def kernel_only():
+        _lib.check(eng._L.gmm_rmsd_matrix(eng._h, RMSD_N, RMSD_A, C.c_void_p(allc.data_ptr()), r0, r1, None,
+                                          C.c_void_p(bits.data_ptr()), RMSD_THR, eng._stream()))
+    kms = ctx.time_steps(kernel_only, 10, warmup=3)
+    ptr, idx = res["lists"]
+    n_pairs = RMSD_N * (RMSD_N - 1) // 2
+    # pairs the kernels compute: 128 x 128 tiles; inside a rank's diagonal square only the upper triangle
     nt = (RMSD_N + 127) // 128
-    ordered = nt * (nt + 1) // 2 * 128 * 128        # pairs the kernel computes (upper-triangle tiles)
-    res["rmsd"] = {"metric": "RMSD pairs/s", "value": (RMSD_N * (RMSD_N - 1) // 2) / (ms * 1e-3),
-                   "unit": "unique pairs/s", "ms": ms, "n_conformers": RMSD_N, "atoms": RMSD_A,
-                   "note": "N x N similarity bitmask; tiles above the diagonal are computed once and mirrored; "
-                           "value counts unique pairs, the roofline counts the pairs actually computed",
-                   "roofline": rmsd_roofline(ordered, ms, peak32)}
-    # the FP32 direct-difference kernel on the same conformers (what a call that wants the values runs)
-    e_simt = Engine(eng.mobile, M.empty_receptor(), M.ContactParams(only_internal=True, rmsd_simt=True), device=dev.index or 0)
+    rows_t = [((b[r + 1] - b[r]) + 127) // 128 for r in range(ctx.world)]
+    computed = sum((rt * nt - rt * (rt - 1) // 2) * 128 * 128 for rt in rows_t)
+    kp = (3 * RMSD_A + 15) // 16 * 16
+    peak_t, src = tensor_peak()
+    kernel_ms = float(np.mean(kms))
+    ach_t = (computed / ctx.world) * 2 * kp / (kernel_ms * 1e-3) / 1e12
+    out = None
+    if ctx.rank == 0:
+        step_ms = float(np.mean(ms))
+        out = {"metric": "RMSD pairs/s", "value": n_pairs / (step_ms * 1e-3), "unit": "unique pairs/s",
+               "n_gpus": ctx.world, "ms_per_step": step_ms, "scaling": "strong",
+               "config": {"workload": RMSD_TEXT,
+                          "step": "all-gather of conformers (NCCL) + row-block bitmask + partner-list compaction + gather of "
+                                  "the lists" if ctx.world > 1 else "bitmask + partner-list compaction",
+                          "l2": "192 MiB buffer written between timed iterations"},
+               "partner_entries": int(idx.shape[0]),
+               "partner_list_bytes": int(idx.shape[0] * 4 + ptr.shape[0] * 8),
+               "bitmask_bytes": RMSD_N * ((RMSD_N + 31) // 32) * 4,
+               "roofline": {"bound": "tensor", "kernel": "rmsd_bits kernel", "achieved": ach_t, "peak": peak_t,
+                            "unit": "TFLOP/s", "frac": ach_t / peak_t, "peak_source": src, "flops_per_pair": 2 * kp,
+                            "kernel_ms": kernel_ms, "pairs_computed_per_rank": computed // ctx.world, "traffic": None,
+                            "note": "MMA flops of the pairs this rank's tiles compute over the kernel's own duration "
+                                    "(centring kernels included); the product is a pre-filter, pairs inside its error "
+                                    "bound are re-decided by the exact f32 sum (bits identical to the FP32 kernel)"},
+               "gpu_launches": int(launches)}
+        out.update(spread(ms))
+        if cpu:
+            out["cpu_baseline"] = cpu_rmsd_baseline()
+    if ctx.world == 1 and ctx.rank == 0 and not ctx.args.quick:
+        # the FP32 direct-difference kernel on the same conformers (what a call that wants the values runs)
+        e_simt = Engine(lig, M.empty_receptor(), M.ContactParams(only_internal=True, rmsd_simt=True), device=ctx.local)
 
-    def rm_simt():
-        _lib.check(e_simt._L.gmm_rmsd_matrix(e_simt._h, RMSD_N, RMSD_A, C.c_void_p(conf.data_ptr()), 0, RMSD_N, None,
-                                             C.c_void_p(bits.data_ptr()), 2.5, e_simt._stream()))
-    ms_s = timed(rm_simt, 5)
-    ach_s = ordered * FLOPS_PER_RMSD_PAIR / (ms_s * 1e-3) / 1e12
-    res["rmsd"]["fp32_kernel"] = {"value": (RMSD_N * (RMSD_N - 1) // 2) / (ms_s * 1e-3), "unit": "unique pairs/s", "ms": ms_s,
-                                  "roofline": {"bound": "fp32", "kernel": "rmsd_tile_kernel", "achieved": ach_s,
-                                               "peak": peak32, "frac": ach_s / peak32, "unit": "TFLOP/s"}}
-    e_simt.close()
-    try:
-        res["configs4_rotamers12_pop32768"] = rotamers_measurement(torch, dev, timed)
-    except Exception as exc:                       # a side measurement must never sink the headline
-        res["configs4_rotamers12_pop32768"] = {"error": repr(exc)[:200]}
-    return res
+        def simt():
+            _lib.check(e_simt._L.gmm_rmsd_matrix(e_simt._h, RMSD_N, RMSD_A, C.c_void_p(allc.data_ptr()), 0, RMSD_N, None,
+                                                 C.c_void_p(bits.data_ptr()), RMSD_THR, e_simt._stream()))
+        sms = float(np.mean(ctx.time_steps(simt, 5, warmup=2)))
+        ach_s = computed * FLOPS_PER_RMSD_PAIR / (sms * 1e-3) / 1e12
+        out["fp32_kernel"] = {"value": n_pairs / (sms * 1e-3), "unit": "unique pairs/s", "ms": sms,
+                              "roofline": {"bound": "fp32", "kernel": "rmsd_tile_kernel", "achieved": ach_s,
+                                           "peak": state["peak32"], "frac": ach_s / state["peak32"], "unit": "TFLOP/s",
+                                           "flops_per_pair": FLOPS_PER_RMSD_PAIR}}
+        e_simt.close()
+    eng.close()
+    return out
 
 
-def rotamers_measurement(torch, dev, timed):
-    """BASELINE.json configs[4] on one GPU: Rotamers gene on 12 flexible side chains + Torsion +
-    Search + Contacts, population 32,768, through the plugin layer's model builder.  Structure:
-    the reference's own 5er1 test complex (committed fixture); chi tables: seeded random rows
-    (the reference takes them from Chimera's Dunbrack library, which is not available here)."""
-    import random
-    import golden_util as G
-    from gaudi_b200 import base
-    cfg, _ = G.configs4_job(12, seed=5)
-    lig = cfg.genes[1]["mol"]
-    random.seed(5)
-    template = base.MolecularIndividual(cfg)
-    env = base.Environment(cfg, device=dev.index or 0)
-    batch = env.attach(template)
+def bench_c5(ctx, state, cpu=False):
+    """configs[4]: population 32,768 sharded by individual over the ranks, same exchange as the headline."""
+    torch = ctx.torch
+    from gaudi_b200 import parallel
+    batch, tors, xf, rot = build_c5(ctx.local)
     eng = batch.engines[0][0]
-    pop = 32768
-    tors, xf, rot = G.configs4_alleles(batch, template, pop, seed=5)
-    t_d, x_d, r_d = (torch.as_tensor(v).to(dev) for v in (tors, xf, rot))
+    sh = parallel.ShardedEvaluator(eng, C5_POP, exchange=ctx.args.exchange)
+    t_d, x_d, r_d = (torch.as_tensor(sh.shard(v)).to(ctx.dev) for v in (tors, xf, rot))
+
+    def step():
+        return sh.evaluate(t_d, x_d, r_d)
+
+    for _ in range(3):
+        step()
+    ctx.barrier()
+    graph, _ = (None, None) if (ctx.args.no_graph or sh.kind == "nccl") else capture_graph(ctx, step)
+    ms = ctx.time_steps(graph.replay if graph is not None else step, 10, warmup=3)
     eng.set_profiling(True)
-    ms = timed(lambda: eng.evaluate(t_d, x_d, r_d), 10)
-    kt = eng.kernel_times()
-    out = {"value": pop / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms, "population": pop,
-           "express_ms": kt["express"], "contacts_ms": kt["sweep"],
-           "mobile_atoms": eng.mobile.n_atoms, "ligand_atoms": lig.n_atoms, "torsions": batch.n_torsions,
-           "rotamer_residues": batch.n_rot_res, "receptor_atoms": eng.receptor.n_atoms,
-           "structure": "5er1 test complex (86-atom ligand, 4,669-atom all-H protein), chi tables synthetic"}
+    km, em = [], []
+    for k in range(5):
+        ctx.flush.fill_(k)
+        eng.evaluate(t_d, x_d, r_d)
+        kt = eng.kernel_times()
+        km.append(kt["sweep"]); em.append(kt["express"])
+    tests = eng.last_pair_tests()
+    eng.set_profiling(False)
+    ctx.barrier()
+    out = None
+    if ctx.rank == 0:
+        step_ms = float(np.mean(ms))
+        kernel_ms = float(np.mean(km))
+        ach = tests * FLOPS_PER_PAIR_TEST / (kernel_ms * 1e-3) / 1e12
+        out = {"metric": "individuals scored/sec (expr + Contacts)", "value": C5_POP / (step_ms * 1e-3),
+               "unit": "individuals/s", "n_gpus": ctx.world, "ms_per_step": step_ms, "scaling": "strong",
+               "config": {"workload": C5_TEXT, "mobile_atoms": eng.mobile.n_atoms, "torsions": batch.n_torsions,
+                          "rotamer_residues": batch.n_rot_res, "receptor_atoms": eng.receptor.n_atoms,
+                          "structure": "5er1 test complex (86-atom ligand, all-H protein), chi tables synthetic",
+                          "launch": "step replayed from a CUDA graph" if graph is not None else "eager launches",
+                          "l2": "192 MiB buffer written between timed iterations"},
+               "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": ach, "peak": state["peak32"],
+                            "unit": "TFLOP/s", "frac": ach / state["peak32"], "kernel_ms": kernel_ms,
+                            "express_ms": float(np.mean(em)), "pair_tests_per_launch": tests,
+                            "flops_per_pair_test": FLOPS_PER_PAIR_TEST, "traffic": None,
+                            "note": "pair tests = mobile atoms x receptor atoms of the swept leaves + intra-mobile pairs"}}
+        out.update(spread(ms))
+        if cpu:
+            co = c_oracle_module().COracle(eng.mobile, eng.receptor, eng.params)
+            n = 8192
+            out["cpu_baseline"] = cpu_contacts_baseline(co, (tors[:n], xf[:n], rot[:n]), budget_s=8.0,
+                                                        what=" (first %d of %d)" % (n, C5_POP))
+    sh.close()
     batch.close()
     return out
 
 
-def c_oracle_for(name):
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import c_oracle
-    params, lig, rec, tors, xf = build_system(name)
-    return c_oracle.COracle(lig, rec, params), tors, xf
+def bench_dense_and_c2(ctx, state):
+    """N = 1 only: the dense (no culling) run of the headline workload and configs[1]."""
+    torch = ctx.torch
+    from gaudi_b200 import model as M
+    from gaudi_b200.engine import Engine
+    res = {}
+    pop, L, T, R = WORKLOADS["c3"]
+    dense = Engine(state["lig"], state["rec"], M.ContactParams(cull=False), device=ctx.local)
+    dense.set_profiling(True)
+    t_d, x_d = torch.as_tensor(state["tors"]).to(ctx.dev), torch.as_tensor(state["xf"]).to(ctx.dev)
+    ms = float(np.mean(ctx.time_steps(lambda: dense.evaluate(t_d, x_d), 3, warmup=2)))
+    kt = dense.kernel_times()
+    tests = dense.last_pair_tests()
+    ach = tests * FLOPS_PER_PAIR_TEST / (kt["sweep"] * 1e-3) / 1e12
+    res["dense"] = {"value": pop / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms,
+                    "roofline": {"achieved": ach, "peak": state["peak32"], "frac": ach / state["peak32"], "unit": "TFLOP/s",
+                                 "kernel_ms": kt["sweep"], "pair_tests_per_launch": tests,
+                                 "note": "in SURVEY.md's 10-flop units; by executed FP32 work (7 flops per pair test) 0.7 x this"}}
+    dense.close()
+    params, lig, rec, tors, xf = build_system("c2")
+    e2 = Engine(lig, rec, params, device=ctx.local)
+    t_d, x_d = torch.as_tensor(tors).to(ctx.dev), torch.as_tensor(xf).to(ctx.dev)
+    ms = float(np.mean(ctx.time_steps(lambda: e2.evaluate(t_d, x_d), 20, warmup=3)))
+    res["configs1_pop4096_rec5k"] = {"value": tors.shape[0] / (ms * 1e-3), "unit": "individuals/s", "ms_per_step": ms}
+    e2.close()
+    return res
 
 
-def cpu_baseline(name, sample):
-    """The oracle's C restatement (fp64, cell list, every host core) on a bounded sample of the
-    same population; the numpy restatement it is validated against is timed beside it."""
-    co, tors, xf = c_oracle_for(name)
-    sample = min(sample, len(tors))
-    co.evaluate(tors[:256], xf[:256])                      # warm
-    reps, dt = 0, 0.0
-    while dt < 10.0 and reps < 40:                         # about 10 s of host work
-        t0 = time.perf_counter()
-        co.evaluate(tors[:sample], xf[:sample])
-        dt += time.perf_counter() - t0
-        reps += 1
-    sample_total = sample * reps
-    out = {"value": sample_total / dt, "unit": "individuals/s", "cores": co.workers, "kind": "port",
-           "sample": "%d passes over the first %d individuals of the same population, C restatement of the reference's CPU path "
-                     "(oracle/gaudi_oracle.c: fp64 express + zone + DetectClash rule + scoring, cell list), "
-                     "%d host threads, %.1f s" % (reps, sample, co.workers, dt)}
-    try:
-        cores = os.cpu_count() or 1
-        pool = CpuPool(name, cores)
-        n_np = 64 * cores
-        dt2, _ = pool.run(0, n_np)
-        pool.close()
-        out["numpy_port"] = {"value": n_np / dt2, "unit": "individuals/s", "cores": cores,
-                             "sample": "%d individuals, numpy/scipy restatement (oracle/gaudi_oracle.py), %d processes" % (n_np, cores)}
-    except Exception as exc:
-        out["numpy_port"] = {"error": repr(exc)[:160]}
-    return out
+def run_b200(args):
+    ctx = Ctx(args)
+    out, state = bench_c3(ctx)
+    first = ctx.rank == 0 and ctx.world == 1
+    if not args.quick:
+        for key, fn in (("rmsd", bench_rmsd), ("configs4", bench_c5)):
+            try:
+                side = fn(ctx, state, cpu=first and not args.no_cpu)
+            except Exception as exc:                   # a side measurement must never sink the headline
+                side = {"error": repr(exc)[:300]}
+            if ctx.rank == 0:
+                out[key] = side
+        if first:
+            try:
+                out.update(bench_dense_and_c2(ctx, state))
+            except Exception as exc:
+                out["dense"] = {"error": repr(exc)[:300]}
+    if first and not args.no_cpu:
+        co = c_oracle_module().COracle(state["lig"], state["rec"], state["params"])
+        n = min(args.cpu_sample, len(state["tors"]))
+        out["cpu_baseline"] = cpu_contacts_baseline(co, (state["tors"][:n], state["xf"][:n]))
+    state["sh"].close()
+    if ctx.world > 1:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+def run_rmsd_only(args):
+    ctx = Ctx(args)
+    from gaudi_b200.engine import measure_fp32_peak
+    state = {"peak32": measure_fp32_peak(ctx.local)}
+    side = bench_rmsd(ctx, state, cpu=(ctx.world == 1 and not args.no_cpu))
+    if ctx.rank == 0:
+        line = {"metric": side["metric"], "value": side["value"], "unit": side["unit"], "n_gpus": ctx.world, "steps": 10,
+                "warmup": 3, "ms_per_step": side["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+        line.update({k: v for k, v in side.items() if k not in line})
+        print(json.dumps(line), flush=True)
+    if ctx.world > 1:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------------
@@ -584,9 +695,22 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.workload == "rmsd":
+        base = cpu_rmsd_baseline(budget_s=max(4.0, min(30.0, 2.0 * args.steps)))
+        value = base["value"]
+        out = {"impl": "reference", "metric": "RMSD pairs/s", "value": value, "unit": "pairs/s", "n_gpus": world,
+               "steps": 1, "warmup": 0, "ms_per_step": None, "higher_is_better": True, "scaling": "strong",
+               "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": RMSD_TEXT},
+               "cpu_baseline": base,
+               "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+               "gpu_launches": 0}
+        print(json.dumps(out), flush=True)
+        return
     name = args.workload
     pop, L, T, R = WORKLOADS[name]
-    co, tors, xf = c_oracle_for(name)
+    params, lig, rec, tors, xf = build_system(name)
+    co = c_oracle_module().COracle(lig, rec, params)
     cores = co.workers
     # one step = one batch of the same population, sized from a probe so that a step is about
     # 1.5 s of host work (the whole 65,536-individual batch on a 16-core box)
@@ -594,27 +718,29 @@ def run_reference(args):
     co.evaluate(tors[:4096], xf[:4096])
     speed = 4096 / (time.perf_counter() - t0)
     per_step = int(min(pop, max(cores * 64, speed * 1.5)))
-    for w in range(min(args.warmup, 1)):
+    warm = min(args.warmup, 2)                    # the host path has no clocks or caches to ramp: two passes at most
+    for w in range(warm):
         co.evaluate(tors[:per_step], xf[:per_step])
-    total = 0.0
+    times = []
     for k in range(args.steps):
         lo = (k * per_step) % max(1, pop - per_step + 1)
         t0 = time.perf_counter()
         co.evaluate(tors[lo:lo + per_step], xf[lo:lo + per_step])
-        total += time.perf_counter() - t0
+        times.append(time.perf_counter() - t0)
+    total = sum(times)
     value = per_step * args.steps / total
     sample = ("each step = %d individuals of the %d-individual population; C restatement (fp64, cell list) of "
               "the reference's Chimera-based CPU path (the reference itself needs UCSF Chimera + Python 2 and "
               "cannot run on this box), %d host threads" % (per_step, pop, cores))
     out = {"impl": "reference", "metric": "individuals scored/sec (expr + Contacts)", "value": value,
-           "unit": "individuals/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True,
+           "unit": "individuals/s", "n_gpus": world, "steps": args.steps,
+           "warmup": warm, "warmup_requested": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True,
            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": "configs[2]: pop %d x (%d-atom, %d-torsion ligand) vs %d-atom receptor box, "
-                                  "Torsion+Search express + Contacts(clashes, hydrophobic)" % (pop, L, T, R)},
+           "config": {"workload": C3_TEXT if name == "c3" else "configs[1]: pop %d, %d-atom ligand, %d-atom receptor" % (pop, L, R)},
            "cpu_baseline": {"value": value, "unit": "individuals/s", "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": value, "unit": "individuals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
+    out.update(spread(np.array(times) * 1e3))
     print(json.dumps(out), flush=True)
 
 
@@ -624,18 +750,18 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["rmsd"])
+    ap.add_argument("--workload", default="c3", choices=["c3", "c2", "rmsd"])
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how the fitness rows are gathered (peer-memory stores, or an NCCL all_gather)")
     ap.add_argument("--cpu-sample", type=int, default=65536, help="individuals in the CPU baseline sample")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
-    ap.add_argument("--quick", action="store_true", help="skip the dense / configs[1] / RMSD side measurements")
+    ap.add_argument("--quick", action="store_true", help="skip the RMSD / configs[4] / dense / configs[1] side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
-        if args.workload == "rmsd":
-            args.workload = "c3"
         run_reference(args)
     elif args.workload == "rmsd":
-        run_rmsd(args)
+        run_rmsd_only(args)
     else:
         run_b200(args)
 

@@ -216,9 +216,10 @@ class Engine(object):
         out[order] = front.cpu().numpy()
         return out
 
-    def similar_lists(self, bits, n, row0=0):
+    def similar_lists(self, bits, n, row0=0, to_host=True):
         """Partner lists of a similarity bitmask from ``rmsd_matrix`` (rows ``row0 ...`` of the
-        ``n x n`` matrix): ``(ptr int64 (rows + 1,), idx int32)`` host arrays, self excluded."""
+        ``n x n`` matrix): ``(ptr int64 (rows + 1,), idx int32)``, self excluded; host arrays, or
+        device tensors with ``to_host=False`` (what ``parallel.sharded_similar_lists`` gathers)."""
         rows = int(bits.shape[0])
         counts = torch.empty(rows, dtype=torch.int32, device=self.torch_device)
         _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
@@ -229,6 +230,8 @@ class Engine(object):
         idx = torch.empty(max(total, 1), dtype=torch.int32, device=self.torch_device)
         _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
                                              None, _dev_ptr(ptr), _dev_ptr(idx), self._stream()))
+        if not to_host:
+            return ptr, idx[:total]
         return ptr.cpu().numpy(), idx[:total].cpu().numpy()
 
     # -- geometric restraint objectives (Distance / Angle) -----------------------------------

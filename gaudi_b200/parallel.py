@@ -11,6 +11,17 @@ import torch
 import torch.distributed as dist
 
 
+def _all_gather_into(out, inp, group=None):
+    """``all_gather_into_tensor``; device tensors under a gloo group (tests with two ranks on one
+    GPU, where NCCL cannot run) are staged through the host."""
+    if inp.is_cuda and dist.get_backend(group) == "gloo":
+        staged = torch.empty(out.shape, dtype=out.dtype)
+        dist.all_gather_into_tensor(staged, inp.cpu(), group=group)
+        out.copy_(staged)
+    else:
+        dist.all_gather_into_tensor(out, inp, group=group)
+
+
 def shard_bounds(n, world):
     """Contiguous, balanced blocks: rank r owns [b[r], b[r+1])."""
     return [(n * r) // world for r in range(world + 1)]
@@ -89,6 +100,54 @@ def sharded_rmsd_bits(rmsd_rows, coords, group=None, counts=None):
     if even:
         return allb
     return torch.cat([allb[r * m:r * m + counts[r]] for r in range(world)])
+
+
+def sharded_similar_lists(engine, coords, counts, threshold=2.5, group=None):
+    """Row-block sharded similarity (gaudi/similarity.py:36-75 over all pairs, the input of the
+    niching pass gaudi/algorithms.py:139-155) where only the PARTNER LISTS travel: ``coords`` is this
+    rank's ``(n_r, A, 3)`` float32 block of conformers (``counts[r]`` conformers on rank r); the
+    conformers are all-gathered (the one real exchange of this stage: every rank needs every
+    column), each rank computes its rows of the bitmask and compacts them into partner lists on its
+    own GPU, and the lists — a few hundred KB where the bitmask is tens of MB — are gathered.
+    Returns ``(ptr int64 (N + 1,), idx int32)`` as device tensors on every rank; the bitmask rows stay
+    where they were computed."""
+    world, rank = _world(group)
+    counts = [int(c) for c in counts]
+    n = sum(counts)
+    row0 = sum(counts[:rank])
+    if world == 1:
+        _, bits = engine.rmsd_matrix(coords, threshold=threshold, values=False)
+        return engine.similar_lists(bits, n, to_host=False)
+    m = max(counts)
+    even = min(counts) == m
+    if even:
+        padded = coords.contiguous()
+    else:
+        padded = torch.zeros((m,) + tuple(coords.shape[1:]), dtype=coords.dtype, device=coords.device)
+        padded[:coords.shape[0]] = coords
+    allc = torch.empty((world * m,) + tuple(coords.shape[1:]), dtype=coords.dtype, device=coords.device)
+    _all_gather_into(allc, padded, group)
+    if not even:
+        allc = torch.cat([allc[r * m:r * m + counts[r]] for r in range(world)])
+    _, bits = engine.rmsd_matrix(allc, row0=row0, row1=row0 + counts[rank], threshold=threshold, values=False)
+    ptr, idx = engine.similar_lists(bits, n, row0=row0, to_host=False)
+    # per-row partner counts of every rank (fixed size), then the list entries padded to the longest
+    per_row = torch.zeros(m, dtype=torch.int64, device=coords.device)
+    per_row[:counts[rank]] = ptr[1:] - ptr[:-1]
+    all_rows = torch.empty(world * m, dtype=torch.int64, device=coords.device)
+    _all_gather_into(all_rows, per_row, group)
+    all_rows = all_rows.view(world, m)
+    totals = all_rows.sum(dim=1).tolist()                 # one device-to-host copy
+    cap = max(max(totals), 1)
+    mine = torch.zeros(cap, dtype=torch.int32, device=coords.device)
+    mine[:idx.shape[0]] = idx
+    all_idx = torch.empty(world * cap, dtype=torch.int32, device=coords.device)
+    _all_gather_into(all_idx, mine, group)
+    rows = torch.cat([all_rows[r, :counts[r]] for r in range(world)])
+    full_ptr = torch.zeros(n + 1, dtype=torch.int64, device=coords.device)
+    torch.cumsum(rows, 0, out=full_ptr[1:])
+    full_idx = torch.cat([all_idx[r * cap:r * cap + int(totals[r])] for r in range(world)])
+    return full_ptr, full_idx
 
 
 # ---------------------------------------------------------------------------------------------

@@ -71,6 +71,16 @@ def _exchange_worker(rank, world, port, out):
                                     and bool(torch.equal(c_last[:pop], want_c)))
         dist.barrier()
         sh.close()
+    # row-block sharded similarity: only the partner lists travel
+    conf = synth.make_conformers(1500, 60, seed=4).astype(np.float32)
+    b = parallel.shard_bounds(1500, world)
+    mine = torch.as_tensor(conf[b[rank]:b[rank + 1]]).to(eng.torch_device)
+    ptr, idx = parallel.sharded_similar_lists(eng, mine, [b[r + 1] - b[r] for r in range(world)], threshold=2.5)
+    _, bits = eng.rmsd_matrix(conf, threshold=2.5, values=False)
+    ptr1, idx1 = eng.similar_lists(bits, 1500)
+    results["lists"] = bool(np.array_equal(ptr.cpu().numpy(), ptr1) and np.array_equal(idx.cpu().numpy(), idx1)
+                            and len(idx1) > 0)
+    dist.barrier()
     # host-resident population: shared page-locked table, each rank uploads and downloads its rows
     hs = parallel.HostShardedEvaluator(eng, 6000, want_xyz=True)
     if rank == 0:

@@ -16,13 +16,15 @@ mode = sys.argv[1] if len(sys.argv) > 1 else "culled"
 pop = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
 if mode == "rotamers":          # BASELINE configs[4] through bench.py's builder
     import bench
-
-    def timed(fn, reps):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        return 1.0
-    print(bench.rotamers_measurement(torch, torch.device("cuda", 0), timed))
+    batch, tors, xf, rot = bench.build_c5(0)
+    eng = batch.engines[0][0]
+    eng.set_profiling(True)
+    n = min(pop, len(tors))
+    t, x, r = (torch.as_tensor(v[:n]).cuda() for v in (tors, xf, rot))
+    for _ in range(4):
+        eng.evaluate(t, x, r)
+    torch.cuda.synchronize()
+    print(mode, n, eng.kernel_times(), eng.last_pair_tests())
     sys.exit(0)
 params = M.ContactParams(cull=(mode != "dense"), tiled=(mode == "tiled"))
 lig = synth.make_ligand(40, 10, seed=1)
