@@ -38,6 +38,7 @@ SIGNATURES = {
     "gmm_exchange_create": (_i, [_vp, _i, _i, _i, _vp]),
     "gmm_exchange_connect": (_i, [_vp, _vp]),
     "gmm_exchange_publish": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(_vp), C.POINTER(_vp), _vp]),
+    "gmm_evaluate_publish": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, C.POINTER(_vp), C.POINTER(_vp), _vp]),
     "gmm_exchange_state": (_i, [_vp, C.POINTER(C.c_uint), C.POINTER(_i), C.POINTER(_vp), C.POINTER(_vp)]),
     "gmm_exchange_destroy": (_i, [_vp]),
     "gmm_set_geometry": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

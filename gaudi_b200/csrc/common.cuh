@@ -74,6 +74,14 @@ struct GeoTerm {
     int has_tolerance, planar;
 };
 
+// Where a Contacts kernel additionally stores each finished individual's scores when a fitness
+// exchange is attached (exchange.cu): every rank's gather block, reached through peer mappings with
+// plain stores.  Lives in device memory; the kernel reads the owner's epoch to pick the buffer.
+struct MirrorTable {
+    int n, rank, max_rows, pad;
+    unsigned char* base[GMM_MAX_PEERS];
+};
+
 struct PairScore {
     long long clash_fx;  // |volume overlap| * 2^32 (0 if not a clash)
     long long hydro_fx;  // LJ-like energy * 2^32   (0 if not a hydrophobic contact)
@@ -215,6 +223,9 @@ struct gmm_ctx {
     void* d_stage = nullptr; size_t stage_bytes = 0;
     void* d_rmsd_ws = nullptr; size_t rmsd_ws_bytes = 0;   // centred conformers + norms (rmsd.cu, bitmask path)
     void* exchange = nullptr;        // gmm::Exchange (exchange.cu): fitness exchange with the other ranks' GPUs
+    const gmm::MirrorTable* d_mirror = nullptr;   // device copy of the peers' blocks (set by gmm_exchange_connect)
+    int pub_row0 = -1;               // >= 0 while gmm_evaluate_publish runs: row of individual 0 in the gathered table
+    bool pub_done = false;           // the Contacts kernel stored the rows itself
 };
 
 namespace gmm {

@@ -37,6 +37,8 @@ struct FusedArgs {
     int ind_bytes;
     int count_tests;  // 1: tally the executed pair tests (gmm_last_pair_tests); on while profiling is enabled
     int tma_pose;     // 1: stage each pose with one TMA bulk copy (size and alignment permit)
+    const MirrorTable* mirror;   // != NULL: also store the rows into every rank's gather block (exchange.cu)
+    int mirror_row0;
 };
 
 struct Acc { long long cfx, hfx; int nc, nh; };
@@ -647,6 +649,21 @@ contacts_fused_kernel(const FusedArgs f) {
         f.scores[2 * (size_t)p] = clash;
         f.scores[2 * (size_t)p + 1] = hydro;
         if (f.counts) { f.counts[2 * (size_t)p] = (int32_t)nc; f.counts[2 * (size_t)p + 1] = (int32_t)nh; }
+        if (f.mirror != nullptr) {
+            // fitness exchange: the row goes to every rank's table now, while the other individuals
+            // are still being scored; plain stores through the peer mappings.  The buffer is the one
+            // of the epoch the signal kernel behind this one will publish (exchange.cu).
+            const MirrorTable& mt = *f.mirror;
+            const unsigned parity = (*reinterpret_cast<const unsigned*>(mt.base[mt.rank] + 4 * GMM_MAX_PEERS) + 1u) & 1u;
+            const size_t buf = ((size_t)mt.max_rows * 24 + 255) / 256 * 256;
+            const size_t row = (size_t)f.mirror_row0 + p;
+#pragma unroll 1
+            for (int r = 0; r < mt.n; ++r) {
+                unsigned char* b = mt.base[r] + 256 + parity * buf;
+                reinterpret_cast<double2*>(b)[row] = make_double2(clash, hydro);
+                reinterpret_cast<int2*>(b + (size_t)mt.max_rows * 16)[row] = make_int2((int)nc, (int)nh);
+            }
+        }
     }
 }
 
@@ -682,6 +699,8 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.mm_pairs = c->d_mm_pairs; f.mm_c2 = c->d_mm_c2; f.n_mm = c->n_mm;
     f.scores = scores; f.counts = counts;
     f.count_tests = c->prof ? 1 : 0;
+    f.mirror = (c->pub_row0 >= 0) ? c->d_mirror : nullptr;
+    f.mirror_row0 = c->pub_row0;
     const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
     const size_t pose_bytes = (size_t)c->M * 3 * sizeof(float);
@@ -709,6 +728,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     kernel<<<S == 1 ? (P + 3) / 4 : P, 128, smem, s>>>(f);
     GMM_LAUNCH_CHECK("contacts_fused_kernel");
     if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[3], s)); c->ev_used[1] = true; c->ev_used[2] = false; }
+    c->pub_done = f.mirror != nullptr;
     *handled = 1;
     return GMM_OK;
 }

@@ -76,7 +76,8 @@ exchange_publish_kernel(const ExchangeArgs a) {
     if (!last) return;
     // every block of this rank has stored and fenced: publish, then wait for the others
     if ((int)threadIdx.x < a.world) {
-        __threadfence_system();
+        // (the release store orders everything this block has observed, i.e. every block's fenced
+        // stores, before the flag: no separate fence)
         unsigned* flag = &reinterpret_cast<ExchangeHeader*>(a.base[threadIdx.x])->flags[a.rank];
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(e) : "memory");
         const unsigned* mine = &self->flags[threadIdx.x];
@@ -97,8 +98,36 @@ exchange_publish_kernel(const ExchangeArgs a) {
     if (threadIdx.x == 0) { self->done_blocks = 0u; self->epoch = e; }
 }
 
+// Publish + wait only: used when the Contacts kernel has already stored the rows itself (they are
+// complete and visible system-wide once that kernel has finished, which stream order guarantees).
+__global__ void __launch_bounds__(32)
+exchange_signal_kernel(const ExchangeArgs a) {
+    ExchangeHeader* self = reinterpret_cast<ExchangeHeader*>(a.base[a.rank]);
+    const unsigned e = self->epoch + 1u;
+    if ((int)threadIdx.x < a.world) {
+        unsigned* flag = &reinterpret_cast<ExchangeHeader*>(a.base[threadIdx.x])->flags[a.rank];
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(e) : "memory");
+        const unsigned* mine = &self->flags[threadIdx.x];
+        unsigned long long t0 = 0;
+        for (unsigned spin = 0;; ++spin) {
+            unsigned seen;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+            if ((int)(seen - e) >= 0) break;
+            if ((spin & 1023u) == 1023u) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 10000000000ull) { self->error = 1u; break; }
+            }
+        }
+    }
+    __syncwarp();
+    if (threadIdx.x == 0) self->epoch = e;
+}
+
 struct Exchange {
     int world = 0, rank = 0, max_rows = 0;
+    MirrorTable* d_mirror = nullptr;
     unsigned char* local = nullptr; size_t bytes = 0;
     unsigned char* peer[GMM_MAX_PEERS] = {nullptr};
     bool connected = false;
@@ -111,6 +140,17 @@ using namespace gmm;
 
 static Exchange* ex_of(gmm_ctx* c) { return static_cast<Exchange*>(c->exchange); }
 
+static int upload_mirror(gmm_ctx* c, Exchange* x) {
+    MirrorTable mt;
+    memset(&mt, 0, sizeof(mt));
+    mt.n = x->world; mt.rank = x->rank; mt.max_rows = x->max_rows;
+    for (int r = 0; r < x->world; ++r) mt.base[r] = x->peer[r];
+    if (!x->d_mirror) GMM_CUDA(cudaMalloc((void**)&x->d_mirror, sizeof(MirrorTable)));
+    GMM_CUDA(cudaMemcpy(x->d_mirror, &mt, sizeof(mt), cudaMemcpyHostToDevice));
+    c->d_mirror = x->d_mirror;
+    return GMM_OK;
+}
+
 extern "C" {
 
 int gmm_exchange_destroy(gmm_ctx* c) {
@@ -121,8 +161,10 @@ int gmm_exchange_destroy(gmm_ctx* c) {
     for (int r = 0; r < x->world; ++r)
         if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
     if (x->local) cudaFree(x->local);
+    if (x->d_mirror) cudaFree(x->d_mirror);
     delete x;
     c->exchange = nullptr;
+    c->d_mirror = nullptr;
     return GMM_OK;
 }
 
@@ -160,6 +202,7 @@ int gmm_exchange_create(gmm_ctx* c, int world, int rank, int max_rows, unsigned 
     memcpy(handle_out, &h, sizeof(h));
     x->connected = (world == 1);
     c->exchange = x;
+    if (world == 1) return upload_mirror(c, x);
     return GMM_OK;
 }
 
@@ -180,7 +223,7 @@ int gmm_exchange_connect(gmm_ctx* c, const unsigned char* handles_h) {
         x->peer[r] = static_cast<unsigned char*>(p);
     }
     x->connected = true;
-    return GMM_OK;
+    return upload_mirror(c, x);
 }
 
 int gmm_exchange_publish(gmm_ctx* c, const double* scores_d, const int32_t* counts_d, int row0, int n_rows,
@@ -199,6 +242,39 @@ int gmm_exchange_publish(gmm_ctx* c, const double* scores_d, const int32_t* coun
     a.scores = scores_d; a.counts = counts_d; a.row0 = row0; a.n_rows = n_rows;
     exchange_publish_kernel<<<x->world * kExSlices, 256, 0, (cudaStream_t)stream>>>(a);
     GMM_LAUNCH_CHECK("exchange_publish_kernel");
+    x->host_epoch += 1;
+    const unsigned parity = x->host_epoch & 1u;
+    if (gathered_scores_out) *gathered_scores_out = exchange_scores(x->local, x->max_rows, parity);
+    if (gathered_counts_out) *gathered_counts_out = exchange_counts(x->local, x->max_rows, parity);
+    return GMM_OK;
+}
+
+int gmm_evaluate_publish(gmm_ctx* c, int P, const double* torsion_deg_d, const double* xform_d,
+                         const double* rot_allele_d, float* out_xyz_d, double* out_scores_d, int32_t* out_counts_d,
+                         int row0, double** gathered_scores_out, int32_t** gathered_counts_out, void* stream) {
+    if (!c || !c->exchange) { set_error("gmm_evaluate_publish: no exchange on this context"); return GMM_ESTATE; }
+    Exchange* x = ex_of(c);
+    if (!x->connected) { set_error("gmm_evaluate_publish: gmm_exchange_connect has not been called"); return GMM_ESTATE; }
+    if (row0 < 0 || P < 0 || row0 + P > x->max_rows) {
+        set_error("gmm_evaluate_publish: rows [%d,%d) outside [0,%d]", row0, row0 + P, x->max_rows);
+        return GMM_EINVAL;
+    }
+    if (!out_scores_d || !out_counts_d) { set_error("gmm_evaluate_publish: NULL output"); return GMM_EINVAL; }
+    // the one-kernel Contacts path stores every finished row into every rank's table itself
+    c->pub_row0 = row0;
+    c->pub_done = false;
+    int rc = gmm_evaluate(c, P, torsion_deg_d, xform_d, rot_allele_d, out_xyz_d, out_scores_d, out_counts_d, stream);
+    c->pub_row0 = -1;
+    if (rc) return rc;
+    if (!c->pub_done || P == 0)      // tiled Contacts path (or nothing to score): copy the rows, then signal
+        return gmm_exchange_publish(c, out_scores_d, out_counts_d, row0, P, gathered_scores_out, gathered_counts_out, stream);
+    DeviceGuard g(c->device);
+    ExchangeArgs a;
+    for (int r = 0; r < GMM_MAX_PEERS; ++r) a.base[r] = r < x->world ? x->peer[r] : nullptr;
+    a.world = x->world; a.rank = x->rank; a.max_rows = x->max_rows;
+    a.scores = nullptr; a.counts = nullptr; a.row0 = row0; a.n_rows = P;
+    exchange_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
+    GMM_LAUNCH_CHECK("exchange_signal_kernel");
     x->host_epoch += 1;
     const unsigned parity = x->host_epoch & 1u;
     if (gathered_scores_out) *gathered_scores_out = exchange_scores(x->local, x->max_rows, parity);

@@ -207,6 +207,19 @@ class FitnessExchange(object):
             int(row0), int(scores.shape[0]), C.byref(ps), C.byref(pc), self.engine._stream()))
         return self._views(ps, pc)
 
+    def evaluate_publish(self, torsions, xforms, rot_alleles, scores, counts, row0):
+        """``Engine.evaluate`` into ``scores`` / ``counts`` + ``publish`` in one call
+        (``gmm_evaluate_publish``): the Contacts kernel stores the rows into every rank's table as
+        the individuals finish."""
+        from . import _lib
+        C = self._C
+        ps, pc = C.c_void_p(), C.c_void_p()
+        p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        _lib.check(self._L.gmm_evaluate_publish(
+            self.engine._h, int(scores.shape[0]), p(torsions), p(xforms), p(rot_alleles), None, p(scores), p(counts),
+            int(row0), C.byref(ps), C.byref(pc), self.engine._stream()))
+        return self._views(ps, pc)
+
     def state(self):
         """Synchronise; ``(epochs completed, timed_out, scores view, counts view)`` of the last epoch."""
         from . import _lib
@@ -252,12 +265,15 @@ class ShardedEvaluator(object):
         ``(scores [P, 2] fp64, counts [P, 2] int32)`` with every rank's rows, on every rank."""
         n = self.hi - self.lo
         s, c = self.scores[:n], self.counts[:n]
+        if self.kind == "peer":
+            eng = self.engine
+            t, x, r = (eng._dev(torsions, torch.float64), eng._dev(xforms, torch.float64),
+                       eng._dev(rot_alleles, torch.float64))
+            gs, gc = self.exchange.evaluate_publish(t, x, r, s, c, self.lo)
+            return gs[:self.population], gc[:self.population]
         self.engine.evaluate(torsions, xforms, rot_alleles, scores_out=s, counts_out=c)
         if self.kind == "none":
             return s, c
-        if self.kind == "peer":
-            gs, gc = self.exchange.publish(s, c, self.lo)
-            return gs[:self.population], gc[:self.population]
         dist.all_gather_into_tensor(self._gs, self.scores, group=self.group)
         dist.all_gather_into_tensor(self._gc, self.counts, group=self.group)
         m, b = self.max_shard, self.bounds

@@ -214,6 +214,13 @@ int gmm_exchange_create(gmm_ctx* ctx, int world, int rank, int max_rows, unsigne
 int gmm_exchange_connect(gmm_ctx* ctx, const unsigned char* handles_h /*[world, 64]*/);
 int gmm_exchange_publish(gmm_ctx* ctx, const double* scores_d, const int32_t* counts_d, int row0, int n_rows,
                          double** gathered_scores_out, int32_t** gathered_counts_out, void* stream);
+/* gmm_evaluate followed by gmm_exchange_publish of its rows, as one call: with the one-kernel
+ * Contacts path every individual's row is stored into every rank's table by the Contacts kernel
+ * itself the moment it is finished (the transfer hides behind the scoring of the others), and only
+ * the epoch flags and the wait remain behind it.  Same outputs as the two calls. */
+int gmm_evaluate_publish(gmm_ctx* ctx, int P, const double* torsion_deg_d, const double* xform_d,
+                         const double* rot_allele_d, float* out_xyz_d, double* out_scores_d, int32_t* out_counts_d,
+                         int row0, double** gathered_scores_out, int32_t** gathered_counts_out, void* stream);
 int gmm_exchange_state(gmm_ctx* ctx, unsigned* epoch_out, int* error_out, double** gathered_scores_out,
                        int32_t** gathered_counts_out);
 int gmm_exchange_destroy(gmm_ctx* ctx);
