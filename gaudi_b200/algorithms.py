@@ -95,7 +95,36 @@ def ea_mu_plus_lambda(population, toolbox, mu, lambda_, cxpb, mutpb, ngen, cfg=N
         logbook.append({"gen": gen, "nevals": nevals, "speed": nevals / max(t2 - t1, 1e-9)})
         if verbose:
             logger.log(100, "gen %d  nevals %d  %.2f ev/s", gen, nevals, logbook[-1]["speed"])
+        # gaudi/algorithms.py:197-201: a copy of the elite every check_every generations, in case
+        # the run is stopped later
+        if halloffame and cfg is not None and cfg.output.check_every and not gen % cfg.output.check_every:
+            try:
+                dump_population(halloffame, cfg, subdir="check{}".format(gen))
+            except Exception:
+                logger.warning("Could not write checkpoint for gen #%s", gen)
     return population, logbook
+
+
+def dump_population(population, cfg, subdir=None):
+    """gaudi/algorithms.py:205-223: ``Individual.write`` for every member (``<name>_<i>.zip``) plus
+    the ``<name>.gaudi-output`` yaml index of file name -> scores.  Returns the index path."""
+    import os
+    from time import strftime
+    import yaml
+    results = {"GAUDI.objectives": ["{} ({})".format(obj.name, obj.module) for obj in cfg.objectives],
+               "GAUDI.results": {}}
+    basepath = cfg.output.path
+    if subdir is not None:
+        basepath = os.path.join(cfg.output.path, subdir)
+        os.makedirs(basepath, exist_ok=True)
+    for i, ind in enumerate(population):
+        filename = ind.write(i, path=basepath)
+        results["GAUDI.results"][os.path.basename(filename)] = [float(v) for v in ind.fitness.values]
+    gaudi_output = os.path.join(basepath, cfg.output.name + ".gaudi-output")
+    with open(gaudi_output, "w+") as out:
+        out.write("# Generated by gaudi_b200 (GaudiMM hot path on B200) on {}\n\n".format(strftime("%Y-%m-%d %H:%M:%S")))
+        out.write(yaml.safe_dump(results, default_flow_style=False))
+    return gaudi_output
 
 
 def launch(cfg, device=0, seed=None, group=None):
@@ -156,3 +185,16 @@ def launch(cfg, device=0, seed=None, group=None):
                                         halloffame=elite, verbose=cfg.output.verbose, environment=environment)
     environment.batch.shutdown()
     return population, log, elite
+
+
+def run(cfg, device=0, seed=None, group=None):
+    """What ``gaudi run`` does after parsing its input (gaudi/cli/gaudi_run.py:137-178): ``launch``,
+    then write the elite with ``dump_population``.  Returns ``(population, logbook, elite, index
+    path)``; ranks other than 0 of a multi-GPU job return ``(None, None, None, None)``."""
+    import os
+    population, log, elite = launch(cfg, device=device, seed=seed, group=group)
+    if population is None:
+        return None, None, None, None
+    os.makedirs(cfg.output.path, exist_ok=True)
+    index = dump_population(elite, cfg)
+    return population, log, elite, index

@@ -100,6 +100,35 @@ class MolecularIndividual(object):
     def similar(self, other):
         return self._similarity(self, other, *self.cfg.similarity.args, **self.cfg.similarity.kwargs)
 
+    def write(self, i, path=None):
+        """gaudi/base.py:231-266: one zip per individual — every gene's file (Molecule genes: mol2
+        with the expressed coordinates; the others: their allele as text) plus a ``.gaudi`` yaml
+        naming them and the scores.  (The yaml is named after the LAST gene, as in the reference,
+        whose loop variable shadows the job name.)"""
+        import os
+        import yaml
+        from zipfile import ZipFile, ZIP_DEFLATED, ZIP_STORED
+        path = path if path is not None else self.cfg.output.path
+        name = self.cfg.output.name
+        compress = ZIP_DEFLATED if self.cfg.output.compress else ZIP_STORED
+        if any(g._expressed_coordinates is None for g in self._molecules.values()):
+            env = getattr(self.cfg, "_environment", None)      # expression happens on the GPU, in batches
+            if env is None:
+                raise RuntimeError("write(): the individual has never been evaluated and the job has no environment")
+            env.evaluate_population([self])
+        zipfilename = os.path.join(path, "{}_{:03d}.zip".format(name, i))
+        with ZipFile(zipfilename, "w", compress) as z:
+            output = OrderedDict()
+            for name, gene in self.genes.items():
+                filename = gene.write(path, "{}_{:03d}".format(name, i))
+                if filename:
+                    z.write(filename, os.path.basename(filename))
+                    os.remove(filename)
+                    output[name] = os.path.basename(filename)
+            output["score"] = [float(v) for v in self.fitness.values]
+            z.writestr("{}_{:03d}.gaudi".format(name, i), yaml.safe_dump(dict(output), default_flow_style=False))
+        return zipfilename
+
     def find_molecule(self, name):
         try:
             return self._molecules[name]

@@ -1,7 +1,7 @@
 """Molecule gene (gaudi/genes/molecule.py): the *source of static topology, coordinates and
-radii* for the hot path.  Fragment-library building, AddH, pdbfixer and mol2 writing are out of
-scope; a Molecule here is one structure file (PDB with
-CONECT/distance-perceived bonds, or mol2)."""
+radii* for the hot path, and the writer of a result's structure file.  Fragment-library building,
+AddH and pdbfixer are out of scope; a Molecule here is one structure
+file (PDB with CONECT/distance-perceived bonds, or mol2)."""
 from __future__ import annotations
 
 import os
@@ -70,6 +70,27 @@ class Molecule(GeneProvider):
 
     def radii(self):
         return molio.vdw_radii(self.mol, self.vdw_radii_overrides)
+
+    def write(self, path=None, name=None, absolute=None, combined_with=None, filetype="mol2"):
+        """gaudi/genes/molecule.py:235-261: the molecule with its EXPRESSED coordinates as
+        ``<path>/<name>_<gene name>.mol2`` (or ``.pdb``); returns the file name."""
+        import tempfile
+        if path and name:
+            fullname = os.path.join(path, "{}_{}.{}".format(name, self.name, filetype))
+        elif absolute:
+            fullname = absolute
+        else:
+            handle, fullname = tempfile.mkstemp(prefix="gaudi", suffix=".{}".format(filetype))
+            os.close(handle)
+        if combined_with:
+            raise NotImplementedError("Molecule.write(combined_with=...) is not available on the B200 path")
+        if filetype == "mol2":
+            molio.write_mol2(self.mol, fullname, xyz=self.xyz(), title=self.name)
+        elif filetype == "pdb":
+            molio.write_pdb(self.mol, fullname, xyz=self.xyz())
+        else:
+            raise ValueError("Filetype {} not recognized. Try with mol2 or pdb".format(filetype))
+        return fullname
 
     def mutate(self, indpb):
         pass

@@ -127,7 +127,7 @@ class Search(GeneProvider):
 
     @property
     def origin(self):
-        return tuple(self.molecule_gene.mol.xyz[self.origin_atom])
+        return tuple(float(v) for v in self.molecule_gene.mol.xyz[self.origin_atom])
 
     @property
     def center(self):
@@ -137,7 +137,7 @@ class Search(GeneProvider):
             return tuple(float(v) for v in self._center)
         mol, serial = self._center if not isinstance(self._center, str) else self._center.split("/")
         gene = self.parent.find_molecule(mol)
-        return tuple(gene.mol.xyz[gene.find_atom(int(serial))])
+        return tuple(float(v) for v in gene.mol.xyz[gene.find_atom(int(serial))])
 
     def device_allele(self):
         """(12,) row-major 3x4 product ``T . R`` handed to ``gmm_express`` (search.py:206-214;

@@ -171,6 +171,40 @@ def read_mol2(path):
     return mol
 
 
+def write_mol2(mol, path, xyz=None, title="gaudi_b200"):
+    """Tripos mol2 of ``mol`` with coordinates ``xyz`` (default: the molecule's own): what the
+    reference gets from Chimera's ``writeMol2`` at gaudi/genes/molecule.py:256 as far as
+    ``read_mol2`` and any mol2 reader care — atom ids, names, coordinates, Sybyl types, residue
+    numbers and names, bonds.  Partial charges are written as 0 (the hot path never holds any)."""
+    xyz = mol.xyz if xyz is None else np.asarray(xyz, np.float64)
+    sybyl = mol.sybyl if getattr(mol, "sybyl", None) else [e.title() for e in mol.element]
+    bonds = getattr(mol, "bonds", None)
+    bonds = np.zeros((0, 2), np.int32) if bonds is None else np.asarray(bonds).reshape(-1, 2)
+    with open(path, "w") as fh:
+        fh.write("@<TRIPOS>MOLECULE\n%s\n%d %d 1\nSMALL\nNO_CHARGES\n\n@<TRIPOS>ATOM\n" % (title, mol.n_atoms, len(bonds)))
+        for i in range(mol.n_atoms):
+            fh.write("%7d %-8s %12.6f %12.6f %12.6f %-6s %5d %s%d 0.0000\n" % (
+                int(mol.serial[i]), mol.name[i], xyz[i, 0], xyz[i, 1], xyz[i, 2], sybyl[i],
+                int(mol.resseq[i]), mol.resname[i], int(mol.resseq[i])))
+        fh.write("@<TRIPOS>BOND\n")
+        for k, (a, b) in enumerate(bonds):
+            fh.write("%6d %6d %6d 1\n" % (k + 1, int(mol.serial[a]), int(mol.serial[b])))
+    return path
+
+
+def write_pdb(mol, path, xyz=None):
+    """Minimal PDB (ATOM/HETATM records) of ``mol`` with coordinates ``xyz``."""
+    xyz = mol.xyz if xyz is None else np.asarray(xyz, np.float64)
+    with open(path, "w") as fh:
+        for i in range(mol.n_atoms):
+            rec = "HETATM" if (getattr(mol, "hetero", None) is not None and mol.hetero[i]) else "ATOM  "
+            fh.write("%s%5d %-4s %3s %1s%4d    %8.3f%8.3f%8.3f  1.00  0.00          %2s\n" % (
+                rec, int(mol.serial[i]) % 100000, mol.name[i][:4], mol.resname[i][:3], (mol.chain[i] or " ")[:1],
+                int(mol.resseq[i]) % 10000, xyz[i, 0], xyz[i, 1], xyz[i, 2], mol.element[i].title()[:2]))
+        fh.write("END\n")
+    return path
+
+
 def perceive_bonds(mol, use_conect=True):
     """Distance-based connectivity (d <= r_a + r_b + 0.4), merged with CONECT records.
     A hydrogen keeps only its shortest bond."""

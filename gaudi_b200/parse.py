@@ -79,6 +79,8 @@ class Settings(Param):
             self[key] = Param(data[key])
         self["genes"] = [Param(g) for g in data["genes"]]
         self["objectives"] = [Param(o) for o in data["objectives"]]
+        if self._path and not os.path.isabs(self["output"]["path"]):    # parse.py:288 RelPathToInputFile
+            self["output"]["path"] = os.path.normpath(os.path.join(base, os.path.expanduser(self["output"]["path"])))
         for g in self["genes"]:          # relative paths resolve against the input file (parse.py:130-138)
             if "path" in g and not os.path.isabs(g["path"]):
                 g["path"] = os.path.normpath(os.path.join(base, g["path"]))

@@ -71,7 +71,7 @@ def configs4_job(n_res=12, seed=5, search_radius=3.0):
     library = {nm: rng.uniform(-180, 180, size=(int(rng.integers(3, 82)), 4)).tolist()
                for nm in sorted(set(prot.resname[a][:3].upper() for a in range(prot.n_atoms)))}
     cfg = parse.Settings({
-        "output": {"verbose": False},
+        "output": {"verbose": False, "check_every": 0},
         "genes": [{"name": "Protein", "module": "gaudi_b200.genes.molecule", "path": "5er1_protein.mol2", "mol": prot},
                   {"name": "Ligand", "module": "gaudi_b200.genes.molecule", "path": "5er1_ligand.mol2", "mol": lig},
                   {"name": "Rotamers", "module": "gaudi_b200.genes.rotamers",

@@ -38,7 +38,7 @@ def job(population=100, generations=10, rotamers=None):
         {"name": "Search", "module": "gaudi_b200.genes.search", "target": "Ligand/1", "radius": 3.0, "rotate": True},
     ]
     return parse.Settings({
-        "output": {"verbose": False, "precision": 3},
+        "output": {"verbose": False, "precision": 3, "check_every": 0},
         "ga": {"population": population, "generations": generations, "mu": 1.0, "lambda_": 1.0},
         "genes": genes,
         "objectives": [
@@ -227,3 +227,29 @@ objectives:
         got = ind.fitness.values
         assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash)
         assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro)
+
+
+def test_run_writes_the_elite(cuda, tmp_path):
+    """``algorithms.run`` = launch + dump_population (gaudi/cli/gaudi_run.py:137-178): the elite ends
+    up on disk as the reference's zip / mol2 / yaml artefacts, and the ligand coordinates in them are
+    the oracle's expression of the written alleles."""
+    import zipfile
+    import yaml
+    from gaudi_b200 import algorithms, molio
+    cfg = job(40, 3)
+    cfg.output.path = str(tmp_path / "out")
+    cfg.output.name = "dock"
+    cfg.output.check_every = 2
+    pop, log, elite, index = algorithms.run(cfg, seed=9)
+    listing = yaml.safe_load(open(index))
+    assert len(listing["GAUDI.results"]) == len(elite) >= 1
+    assert (tmp_path / "out" / "check2" / "dock.gaudi-output").exists()          # the check_every dump
+    batch = cfg._environment.batch
+    for k, ind in enumerate(elite):
+        zname = tmp_path / "out" / ("dock_%03d.zip" % k)
+        assert listing["GAUDI.results"][zname.name] == list(ind.fitness.values)
+        with zipfile.ZipFile(str(zname)) as z:
+            z.extract("Ligand_%03d_Ligand.mol2" % k, str(tmp_path))
+        back = molio.read_mol2(str(tmp_path / ("Ligand_%03d_Ligand.mol2" % k)))
+        _, xyz = oracle_scores(batch, ind)
+        assert np.abs(back.xyz - xyz[batch.lig_slice]).max() < 1e-4

@@ -314,3 +314,56 @@ objectives:
     bad.write_text("genes:\n  - {name: M, module: gaudi.genes.mutamers, residues: [Protein/1]}\n")
     with pytest.raises(NotImplementedError, match="gaudi.genes.mutamers"):
         parse.Settings(str(bad))
+
+
+def test_results_writer_round_trip(tmp_path):
+    """Individual.write / dump_population (gaudi/base.py:231-266, gaudi/algorithms.py:205-223): one
+    zip per individual holding a mol2 per Molecule gene with the EXPRESSED coordinates, the other
+    genes' alleles as text and a yaml with the scores, plus the .gaudi-output index; read back, the
+    files give the alleles, the scores and the coordinates that went in."""
+    import ast
+    import zipfile
+    import yaml
+    import golden_util as G
+    from gaudi_b200 import algorithms, base, molio, parse
+    random.seed(4)
+    cfg = parse.Settings({
+        "output": {"path": str(tmp_path / "results"), "name": "job", "verbose": False, "check_every": 0},
+        "genes": [{"name": "Protein", "module": "gaudi_b200.genes.molecule", "path": "p.mol2", "mol": G.load("5er1_protein_mol2")},
+                  {"name": "Ligand", "module": "gaudi_b200.genes.molecule", "path": "l.mol2", "mol": G.load("5er1_ligand_mol2")},
+                  {"name": "Torsion", "module": "gaudi_b200.genes.torsion", "target": "Ligand", "flexibility": 360},
+                  {"name": "Search", "module": "gaudi_b200.genes.search", "target": "Ligand/1", "radius": 3.0}],
+        "objectives": [{"name": "Clashes", "module": "gaudi_b200.objectives.contacts", "which": "clashes",
+                        "probes": ["Ligand"], "radius": 5.0, "weight": -1.0},
+                       {"name": "Contacts", "module": "gaudi_b200.objectives.contacts", "which": "hydrophobic",
+                        "probes": ["Ligand"], "radius": 5.0, "weight": -1.0}]})
+    os.makedirs(cfg.output.path)
+    rng = np.random.default_rng(2)
+    pop = []
+    for k in range(3):
+        ind = base.MolecularIndividual(cfg)
+        ind.fitness.values = (round(10.0 * k + 0.125, 3), round(-3.5 - k, 3))
+        for gene in ind._molecules.values():        # what the batched evaluate leaves behind (post_express)
+            gene._expressed_coordinates = gene.mol.xyz + rng.normal(size=gene.mol.xyz.shape)
+        pop.append(ind)
+    index = algorithms.dump_population(pop, cfg, subdir="check7")
+    listing = yaml.safe_load(open(index))
+    assert listing["GAUDI.objectives"] == ["Clashes (gaudi_b200.objectives.contacts)", "Contacts (gaudi_b200.objectives.contacts)"]
+    assert sorted(listing["GAUDI.results"]) == ["job_000.zip", "job_001.zip", "job_002.zip"]
+    for k, ind in enumerate(pop):
+        assert listing["GAUDI.results"]["job_%03d.zip" % k] == list(ind.fitness.values)
+        with zipfile.ZipFile(os.path.join(cfg.output.path, "check7", "job_%03d.zip" % k)) as z:
+            names = sorted(z.namelist())
+            assert names == sorted(["Protein_%03d_Protein.mol2" % k, "Ligand_%03d_Ligand.mol2" % k,
+                                    "Torsion_%03d_Torsion.txt" % k, "Search_%03d_Search.txt" % k, "Search_%03d.gaudi" % k])
+            meta = yaml.safe_load(z.read("Search_%03d.gaudi" % k))
+            assert meta["score"] == list(ind.fitness.values) and meta["Ligand"] == "Ligand_%03d_Ligand.mol2" % k
+            assert ast.literal_eval(z.read("Torsion_%03d_Torsion.txt" % k).decode()) == list(ind.genes["Torsion"].allele)
+            got = ast.literal_eval(z.read("Search_%03d_Search.txt" % k).decode())
+            assert np.allclose(np.array(got[0]), np.array(ind.genes["Search"].allele[0]))
+            z.extract("Ligand_%03d_Ligand.mol2" % k, str(tmp_path))
+        back = molio.read_mol2(str(tmp_path / ("Ligand_%03d_Ligand.mol2" % k)))
+        lig = ind.find_molecule("Ligand")
+        assert np.abs(back.xyz - lig._expressed_coordinates).max() < 1e-6
+        assert np.array_equal(back.bonds, lig.mol.bonds) and back.sybyl == lig.mol.sybyl
+    assert not [f for f in os.listdir(os.path.join(cfg.output.path, "check7")) if f.endswith((".mol2", ".txt"))]
