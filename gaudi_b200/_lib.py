@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgaudimm_b200.so")
 
 GMM_OK, GMM_EINVAL, GMM_ECUDA, GMM_ESTATE, GMM_ELIMIT = 0, -1, -2, -3, -4
-OPT_ONLY_INTERNAL, OPT_NO_CULL, OPT_TILED, OPT_SEQUENTIAL_EXPRESS, OPT_RMSD_SIMT = 1, 2, 4, 8, 16
+OPT_ONLY_INTERNAL, OPT_NO_CULL, OPT_TILED, OPT_SEQUENTIAL_EXPRESS, OPT_RMSD_SIMT, OPT_RMSD_HMMA = 1, 2, 4, 8, 16, 32
 MAX_MOBILE_ATOMS, MAX_TORSIONS = 1024, 1024
 
 _vp, _i, _d = C.c_void_p, C.c_int, C.c_double

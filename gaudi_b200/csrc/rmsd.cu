@@ -14,11 +14,10 @@
 #include <cuda_fp16.h>
 #include <mma.h>
 
-#include "common.cuh"
+#include "rmsd_common.cuh"
 
 namespace gmm {
 
-constexpr int kRT = 128;         // tile edge (pairs)
 constexpr int kRS = kRT + 4;     // padded row stride (floats), keeps 16-byte alignment
 
 struct RmsdArgs {
@@ -169,18 +168,6 @@ rmsd_tile_kernel(const RmsdArgs a) {
 constexpr int kMK = 64;          // coordinates per staged chunk (4 k-steps of the m16n16k16 MMA)
 constexpr int kMS = kMK + 8;     // padded row stride of a staged chunk (halves)
 constexpr int kMD = kRT + 4;     // padded row stride of the dot-product tile (floats)
-constexpr int kMQ = 4096;        // queue of pairs to re-decide, per tile
-
-struct RmsdMmaArgs {
-    int N, K, Kp, row0, row1, words;
-    const float* xyz;            // original coordinates [N][K]
-    const __half* xc;            // re-centred, rounded to half, zero-padded [N][Kp]
-    const int* overflow;         // != 0: some re-centred coordinate does not fit half -> nothing is pre-decided
-    const float* norm;           // [N] |xc|^2
-    uint32_t* bits;
-    float thr2, inv_a, cut;      // cut = thr2 * A: the threshold on the un-normalised sum
-    int sym, R0, R1;
-};
 
 __global__ void rmsd_colsum_kernel(int N, int K, const float* __restrict__ xyz, float* __restrict__ colsum) {
     // grid.x blocks of 256 conformers each add their column sums into colsum[K] (pre-zeroed)
@@ -215,27 +202,6 @@ __global__ void rmsd_center_kernel(int N, int K, int Kp, const float* __restrict
 __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
-}
-
-// sum_k (x_k - y_k)^2 accumulated in k order with one FFMA per term: the very sequence of roundings
-// the FP32 kernel's accumulators go through, so the decision taken from it is that kernel's.
-__device__ __forceinline__ float exact_sum(const float* __restrict__ x, const float* __restrict__ y, int K, bool vec) {
-    float s = 0.f;
-    if (vec) {      // K a multiple of 4 and both rows 16-byte aligned: same order, a quarter of the loads
-        const float4* x4 = reinterpret_cast<const float4*>(x);
-        const float4* y4 = reinterpret_cast<const float4*>(y);
-#pragma unroll 5
-        for (int k = 0; k < K / 4; ++k) {
-            const float4 p = x4[k], q = y4[k];
-            float d = p.x - q.x; s = fmaf(d, d, s);
-            d = p.y - q.y; s = fmaf(d, d, s);
-            d = p.z - q.z; s = fmaf(d, d, s);
-            d = p.w - q.w; s = fmaf(d, d, s);
-        }
-    } else {
-        for (int k = 0; k < K; ++k) { const float d = x[k] - y[k]; s = fmaf(d, d, s); }
-    }
-    return s;
 }
 
 __global__ void __launch_bounds__(256, 2)
@@ -447,6 +413,11 @@ static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0,
     a.thr2 = (float)(thr * thr); a.inv_a = 1.0f / (float)A; a.cut = a.thr2 * (float)A;
     a.sym = (row0 % kRT == 0) ? 1 : 0;
     a.R0 = row0 / kRT; a.R1 = (row1 + kRT - 1) / kRT;
+    if (!(c->prm.options & GMM_OPT_RMSD_HMMA)) {      // the tcgen05 / TMEM / TMA kernel (rmsd_tc.cu)
+        int handled = 0;
+        const int rc = launch_rmsd_tc(c, a, s, &handled);
+        if (rc != GMM_OK || handled) return rc;
+    }
     dim3 grid((N + kRT - 1) / kRT, (row1 - row0 + kRT - 1) / kRT);
     const size_t staging = (size_t)4 * kRT * kMS * sizeof(__half), dtile = (size_t)kRT * kMD * sizeof(float);
     const size_t smem = (staging > dtile ? staging : dtile) + (2 * kRT + kRT * 4 + kMQ + 4) * sizeof(float);

@@ -47,7 +47,8 @@ class Engine(object):
         opts = ((_lib.OPT_ONLY_INTERNAL if p.only_internal else 0) | (0 if p.cull else _lib.OPT_NO_CULL)
                 | (_lib.OPT_TILED if p.tiled else 0)
                 | (_lib.OPT_SEQUENTIAL_EXPRESS if getattr(p, 'sequential_express', False) else 0)
-                | (_lib.OPT_RMSD_SIMT if getattr(p, 'rmsd_simt', False) else 0))
+                | (_lib.OPT_RMSD_SIMT if getattr(p, 'rmsd_simt', False) else 0)
+                | (_lib.OPT_RMSD_HMMA if getattr(p, 'rmsd_hmma', False) else 0))
         _lib.check(self._L.gmm_set_params(h, p.radius, p.clash_threshold, p.hydrophobic_threshold,
                                           p.hbond_allowance, p.assumed_max_vdw, p.cutoff, p.weight,
                                           opts))

@@ -110,6 +110,7 @@ class ContactParams:
     tiled: bool = False     # B200 path only: two-kernel tiled Contacts path instead of the fused one
     sequential_express: bool = False   # B200 path only: bond rotations one after another (reference order)
     rmsd_simt: bool = False            # B200 path only: similarity bitmask by the FP32 direct-difference kernel
+    rmsd_hmma: bool = False            # B200 path only: pre-filter product by mma.sync instead of tcgen05 (cross-check)
 
 
 @dataclass

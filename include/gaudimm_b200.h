@@ -52,6 +52,9 @@ extern "C" {
 #define GMM_OPT_TILED          4  /* use the two-kernel tiled Contacts path instead of the fused one */
 #define GMM_OPT_RMSD_SIMT      16  /* bitmask-only gmm_rmsd_matrix calls: use the FP32 direct-difference kernel
                                     * instead of the tensor-core pre-filter + exact re-decision (same bits) */
+#define GMM_OPT_RMSD_HMMA      32  /* bitmask-only gmm_rmsd_matrix calls: run the product of the pre-filter with
+                                    * mma.sync (the first tensor-core version) instead of tcgen05 + TMEM + TMA;
+                                    * same bits, kept as a cross-check */
 #define GMM_OPT_SEQUENTIAL_EXPRESS 8 /* apply the bond rotations one after another on the current coordinates
                                      * (the reference's own order of operations) even when the model allows the
                                      * faster kinematic-tree form; results agree to fp64 rounding */
