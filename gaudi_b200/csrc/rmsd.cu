@@ -170,18 +170,27 @@ constexpr int kMS = kMK + 8;     // padded row stride of a staged chunk (halves)
 constexpr int kMD = kRT + 4;     // padded row stride of the dot-product tile (floats)
 
 __global__ void rmsd_colsum_kernel(int N, int K, const float* __restrict__ xyz, float* __restrict__ colsum) {
-    // grid.x blocks of 256 conformers each add their column sums into colsum[K] (pre-zeroed)
-    const int n0 = blockIdx.x * 256;
+    // grid.x blocks of 32 conformers each add their column sums into colsum[K] (pre-zeroed)
+    const int n0 = blockIdx.x * 32;
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
         float s = 0.f;
-        const int n1 = min(N, n0 + 256);
+        const int n1 = min(N, n0 + 32);
+#pragma unroll 8
         for (int n = n0; n < n1; ++n) s += xyz[(size_t)n * K + k];
         atomicAdd(&colsum[k], s);
     }
 }
 
+// Re-centred fp16 copies of the conformers and their squared norms.  ext = 0: one array, zero
+// padded to Kp columns (mma.sync kernel).  ext = 1 (tcgen05 kernel): two arrays whose first K
+// columns are the same and whose next six fold the norms and the threshold into the product itself:
+//     row role     [x, n_hi, n_lo, n_ll, 1, 1, 1]      n = -|x|^2 / 2 split over three halves
+//     column role  [x, 1, 1, 1, m_hi, m_lo, m_ll]      m = -|x|^2 / 2 + cut / 2
+// so that  a' . b' = a . b - (|a|^2 + |b|^2 - cut) / 2 = -(approximate sum - cut) / 2  comes straight
+// out of the tensor cores and the epilogue compares it with the error bound alone.
 __global__ void rmsd_center_kernel(int N, int K, int Kp, const float* __restrict__ xyz, const float* __restrict__ colsum,
-                                   __half* __restrict__ xc, float* __restrict__ norm, int* __restrict__ overflow) {
+                                   __half* __restrict__ xc, __half* __restrict__ xcb, float half_cut, int ext,
+                                   float* __restrict__ norm, int* __restrict__ overflow) {
     const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (n >= N) return;
     const float inv = 1.0f / (float)N;
@@ -191,11 +200,29 @@ __global__ void rmsd_center_kernel(int N, int K, int Kp, const float* __restrict
         float v = 0.f;
         if (k < K) v = xyz[(size_t)n * K + k] - colsum[k] * inv;
         big = big || !(fabsf(v) < 6.0e4f);
-        xc[(size_t)n * Kp + k] = __float2half_rn(v);
+        const __half h = __float2half_rn(v);
+        xc[(size_t)n * Kp + k] = h;
+        if (ext) xcb[(size_t)n * Kp + k] = h;
         s = fmaf(v, v, s);                       // the norm is of the unrounded value
     }
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (lane == 0) norm[n] = s;
+    if (ext) {
+        __syncwarp();
+        big = big || !(s < 1.0e5f);              // -|x|^2 / 2 has to fit a half
+        if (lane < 6) {
+            const float val = (lane < 3) ? -0.5f * s : -0.5f * s + half_cut;     // lanes 0-2: n, lanes 3-5: m
+            const __half hi = __float2half_rn(val);
+            const __half lo = __float2half_rn(val - __half2float(hi));
+            const __half ll = __float2half_rn(val - __half2float(hi) - __half2float(lo));
+            const int piece = lane % 3;
+            const __half pc = piece == 0 ? hi : piece == 1 ? lo : ll;
+            const __half one = __float2half_rn(1.0f);
+            // row role: pieces of n at K .. K+2, ones at K+3 .. K+5; column role: the other way round
+            xc[(size_t)n * Kp + K + lane] = lane < 3 ? pc : one;
+            xcb[(size_t)n * Kp + K + lane] = lane < 3 ? one : pc;
+        }
+    }
     if (big) atomicExch(overflow, 1);
 }
 
@@ -381,10 +408,14 @@ rmsd_bits_mma_kernel(const RmsdMmaArgs a) {
 
 // Workspace of the bitmask path: re-centred fp16 conformers, their squared norms, column sums, flag.
 // Grown on demand (device-wide synchronisation + cudaMalloc); gmm_reserve_rmsd() pre-sizes it.
+// Kt: columns of the staged copies = 3 A coordinates + the six folded columns of the tcgen05 path,
+// rounded up to a multiple of 16
+static int staged_columns(int A) { return (3 * A + 6 + 15) & ~15; }
+
 int reserve_rmsd_workspace(gmm_ctx* c, int N, int A) {
-    const int K = 3 * A, Kp = (K + 15) & ~15;
-    const size_t xc_bytes = ((size_t)N * Kp * sizeof(__half) + 255) / 256 * 256;
-    const size_t need = xc_bytes + ((size_t)N + Kp + 64) * sizeof(float);
+    const int Kt = staged_columns(A);
+    const size_t xc_bytes = ((size_t)N * Kt * sizeof(__half) + 255) / 256 * 256;
+    const size_t need = 2 * xc_bytes + ((size_t)N + Kt + 64) * sizeof(float);
     if (need > c->rmsd_ws_bytes) {
         if (c->d_rmsd_ws) { GMM_CUDA(cudaDeviceSynchronize()); cudaFree(c->d_rmsd_ws); c->d_rmsd_ws = nullptr; c->rmsd_ws_bytes = 0; }
         GMM_CUDA(cudaMalloc(&c->d_rmsd_ws, need));
@@ -395,28 +426,37 @@ int reserve_rmsd_workspace(gmm_ctx* c, int N, int A) {
 
 static int launch_rmsd_mma(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, uint32_t* out_bits,
                            double thr, cudaStream_t s) {
-    const int K = 3 * A, Kp = (K + 15) & ~15;
-    const size_t xc_bytes = ((size_t)N * Kp * sizeof(__half) + 255) / 256 * 256;
+    const bool tc = !(c->prm.options & GMM_OPT_RMSD_HMMA);
+    const int K = 3 * A, Kt = staged_columns(A), Kp = tc ? Kt : ((K + 15) & ~15);
+    const size_t xc_bytes = ((size_t)N * Kt * sizeof(__half) + 255) / 256 * 256;
     { const int rc = reserve_rmsd_workspace(c, N, A); if (rc) return rc; }
     __half* xc = static_cast<__half*>(c->d_rmsd_ws);
-    float* norm = reinterpret_cast<float*>(static_cast<unsigned char*>(c->d_rmsd_ws) + xc_bytes);
+    __half* xcb = reinterpret_cast<__half*>(static_cast<unsigned char*>(c->d_rmsd_ws) + xc_bytes);
+    float* norm = reinterpret_cast<float*>(static_cast<unsigned char*>(c->d_rmsd_ws) + 2 * xc_bytes);
     float* colsum = norm + N;
-    int* overflow = reinterpret_cast<int*>(colsum + Kp);
-    GMM_CUDA(cudaMemsetAsync(colsum, 0, sizeof(float) * (Kp + 1), s));       // column sums and the flag
-    rmsd_colsum_kernel<<<(N + 255) / 256, 192, 0, s>>>(N, K, xyz, colsum);
+    int* overflow = reinterpret_cast<int*>(colsum + Kt);
+    const float cut_f = (float)(thr * thr) * (float)A;
+    GMM_CUDA(cudaMemsetAsync(colsum, 0, sizeof(float) * (Kt + 1), s));       // column sums and the flag
+    rmsd_colsum_kernel<<<(N + 31) / 32, 192, 0, s>>>(N, K, xyz, colsum);
     GMM_LAUNCH_CHECK("rmsd_colsum_kernel");
-    rmsd_center_kernel<<<(int)(((size_t)N * 32 + 255) / 256), 256, 0, s>>>(N, K, Kp, xyz, colsum, xc, norm, overflow);
+    rmsd_center_kernel<<<(int)(((size_t)N * 32 + 255) / 256), 256, 0, s>>>(N, K, Kp, xyz, colsum, xc, xcb, 0.5f * cut_f,
+                                                                           tc ? 1 : 0, norm, overflow);
     GMM_LAUNCH_CHECK("rmsd_center_kernel");
     RmsdMmaArgs a;
     a.N = N; a.K = K; a.Kp = Kp; a.row0 = row0; a.row1 = row1; a.words = (N + 31) / 32;
-    a.xyz = xyz; a.xc = xc; a.norm = norm; a.overflow = overflow; a.bits = out_bits;
+    a.xyz = xyz; a.xc = xc; a.xcb = xcb; a.norm = norm; a.overflow = overflow; a.bits = out_bits;
     a.thr2 = (float)(thr * thr); a.inv_a = 1.0f / (float)A; a.cut = a.thr2 * (float)A;
     a.sym = (row0 % kRT == 0) ? 1 : 0;
     a.R0 = row0 / kRT; a.R1 = (row1 + kRT - 1) / kRT;
-    if (!(c->prm.options & GMM_OPT_RMSD_HMMA)) {      // the tcgen05 / TMEM / TMA kernel (rmsd_tc.cu)
+    if (tc) {                                          // the tcgen05 / TMEM / TMA kernel (rmsd_tc.cu)
         int handled = 0;
         const int rc = launch_rmsd_tc(c, a, s, &handled);
         if (rc != GMM_OK || handled) return rc;
+        // no tensor map on this driver: stage the plain copy and run the mma.sync kernel
+        a.Kp = (K + 15) & ~15;
+        rmsd_center_kernel<<<(int)(((size_t)N * 32 + 255) / 256), 256, 0, s>>>(N, K, a.Kp, xyz, colsum, xc, xcb, 0.f, 0, norm,
+                                                                               overflow);
+        GMM_LAUNCH_CHECK("rmsd_center_kernel");
     }
     dim3 grid((N + kRT - 1) / kRT, (row1 - row0 + kRT - 1) / kRT);
     const size_t staging = (size_t)4 * kRT * kMS * sizeof(__half), dtile = (size_t)kRT * kMD * sizeof(float);

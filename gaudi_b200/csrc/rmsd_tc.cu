@@ -18,8 +18,8 @@
 //              shared memory, no ballots; undecided pairs go to a queue in the (now free) operand
 //              buffers and are re-decided by all threads with the exact sum.
 //
-// One 128 x 128 tile per CTA, 128 threads, ~100 KB of shared memory: two CTAs per SM overlap one
-// tile's loads and MMA with the other's epilogue.
+// One 128 x 128 tile per CTA, 128 threads, 36 KB of shared memory: four CTAs per SM overlap each
+// other's phases.
 #include <cuda.h>
 
 #include "rmsd_common.cuh"
@@ -27,13 +27,17 @@
 namespace gmm {
 
 constexpr int kTcBlockK = 64;                         // halves per staged block: 128 bytes, one swizzle atom
-constexpr int kTcStages = 3;                          // 3 x (16 KB + 16 KB): all of K for 60 atoms (K = 192)
+constexpr int kTcStages = 1;                          // one 16 KB + 16 KB block in flight per CTA: what bounds the kernel is
+                                                      // latency, not bandwidth, and 36 KB of shared memory per CTA lets
+                                                      // four CTAs (4 x 128 TMEM columns = all 512) share an SM and
+                                                      // overlap each other's load / MMA / epilogue / re-decision phases
+                                                      // (measured: 3 stages, 2 CTAs per SM 0.267 ms; 2: 0.214; 1: 0.173)
 constexpr int kTcStageBytes = 2 * kRT * kTcBlockK * 2;
 constexpr int kTcQueue = 4096;                        // undecided pairs per tile (aliases the operand buffers)
 constexpr int kTcTmemCols = 128;
 
 struct TcSmem {                                       // behind the 1024-byte aligned operand ring
-    float2 col[kRT];                                  // hi_c, lo_c per tile column
+    float ecw[4];                                     // per 32-column word: the largest column part of the error bound
     uint32_t words[kRT * 4];                          // the tile's bits, [row][4 words]
     unsigned long long full[kTcStages], empty[kTcStages], done;
     uint32_t tmem_base;
@@ -110,7 +114,8 @@ __device__ __forceinline__ void tmem_load_32(uint32_t taddr, float (&v)[32]) {
 }
 
 __global__ void __launch_bounds__(128)
-rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const RmsdMmaArgs a) {
+rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_b,
+                    const RmsdMmaArgs a) {
     extern __shared__ unsigned char tc_smem_raw[];
     // the operand ring needs 1024-byte alignment (swizzle atom = 8 rows x 128 bytes)
     unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -135,18 +140,18 @@ rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const RmsdMmaArgs 
                      ::"r"(smem_u32(&sm->tmem_base)), "n"(kTcTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // per-column thresholds (see rmsd.cu): with e = 1.2e-3 (|a|^2 + |b|^2) + c0 the bound on the error
-    // of |a|^2 + |b|^2 - 2 D, a pair is certainly similar when D > hi_r + hi_c and certainly not
-    // when D < lo_r + lo_c; columns past N can never pass either test
+    // The accumulator holds u = a . b - (|a|^2 + |b|^2 - cut) / 2 = -(approximate sum - cut) / 2
+    // (norms and threshold ride in six extra operand columns, rmsd_center_kernel).  The error of the
+    // approximate sum is bounded by 1.2e-3 (|a|^2 + |b|^2) + c0 (fp16 rounding of the inputs,
+    // Cauchy-Schwarz, slack for the accumulation; rmsd.cu), so with e = half of that a pair is
+    // certainly similar when u > e, certainly not when u < -e.  e = (row part) + (column part); the
+    // column part is taken as the largest of the word's 32 columns, which only widens the band.
     const float c0 = 1e-4f * a.cut + 1e-4f;
     {
         const int col = c_base + tid;
-        float2 t = make_float2(3.0e38f, 3.0e38f);
-        if (col < a.N) {
-            const float nc = a.norm[col];
-            t = make_float2(0.5f * (1.0012f * nc - a.cut + c0), 0.5f * (0.9988f * nc - a.cut - c0));
-        }
-        sm->col[tid] = t;
+        const float nc = col < a.N ? a.norm[col] : 0.f;
+        const unsigned mx = __reduce_max_sync(0xffffffffu, __float_as_uint(nc));      // norms are >= 0
+        if (lane == 0) sm->ecw[warp] = 0.0006f * __uint_as_float(mx);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -161,7 +166,7 @@ rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const RmsdMmaArgs 
             mbar_expect_tx(&sm->full[s], kTcStageBytes);
             unsigned char* dst = ring + (size_t)s * kTcStageBytes;
             tma_load_2d(dst, &tmap, kb * kTcBlockK, r_base, &sm->full[s]);
-            tma_load_2d(dst + kTcStageBytes / 2, &tmap, kb * kTcBlockK, c_base, &sm->full[s]);
+            tma_load_2d(dst + kTcStageBytes / 2, &tmap_b, kb * kTcBlockK, c_base, &sm->full[s]);
         }
     } else if (tid == 32) {
         // ---- MMA issuer ----
@@ -182,8 +187,7 @@ rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const RmsdMmaArgs 
     // ---- epilogue: thread t = accumulator row t ----
     const int row = r_base + tid;
     const bool row_ok = row < a.row1;
-    const float nr = row_ok ? a.norm[row] : 0.f;
-    const float hi_r = 0.5f * 1.0012f * nr, lo_r = 0.5f * 0.9988f * nr;
+    const float er = 0.0006f * (row_ok ? a.norm[row] : 0.f) + 0.5f * c0;
     const bool nothing_decided = *a.overflow != 0;
     const bool vec = (a.K % 4 == 0) && (reinterpret_cast<uintptr_t>(a.xyz) % 16 == 0);
     mbar_wait(&sm->done, 0);
@@ -193,18 +197,15 @@ rmsd_bits_tc_kernel(const __grid_constant__ CUtensorMap tmap, const RmsdMmaArgs 
     for (int q = 0; q < 4; ++q) {
         float v[32];
         tmem_load_32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(q * 32), v);
+        const float e = er + sm->ecw[q];
         uint32_t yes = 0, maybe = 0;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const float2 t = sm->col[q * 32 + j];
-            const bool y = v[j] > hi_r + t.x;
-            const bool n = v[j] < lo_r + t.y;
-            yes |= (uint32_t)y << j;
-            maybe |= (uint32_t)(!y && !n) << j;
+            yes |= (uint32_t)(v[j] > e) << j;
+            maybe |= (uint32_t)(fabsf(v[j]) <= e) << j;
         }
         if (nothing_decided) { yes = 0; maybe = 0xffffffffu; }
-        // columns past N: their thresholds are +huge, so "not similar" was certain (maybe = 0) unless
-        // nothing is pre-decided; mask them here for that case
+        // columns past N were zero-filled by TMA (u = 0, inside the band): mask them
         const int left = a.N - (c_base + q * 32);
         const uint32_t valid = left >= 32 ? 0xffffffffu : (left <= 0 ? 0u : ((1u << left) - 1u));
         if (!row_ok) { yes = 0; maybe = 0; }
@@ -299,7 +300,7 @@ int launch_rmsd_tc(gmm_ctx* c, const RmsdMmaArgs& a, cudaStream_t s, int* handle
     if (encode == nullptr) return GMM_OK;
     // [N rows][Kp halves] row-major: dimension 0 = K (contiguous).  The map covers the workspace of
     // THIS context's device and nothing else.
-    CUtensorMap tmap;
+    CUtensorMap tmap, tmap_b;
     const cuuint64_t dims[2] = {(cuuint64_t)a.Kp, (cuuint64_t)a.N};
     const cuuint64_t strides[1] = {(cuuint64_t)a.Kp * sizeof(__half)};
     const cuuint32_t box[2] = {(cuuint32_t)kTcBlockK, (cuuint32_t)kRT};
@@ -308,10 +309,14 @@ int launch_rmsd_tc(gmm_ctx* c, const RmsdMmaArgs& a, cudaStream_t s, int* handle
                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return GMM_OK;
+    const CUresult rb = encode(&tmap_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(a.xcb), dims, strides, box,
+                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rb != CUDA_SUCCESS) return GMM_OK;
     const size_t smem = 1024 + (size_t)kTcStages * kTcStageBytes + sizeof(TcSmem);
     { const int rc = allow_dynamic_smem((const void*)rmsd_bits_tc_kernel, c->device, smem); if (rc) return rc; }
     dim3 grid((a.N + kRT - 1) / kRT, (a.row1 - a.row0 + kRT - 1) / kRT);
-    rmsd_bits_tc_kernel<<<grid, 128, smem, s>>>(tmap, a);
+    rmsd_bits_tc_kernel<<<grid, 128, smem, s>>>(tmap, tmap_b, a);
     GMM_LAUNCH_CHECK("rmsd_bits_tc_kernel");
     *handled = 1;
     return GMM_OK;
