@@ -495,9 +495,10 @@ def bench_rmsd(ctx, state, cpu=False):
     mine = torch.as_tensor(conf[b[ctx.rank]:b[ctx.rank + 1]]).to(ctx.dev)
     allc = torch.as_tensor(conf).to(ctx.dev)
     res = {}
+    sim = parallel.ShardedSimilarity(eng, counts, RMSD_A, threshold=RMSD_THR)
 
     def step():
-        res["lists"] = parallel.sharded_similar_lists(eng, mine, counts, threshold=RMSD_THR)
+        res["lists"] = sim.step(mine)
 
     l0 = launch_count()
     ms = ctx.time_steps(step, 10, warmup=3)
@@ -526,8 +527,9 @@ def bench_rmsd(ctx, state, cpu=False):
         out = {"metric": "RMSD pairs/s", "value": n_pairs / (step_ms * 1e-3), "unit": "unique pairs/s",
                "n_gpus": ctx.world, "ms_per_step": step_ms, "scaling": "strong",
                "config": {"workload": RMSD_TEXT,
-                          "step": "all-gather of conformers (NCCL) + row-block bitmask + partner-list compaction + gather of "
-                                  "the lists" if ctx.world > 1 else "bitmask + partner-list compaction",
+                          "step": ("all-gather of conformers (NCCL) + row-block bitmask + partner-list compaction + all-gather "
+                                   "of the packed lists + copy to the host (parallel.ShardedSimilarity)") if ctx.world > 1
+                                  else "bitmask + partner-list compaction + copy of the lists to the host",
                           "l2": "192 MiB buffer written between timed iterations"},
                "partner_entries": int(idx.shape[0]),
                "partner_list_bytes": int(idx.shape[0] * 4 + ptr.shape[0] * 8),

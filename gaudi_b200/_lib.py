@@ -44,7 +44,7 @@ SIGNATURES = {
     "gmm_set_geometry": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_geometry": (_i, [_vp, _i, _vp, _vp, _vp]),
     "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),
-    "gmm_similar_lists": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "gmm_similar_lists": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_longlong, _vp]),
     "gmm_niching_host": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gmm_fronts2_host": (_i, [_i, _vp, _vp]),
     "gmm_nondominated_fronts": (_i, [_vp, _i, _i, _vp, _vp, _vp]),

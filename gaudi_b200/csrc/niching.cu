@@ -29,7 +29,7 @@ __global__ void sim_count_kernel(int rows, int row0, int words, const uint32_t* 
 
 // one warp per row: partner indices in ascending order at idx[ptr[r] ...]
 __global__ void sim_fill_kernel(int rows, int row0, int words, const uint32_t* __restrict__ bits,
-                                const int64_t* __restrict__ ptr, int32_t* __restrict__ idx) {
+                                const int64_t* __restrict__ ptr, int32_t* __restrict__ idx, int64_t cap) {
     const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (r >= rows) return;
     const uint32_t* row = bits + (size_t)r * words;
@@ -47,7 +47,8 @@ __global__ void sim_fill_kernel(int rows, int row0, int words, const uint32_t* _
         }
         int64_t at = base + incl - c;
         while (v) {
-            idx[at++] = (w << 5) + (__ffs(v) - 1);
+            if (at < cap) idx[at] = (w << 5) + (__ffs(v) - 1);     // entries past the caller's capacity are dropped
+            ++at;
             v &= v - 1;
         }
         base += __shfl_sync(0xffffffffu, incl, 31);
@@ -57,7 +58,7 @@ __global__ void sim_fill_kernel(int rows, int row0, int words, const uint32_t* _
 }  // namespace gmm
 
 extern "C" int gmm_similar_lists(gmm_ctx* c, int N, int row0, int row1, const uint32_t* bits_d, int32_t* counts_d,
-                                 const int64_t* ptr_d, int32_t* idx_d, void* stream) {
+                                 const int64_t* ptr_d, int32_t* idx_d, long long idx_capacity, void* stream) {
     if (c == nullptr) { gmm::set_error("gmm_similar_lists: ctx is NULL"); return GMM_EINVAL; }
     if (N < 0 || row0 < 0 || row0 > row1 || row1 > N) {
         gmm::set_error("gmm_similar_lists: rows [%d,%d) outside [0,%d]", row0, row1, N);
@@ -78,7 +79,8 @@ extern "C" int gmm_similar_lists(gmm_ctx* c, int N, int row0, int row1, const ui
         GMM_LAUNCH_CHECK("sim_count_kernel");
     }
     if (ptr_d && idx_d) {
-        gmm::sim_fill_kernel<<<blocks, threads, 0, s>>>(rows, row0, words, bits_d, ptr_d, idx_d);
+        gmm::sim_fill_kernel<<<blocks, threads, 0, s>>>(rows, row0, words, bits_d, ptr_d, idx_d,
+                                                        idx_capacity > 0 ? (int64_t)idx_capacity : INT64_MAX);
         GMM_LAUNCH_CHECK("sim_fill_kernel");
     }
     return GMM_OK;

@@ -224,13 +224,13 @@ class Engine(object):
         rows = int(bits.shape[0])
         counts = torch.empty(rows, dtype=torch.int32, device=self.torch_device)
         _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
-                                             _dev_ptr(counts), None, None, self._stream()))
+                                             _dev_ptr(counts), None, None, 0, self._stream()))
         ptr = torch.zeros(rows + 1, dtype=torch.int64, device=self.torch_device)
         torch.cumsum(counts, 0, out=ptr[1:])
         total = int(ptr[-1].item())
         idx = torch.empty(max(total, 1), dtype=torch.int32, device=self.torch_device)
         _lib.check(self._L.gmm_similar_lists(self._h, int(n), int(row0), int(row0) + rows, _dev_ptr(bits),
-                                             None, _dev_ptr(ptr), _dev_ptr(idx), self._stream()))
+                                             None, _dev_ptr(ptr), _dev_ptr(idx), total, self._stream()))
         if not to_host:
             return ptr, idx[:total]
         return ptr.cpu().numpy(), idx[:total].cpu().numpy()

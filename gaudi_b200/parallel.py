@@ -150,6 +150,87 @@ def sharded_similar_lists(engine, coords, counts, threshold=2.5, group=None):
     return full_ptr, full_idx
 
 
+class ShardedSimilarity(object):
+    """``sharded_similar_lists`` for a generational loop: every buffer is allocated once, a step is
+    two collectives (conformers in, packed partner lists out), nine kernel launches and ONE
+    host synchronisation, and the partner lists arrive as HOST arrays on every rank (the greedy
+    niching pass that consumes them, gaudi/algorithms.py:139-155, runs on the host).
+
+    ``counts[r]`` conformers of ``atoms`` atoms live on rank r.  ``cap``: room for partner entries per
+    rank (default 8 per row: the whole packed buffer crosses PCIe every step, so it is kept small); a
+    step that needs more doubles it, runs again, and the larger buffer stays."""
+
+    def __init__(self, engine, counts, atoms, threshold=2.5, group=None, cap=None):
+        import numpy as np
+        self.engine, self.group, self.threshold = engine, group, float(threshold)
+        self.world, self.rank = _world(group)
+        self.counts = [int(c) for c in counts]
+        self.n, self.m, self.atoms = sum(self.counts), max(self.counts), int(atoms)
+        self.row0 = sum(self.counts[:self.rank])
+        self.rows = self.counts[self.rank]
+        dev = engine.torch_device
+        self.even = min(self.counts) == self.m
+        self.allc = torch.empty((self.world * self.m, self.atoms, 3), dtype=torch.float32, device=dev)
+        self.pad = None if self.even else torch.zeros((self.m, self.atoms, 3), dtype=torch.float32, device=dev)
+        self.bits = torch.empty((self.rows, (self.n + 31) // 32), dtype=torch.int32, device=dev)
+        self.ptr = torch.zeros(self.rows + 1, dtype=torch.int64, device=dev)
+        self._np = np
+        self._alloc(int(cap) if cap else 8 * self.m)
+        engine.reserve_rmsd(self.n, self.atoms)
+
+    def _alloc(self, cap):
+        dev = self.engine.torch_device
+        self.cap = cap
+        self.packed = torch.zeros(self.m + cap, dtype=torch.int32, device=dev)      # [per-row counts | entries]
+        self.gathered = torch.empty(self.world * (self.m + cap), dtype=torch.int32, device=dev)
+        self.host = torch.empty(self.world * (self.m + cap), dtype=torch.int32).pin_memory()
+
+    def step(self, coords):
+        """``coords``: this rank's ``(counts[rank], atoms, 3)`` float32 device block.  Returns host
+        ``(ptr int64 (N + 1,), idx int32)`` for all N conformers."""
+        import ctypes as C
+        from . import _lib
+        eng, np = self.engine, self._np
+        L, h, stream = eng._L, eng._h, eng._stream()
+        if self.world > 1:
+            src = coords
+            if not self.even:
+                self.pad[:self.rows] = coords
+                src = self.pad
+            _all_gather_into(self.allc, src.contiguous(), self.group)
+            allc = self.allc
+            if not self.even:
+                allc = torch.cat([self.allc[r * self.m:r * self.m + self.counts[r]] for r in range(self.world)])
+        else:
+            allc = coords.contiguous()
+        p = lambda t: C.c_void_p(t.data_ptr())
+        _lib.check(L.gmm_rmsd_matrix(h, self.n, self.atoms, p(allc), self.row0, self.row0 + self.rows, None, p(self.bits),
+                                     self.threshold, stream))
+        counts_d = self.packed[:self.rows]
+        _lib.check(L.gmm_similar_lists(h, self.n, self.row0, self.row0 + self.rows, p(self.bits), p(counts_d), None, None, 0, stream))
+        torch.cumsum(counts_d, 0, out=self.ptr[1:])
+        # entries beyond the capacity are dropped by the bound the fill pass is given; the host sees
+        # the true totals in the counts and retries with more room
+        _lib.check(L.gmm_similar_lists(h, self.n, self.row0, self.row0 + self.rows, p(self.bits), None, p(self.ptr),
+                                       C.c_void_p(self.packed.data_ptr() + 4 * self.m), self.cap, stream))
+        if self.world > 1:
+            _all_gather_into(self.gathered, self.packed, self.group)
+            self.host.copy_(self.gathered, non_blocking=True)
+        else:
+            self.host.copy_(self.packed, non_blocking=True)
+        torch.cuda.current_stream(eng.torch_device).synchronize()
+        host = self.host.numpy().reshape(self.world, self.m + self.cap)
+        per_row = [host[r, :self.counts[r]] for r in range(self.world)]
+        totals = [int(c.sum()) for c in per_row]
+        if max(totals) > self.cap:
+            self._alloc(2 * max(totals))
+            return self.step(coords)
+        ptr = np.zeros(self.n + 1, np.int64)
+        np.cumsum(np.concatenate(per_row), out=ptr[1:])
+        idx = np.concatenate([host[r, self.m:self.m + totals[r]] for r in range(self.world)])
+        return ptr, idx
+
+
 # ---------------------------------------------------------------------------------------------
 # Fitness exchange through peer memory (gmm_exchange_*): the all-gather without a collective
 # ---------------------------------------------------------------------------------------------

@@ -238,9 +238,11 @@ int gmm_express_is_tree(gmm_ctx* ctx);
  * [row0,row1) of the N x N matrix, ceil(N/32) uint32 words per row.  Two passes:
  *   count pass  counts_d != NULL: counts_d[r] = set bits of row r, its own column excluded;
  *   fill pass   ptr_d + idx_d   : idx_d[ptr_d[r] ...] = partner columns of row r, ascending;
- * ptr_d is the exclusive prefix sum of the counts (int64, rows + 1 entries), made by the caller. */
+ * ptr_d is the exclusive prefix sum of the counts (int64, rows + 1 entries), made by the caller.
+ * idx_capacity > 0: idx_d holds that many entries and entries beyond it are dropped (a caller that
+ * sized idx_d before knowing the counts compares them with its capacity afterwards); <= 0: no bound. */
 int gmm_similar_lists(gmm_ctx* ctx, int N, int row0, int row1, const uint32_t* bits_d, int32_t* counts_d,
-                      const int64_t* ptr_d, int32_t* idx_d, void* stream);
+                      const int64_t* ptr_d, int32_t* idx_d, long long idx_capacity, void* stream);
 
 /* Non-dominated sorting for the selection step (gaudi/algorithms.py:160 -> DEAP selNSGA2 ->
  * sortNondominated).  w_sorted_d: [n, m] fp64 weighted fitness values (larger is better in every

@@ -80,6 +80,12 @@ def _exchange_worker(rank, world, port, out):
     ptr1, idx1 = eng.similar_lists(bits, 1500)
     results["lists"] = bool(np.array_equal(ptr.cpu().numpy(), ptr1) and np.array_equal(idx.cpu().numpy(), idx1)
                             and len(idx1) > 0)
+    # the same through the preallocated generational path (one host synchronisation per step), with a
+    # capacity too small for the first step so that the retry is exercised too
+    sim = parallel.ShardedSimilarity(eng, [b[r + 1] - b[r] for r in range(world)], 60, threshold=2.5, cap=16)
+    for _ in range(2):
+        ptr2, idx2 = sim.step(mine)
+        results["lists_prealloc"] = bool(np.array_equal(ptr2, ptr1) and np.array_equal(idx2, idx1)) and results.get("lists_prealloc", True)
     dist.barrier()
     # host-resident population: shared page-locked table, each rank uploads and downloads its rows
     hs = parallel.HostShardedEvaluator(eng, 6000, want_xyz=True)
