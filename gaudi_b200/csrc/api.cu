@@ -302,6 +302,41 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
     c->n_mm = (int)mm.size();
     c->h_mm_pairs = mm; c->h_mflags_slot = fl;
     if ((rc = upload(&c->d_mm_pairs, mm.data(), mm.size()))) return rc;
+    // Where each mobile atom can ever be: atoms the Search gene moves can be anywhere; an atom that only
+    // bond rotations move (a flexible side chain) stays within a ball around the pivot of its
+    // outermost rotation.  With nested moving sets the rotations about the template axes, innermost
+    // first, give |x_final - b_1| <= |x - b_K| + sum |b_k+1 - b_k| (b_k = the moving-side atom of the
+    // k-th rotation that turns x, outermost first; each rotation keeps the distance to its own
+    // pivot).  gmm_set_receptor drops intra-mobile pairs whose balls can never come within reach.
+    c->h_ball.assign((size_t)Mp, make_float4(0.f, 0.f, 0.f, 3.0e38f));
+    if (c->tree_ok || T == 0) {
+        std::vector<int> cnt(T, 0);
+        for (int t = 0; t < T; ++t)
+            for (int i = 0; i < M; ++i) cnt[t] += ((tors_mask_h[(size_t)t * W + (i >> 6)] >> (i & 63)) & 1ull) ? 1 : 0;
+        for (int i = 0; i < M; ++i) {
+            if (flags_h[i] & GMM_F_XFORM) continue;
+            std::vector<int> chain;
+            for (int t = 0; t < T; ++t)
+                if ((tors_mask_h[(size_t)t * W + (i >> 6)] >> (i & 63)) & 1ull) chain.push_back(t);
+            std::stable_sort(chain.begin(), chain.end(), [&](int a, int b) { return cnt[a] > cnt[b]; });
+            const double* x = xyz0_h + 3 * (size_t)i;
+            double ctr[3] = {x[0], x[1], x[2]}, reach = 0.0;
+            if (!chain.empty()) {
+                const double* b1 = xyz0_h + 3 * (size_t)tors_moving_h[chain[0]];
+                for (int d = 0; d < 3; ++d) ctr[d] = b1[d];
+                const double* prev = b1;
+                for (size_t k = 1; k < chain.size(); ++k) {
+                    const double* bk = xyz0_h + 3 * (size_t)tors_moving_h[chain[k]];
+                    reach += std::sqrt((bk[0] - prev[0]) * (bk[0] - prev[0]) + (bk[1] - prev[1]) * (bk[1] - prev[1]) +
+                                       (bk[2] - prev[2]) * (bk[2] - prev[2]));
+                    prev = bk;
+                }
+                reach += std::sqrt((x[0] - prev[0]) * (x[0] - prev[0]) + (x[1] - prev[1]) * (x[1] - prev[1]) +
+                                   (x[2] - prev[2]) * (x[2] - prev[2]));
+            }
+            c->h_ball[c->h_atom2slot[i]] = make_float4((float)ctr[0], (float)ctr[1], (float)ctr[2], (float)(reach * 1.0001 + 1e-3));
+        }
+    }
     c->has_mobile = true;
     return GMM_OK;
 }
@@ -502,13 +537,25 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     {   // squared pre-filter cutoff of every intra-mobile pair: constant per pair under these parameters
         float thr_min, thr_tight;
         prefilter_cutoffs(c, &thr_min, &thr_tight);
-        std::vector<float> c2(c->h_mm_pairs.size());
-        for (size_t e = 0; e < c2.size(); ++e) {
+        std::vector<float> c2;
+        std::vector<uint32_t> kept;
+        c2.reserve(c->h_mm_pairs.size()); kept.reserve(c->h_mm_pairs.size());
+        for (size_t e = 0; e < c->h_mm_pairs.size(); ++e) {
             const int sa = c->h_mm_pairs[e] & 0xffff, sb = c->h_mm_pairs[e] >> 16;
             const bool both = (c->h_mflags_slot[sa] & c->h_mflags_slot[sb] & GMM_F_HYDROPHOBIC) != 0;
             const float cc = c->h_mrad[sa] + c->h_mrad[sb] - (both ? thr_min : thr_tight);
-            c2[e] = cc * cc * 1.000004f + 1e-6f;
+            // two atoms that only bond rotations move and whose balls never come within the pair's
+            // cutoff can never be reported: not walked at all (side chains of different residues)
+            const float4 ba = c->h_ball[sa], bb = c->h_ball[sb];
+            if (ba.w < 1.0e30f && bb.w < 1.0e30f) {
+                const double dx = (double)ba.x - bb.x, dy = (double)ba.y - bb.y, dz = (double)ba.z - bb.z;
+                if (std::sqrt(dx * dx + dy * dy + dz * dz) - ba.w - bb.w > (double)cc + 0.01) continue;
+            }
+            kept.push_back(c->h_mm_pairs[e]);
+            c2.push_back(cc * cc * 1.000004f + 1e-6f);
         }
+        c->n_mm = (int)kept.size();
+        if ((rc = upload(&c->d_mm_pairs, kept.data(), kept.size()))) return rc;
         if ((rc = upload(&c->d_mm_c2, c2.data(), c2.size()))) return rc;
     }
     c->has_receptor = true;

@@ -182,6 +182,7 @@ struct gmm_ctx {
     bool all_seed = true;
     std::vector<int32_t> h_slot2atom, h_atom2slot;
     std::vector<float> h_mrad;
+    std::vector<float4> h_ball;       // [Mp] slot order: where the atom can ever be (template frame), w = radius, 3e38 = anywhere
     // rotamers
     int n_res = 0; int32_t* d_rot_ptr = nullptr; double* d_rot_delta = nullptr;
 

@@ -258,12 +258,13 @@ contacts_fused_kernel(const FusedArgs f) {
         bool in = s < a.n_seed;
         if (!in && s < a.M && !internal) {
             const float4 q = ligx[s];
-#pragma unroll 1
-            for (int k = 0; k < a.n_seed && !in; ++k)
-                in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
+            // static seeds first: a flexible side chain's atoms mostly sit within the radius of their own CB
 #pragma unroll 1
             for (int k = 0; k < a.n_sseed && !in; ++k)
                 in = dist2f(a.sseed[k].x, a.sseed[k].y, a.sseed[k].z, q.x, q.y, q.z) <= a.rad2;
+#pragma unroll 1
+            for (int k = 0; k < a.n_seed && !in; ++k)
+                in = dist2f(ligx[k].x, ligx[k].y, ligx[k].z, q.x, q.y, q.z) <= a.rad2;
         }
         const unsigned bits = __ballot_sync(0xffffffffu, in && s < a.M);
         if (lane == 0) zm[base >> 5] = bits;

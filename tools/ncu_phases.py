@@ -20,7 +20,7 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "gaudi_b200", "libgaudimm_b200.so")
 SRC = os.path.join(ROOT, "gaudi_b200", "csrc", "contacts_fused.cu")
-KERNEL = "_ZN3gmm21contacts_fused_kernelILi1ELb1ELb1"
+KERNEL = os.environ.get("GMM_PHASE_KERNEL", "_ZN3gmm21contacts_fused_kernelILi1ELb1ELb1")
 
 
 def line_table():
