@@ -55,13 +55,21 @@ rmsd_tile_kernel(const RmsdArgs a) {
     if (in_square && cbk < rb) return;                        // written by tile (cbk, rb)
     const bool mirror = in_square && cbk > rb;
 
-    // stage chunk `c` into buffer `buf`: flat element e -> (conformer r = e / RK, coordinate k = e % RK);
-    // consecutive threads read consecutive coordinates of a conformer (coalesced), and scatter
-    // them transposed; out-of-range elements are zero-filled with plain stores.
+    // stage chunk `c` into buffer `buf`, transposed (k-major).  A warp moves 8 conformers x 4 consecutive
+    // coordinates per step: lane -> (k = 4 kg + (lane & 3), r = base + (lane >> 2 & 3) + 16 (lane >> 4)).
+    // With the row stride of 132 floats the shared-memory bank of element (k, r) is (4 k + r) mod 32,
+    // which this mapping makes distinct for the 32 lanes (the flat mapping e -> (e / RK, e % RK) put
+    // consecutive lanes 4 banks apart: 4-way conflicts on every scatter); each conformer still
+    // contributes a contiguous 16-byte piece to the global read.  Out-of-range elements are zero-filled
+    // with plain stores.
+    static_assert(RK % 4 == 0, "chunks are moved in groups of 4 coordinates");
     auto stage = [&](int c, int buf) {
         const int k0 = c * RK;
-        for (int e = tid; e < RK * kRT; e += 256) {
-            const int r = e / RK, k = e - r * RK;
+        const int warp_id = tid >> 5, ln = tid & 31;
+        const int k_l = ln & 3, r_l = ((ln >> 2) & 3) + 16 * (ln >> 4);
+        for (int u = warp_id; u < 16 * (RK / 4); u += 8) {
+            const int rg = u & 15, kg = u >> 4;
+            const int r = 32 * (rg >> 2) + 4 * (rg & 3) + r_l, k = 4 * kg + k_l;
             const int gk = k0 + k, ra = r_base + r, cb = c_base + r;
             if (gk < a.K && ra < a.row1) cp_async_4(&As[buf][k][r], a.xyz + (size_t)ra * a.K + gk);
             else As[buf][k][r] = 0.f;
