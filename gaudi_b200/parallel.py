@@ -225,9 +225,14 @@ class ShardedSimilarity(object):
         if max(totals) > self.cap:
             self._alloc(2 * max(totals))
             return self.step(coords)
+        if self.cap > 4 * max(max(totals), self.m):          # far too roomy: every step pays for it on PCIe
+            self._shrink_to = 2 * max(max(totals), self.m)
         ptr = np.zeros(self.n + 1, np.int64)
         np.cumsum(np.concatenate(per_row), out=ptr[1:])
         idx = np.concatenate([host[r, self.m:self.m + totals[r]] for r in range(self.world)])
+        if getattr(self, "_shrink_to", None):                 # (after the results have left the old buffer)
+            self._alloc(self._shrink_to)
+            self._shrink_to = None
         return ptr, idx
 
 
