@@ -360,8 +360,8 @@ class ShardedEvaluator(object):
         self.engine.evaluate(torsions, xforms, rot_alleles, scores_out=s, counts_out=c)
         if self.kind == "none":
             return s, c
-        dist.all_gather_into_tensor(self._gs, self.scores, group=self.group)
-        dist.all_gather_into_tensor(self._gc, self.counts, group=self.group)
+        _all_gather_into(self._gs, self.scores, self.group)
+        _all_gather_into(self._gc, self.counts, self.group)
         m, b = self.max_shard, self.bounds
         if all(b[r + 1] - b[r] == m for r in range(self.world)):
             return self._gs, self._gc
@@ -406,7 +406,9 @@ class HostSharded(object):
         self.nbytes = max(at, 4096)
         path = [None]
         if self.rank == 0:
-            path[0] = "/dev/shm/gaudimm_b200_%s" % uuid.uuid4().hex
+            import tempfile
+            base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
+            path[0] = os.path.join(base, "gaudimm_b200_%s" % uuid.uuid4().hex)
             with open(path[0], "wb") as fh:
                 fh.truncate(self.nbytes)
         if self.world > 1:
@@ -431,13 +433,19 @@ class HostSharded(object):
             os.unlink(self.path)          # the mappings keep the segment alive; nothing is left behind on a crash
 
     def _wait(self, cond, what):
+        """Spin on a header slot: a few milliseconds flat out (a step is a fraction of a millisecond),
+        then with short sleeps, so that ranks idling between generations do not burn a core each."""
         import time
         t0 = time.perf_counter()
         spins = 0
         while not cond():
             spins += 1
-            if (spins & 0xfff) == 0 and time.perf_counter() - t0 > self.timeout:
-                raise RuntimeError("HostSharded: rank %d waited more than %.0f s for %s" % (self.rank, self.timeout, what))
+            if (spins & 0xff) == 0:
+                waited = time.perf_counter() - t0
+                if waited > self.timeout:
+                    raise RuntimeError("HostSharded: rank %d waited more than %.0f s for %s" % (self.rank, self.timeout, what))
+                if waited > 5e-3:
+                    time.sleep(2e-4)
 
     def run(self, n_rows, fn):
         """Collective.  Rank 0's ``n_rows`` counts; returns the row bounds used."""

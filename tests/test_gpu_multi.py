@@ -40,6 +40,14 @@ def _exchange_worker(rank, world, port, out):
     eng = Engine(lig, rec, params, device=dev)
     pop = 5001                                                      # ragged over the ranks
     results = {}
+    # "nccl" = the collective variant (all_gather_into_tensor; under this test's gloo group it is staged
+    # through the host), kept as the cross-check of the peer-store exchange
+    sh = parallel.ShardedEvaluator(eng, pop, exchange="nccl")
+    tors, xf = synth.make_alleles(pop, 10, seed=2)
+    s, c = sh.evaluate(torch.as_tensor(sh.shard(tors)).to(eng.torch_device), torch.as_tensor(sh.shard(xf)).to(eng.torch_device))
+    want_s, want_c, _ = eng.evaluate(tors, xf)
+    results["collective"] = bool(torch.equal(s, want_s) and torch.equal(c, want_c))
+    sh.close()
     for kind in ("peer",):
         sh = parallel.ShardedEvaluator(eng, pop, exchange=kind)
         for step, seed in enumerate((3, 4, 5)):                     # three epochs: both buffers, then reuse
