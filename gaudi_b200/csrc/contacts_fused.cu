@@ -122,7 +122,7 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
             unsigned hits = 0;
             // slots [0, n_hseed) are hydrophobic seeds, [n_hseed, n_seed) the other seeds; mobile
             // atoms that are not seeds (flexible side chains) are not sorted and keep the wide cutoff
-#pragma unroll 2
+#pragma unroll 4
             for (int k = 0; k < n; ++k) {
                 const int s = s0 + k;
                 const float4 m = ligc[s];
@@ -424,7 +424,7 @@ contacts_fused_kernel(const FusedArgs f) {
                         const float b0 = bx[0], b1 = bx[1], b2 = bx[2], b3 = bx[3], b4 = bx[4], b5 = bx[5];
                         const float reach = fmaxf(sqrtf(a.rad2), bx[6] + a.rmax_mobile - a.thr_min) + a.reach_extra;
                         float mn = 3e38f;
-#pragma unroll 2
+#pragma unroll 4
                         for (int s = 0; s < a.M; ++s) {
                             const float4 m = ligx[s];
                             const float ex = fmaxf(fmaxf(b0 - m.x, m.x - b3), 0.f);
@@ -478,7 +478,7 @@ contacts_fused_kernel(const FusedArgs f) {
             // two mobile atoms per step: 6 FFMA + one 3-input FMNMX3 per receptor atom
             int s = 0;
             if (CULL) {
-#pragma unroll 2
+#pragma unroll 4
                 for (; s + 1 < a.n_seed; s += 2) {
                     const float4 m = ligc[s], q = ligc[s + 1];
 #pragma unroll
