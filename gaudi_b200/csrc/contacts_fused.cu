@@ -181,17 +181,24 @@ contacts_fused_kernel(const FusedArgs f) {
     uint32_t* pq = cq + kCandQ;
 
     // ---- 0. stage the pose --------------------------------------------------------------
-    // The pose's M x 3 floats are one contiguous, 16-byte aligned block in HBM: a single TMA
-    // bulk copy (cp.async.bulk, SASS UBLKCP) lands it in this team's queue area (unused until the
-    // sweep), completion signalled on an mbarrier; lanes then permute it into slot order.  Poses
-    // whose byte count is not a multiple of 16 or that do not fit the landing area are read with
-    // plain loads instead (f.tma_pose == 0, decided per launch).
-    if (f.tma_pose) {
-        const float* raw = reinterpret_cast<const float*>(smem_raw + (size_t)IPC * f.ind_bytes) +
-                           (size_t)(warp - wt) * (kCandQ + kPairQ);
+    // The pose's M x 3 floats are one contiguous block in HBM: a single TMA bulk copy (cp.async.bulk,
+    // SASS UBLKCP), completion signalled on an mbarrier; lanes then permute it into slot order.
+    // General form (!PLAIN): the 16-byte aligned span around the pose lands in the area of the centred
+    // copy (written only after the bounding sphere is known); a pose whose span would end past the
+    // array (the last one, when P x M x 12 is not a multiple of 16) is read with plain loads.
+    // PLAIN keeps the narrower form — poses of whole 16-byte multiples landing in this team's queue
+    // area: with the general one compiled in, the same sweep loop got a different register
+    // assignment and configs[2] ran 1.3 % slower.  f.tma_pose == 0 (decided per
+    // launch): plain loads for everything.
+    const unsigned shift = PLAIN ? 0u : (((unsigned)p * (unsigned)(a.M * 3)) & 3u);
+    if (f.tma_pose && (PLAIN || p + 1 < a.P || (((unsigned)a.P * (unsigned)(a.M * 3)) & 3u) == 0u)) {
+        const float* raw = PLAIN ? reinterpret_cast<const float*>(smem_raw + (size_t)IPC * f.ind_bytes) +
+                                       (size_t)(warp - wt) * (kCandQ + kPairQ)
+                                 : reinterpret_cast<const float*>(ligc);
         unsigned long long* mbar = reinterpret_cast<unsigned long long*>(nlist_p + 2);
         const unsigned mbar_s = (unsigned)__cvta_generic_to_shared(mbar);
-        const unsigned bytes = (unsigned)(a.M * 3 * sizeof(float));
+        const unsigned bytes = PLAIN ? (unsigned)(a.M * 3 * sizeof(float))
+                                     : ((shift + (unsigned)(a.M * 3) + 3u) & ~3u) * (unsigned)sizeof(float);
         if (tlane == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_s));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -200,7 +207,7 @@ contacts_fused_kernel(const FusedArgs f) {
         if (tlane == 0) {
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar_s), "r"(bytes) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         ::"r"((unsigned)__cvta_generic_to_shared(raw)), "l"(a.xyz + (size_t)p * a.M * 3),
+                         ::"r"((unsigned)__cvta_generic_to_shared(raw)), "l"(a.xyz + ((size_t)p * a.M * 3 - shift)),
                            "r"(bytes), "r"(mbar_s) : "memory");
         }
         // The wait is bounded by TIME (two seconds of the global timer, looked at every 4,096 polls),
@@ -232,7 +239,7 @@ contacts_fused_kernel(const FusedArgs f) {
         for (int s = tlane; s < a.Mp; s += TL) {
             const int atom = a.slot2atom[s];
             float4 v = make_float4(kFar, kFar, kFar, 0.f);
-            if (atom >= 0) v = make_float4(raw[3 * atom], raw[3 * atom + 1], raw[3 * atom + 2], a.mrad[s]);
+            if (atom >= 0) v = make_float4(raw[shift + 3 * atom], raw[shift + 3 * atom + 1], raw[shift + 3 * atom + 2], a.mrad[s]);
             ligx[s] = v;
         }
     } else {
@@ -704,9 +711,12 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     f.mirror_row0 = c->pub_row0;
     const size_t ind = fused_ind_bytes(c);
     f.ind_bytes = (int)ind;
+    const bool plain = c->all_seed && c->n_sseed == 0 && c->ms_nnz == 0 && !(c->prm.options & GMM_OPT_ONLY_INTERNAL);
     const size_t pose_bytes = (size_t)c->M * 3 * sizeof(float);
-    f.tma_pose = (pose_bytes % 16 == 0 && pose_bytes <= (kCandQ + kPairQ) * sizeof(uint32_t) &&
-                  (reinterpret_cast<uintptr_t>(xyz) % 16) == 0) ? 1 : 0;
+    // PLAIN: whole 16-byte multiples that fit the queue area; otherwise the aligned span (at most
+    // 12 M + 24 bytes) has to fit the centred copy's 16 Mp bytes
+    f.tma_pose = ((reinterpret_cast<uintptr_t>(xyz) % 16) == 0 &&
+                  (plain ? (pose_bytes % 16 == 0 && pose_bytes <= (kCandQ + kPairQ) * sizeof(uint32_t)) : c->M >= 6)) ? 1 : 0;
     const size_t queues = kFusedQueues;
     const size_t limit = kFusedSmemLimit;
     // warp-per-individual from this population on; below it a CTA per individual fills the GPU better
@@ -717,7 +727,6 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
     if (c->prof) GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));   // the pair-test tally
     const bool cull = f.s.cull != 0;
-    const bool plain = c->all_seed && c->n_sseed == 0 && c->ms_nnz == 0 && !(c->prm.options & GMM_OPT_ONLY_INTERNAL);
     void (*const variants[8])(const FusedArgs) = {
         contacts_fused_kernel<1, false, false>, contacts_fused_kernel<1, false, true>,
         contacts_fused_kernel<1, true, false>, contacts_fused_kernel<1, true, true>,

@@ -144,6 +144,21 @@ def test_rotamers_flexible_side_chains(cuda):
                if not any((int(m[int(a) >> 6]) >> (int(a) & 63)) & 1 for m in eng.mobile.tors_mask)]
     assert len(ca_like) >= 1
     assert np.abs(xyz[:, ca_like] - eng.mobile.xyz0[ca_like]).max() < 1e-5
+    # Pose staging with flexible side chains: the fused kernel copies the 16-byte aligned span around
+    # each pose (12 M bytes, here at every alignment) and reads the last pose of an array that does not
+    # end on a 16-byte boundary with plain loads.  Warp-per-individual (2,701 and 2,700 poses) and
+    # CTA-per-individual (49, 1): fused == tiled, bit for bit.
+    import dataclasses
+    from gaudi_b200.engine import Engine
+    tiled = Engine(eng.mobile, eng.receptor, dataclasses.replace(eng.params, tiled=True), device=0)
+    reps = -(-2701 // 48)
+    T, X, R = (np.tile(v, (reps, 1))[:2701] for v in batch.pack(pop))
+    T = T + rng.uniform(-20, 20, size=T.shape)
+    for n in (2701, 2700, 49, 1):
+        s1, c1, x1 = eng.evaluate(T[:n], X[:n], R[:n], want_xyz=True)
+        s2, c2 = tiled.contacts(x1)
+        assert cuda.equal(s1, s2) and cuda.equal(c1, c2), n
+    tiled.close()
 
 
 def test_tensor_ga_configs0(cuda):
