@@ -293,11 +293,14 @@ int gmm_set_mobile(gmm_ctx* c, int M, const double* xyz0_h, const float* radius_
     if ((rc = upload(&c->d_mrad_slot, rad.data(), (size_t)Mp))) return rc;
     if ((rc = upload(&c->d_mflags_slot, fl.data(), (size_t)Mp))) return rc;
     // intra-mobile pairs more than bond_separation bonds apart, in slot indices
+    // (in slot order: 32 consecutive pairs then read one slot and a run of consecutive ones from shared
+    // memory — a broadcast and a conflict-free vector load)
     std::vector<uint32_t> mm;
-    for (int a = 0; a < M; ++a)
-        for (int b = a + 1; b < M; ++b) {
+    for (int sa = 0; sa < M; ++sa)
+        for (int sb = sa + 1; sb < M; ++sb) {
+            const int a = order[sa], b = order[sb];
             const bool excl = (excl_mask_h[(size_t)a * W + (b >> 6)] >> (b & 63)) & 1ull;
-            if (!excl) mm.push_back((uint32_t)c->h_atom2slot[a] | ((uint32_t)c->h_atom2slot[b] << 16));
+            if (!excl) mm.push_back((uint32_t)sa | ((uint32_t)sb << 16));
         }
     c->n_mm = (int)mm.size();
     c->h_mm_pairs = mm; c->h_mflags_slot = fl;

@@ -623,9 +623,14 @@ contacts_fused_kernel(const FusedArgs f) {
     }
 
     // ---- 4. pairs inside the mobile set ------------------------------------------------------
+    // (the next pair's record is fetched before this one is worked on: at the occupancy a large mobile
+    // set leaves, nothing else hides the load)
+    uint32_t pr_next = 0; float c2_next = 0.f;
+    if (tlane < f.n_mm) { pr_next = f.mm_pairs[tlane]; c2_next = f.mm_c2[tlane]; }
     for (int e = tlane; e < f.n_mm; e += TL) {
-        const uint32_t pr = f.mm_pairs[e];
-        const float c2 = f.mm_c2[e];                   // (r_a + r_b - cutoff)^2, fixed per pair
+        const uint32_t pr = pr_next;
+        const float c2 = c2_next;                      // (r_a + r_b - cutoff)^2, fixed per pair
+        if (e + TL < f.n_mm) { pr_next = f.mm_pairs[e + TL]; c2_next = f.mm_c2[e + TL]; }
         const int sa = pr & 0xffff, sb = pr >> 16;
         if (!PLAIN && !a.all_seed && (!((zm[sa >> 5] >> (sa & 31)) & 1u) || !((zm[sb >> 5] >> (sb & 31)) & 1u))) continue;
         const float4 A = ligx[sa], B = ligx[sb];
