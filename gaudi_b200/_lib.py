@@ -17,6 +17,17 @@ MAX_MOBILE_ATOMS, MAX_TORSIONS = 1024, 1024
 
 _vp, _i, _d = C.c_void_p, C.c_int, C.c_double
 
+
+class CoordSite(C.Structure):
+    """``gmm_coord_site`` of include/gaudimm_b200.h."""
+    _fields_ = [("n_atoms", _i), ("mobile_row", _vp), ("xyz", _vp), ("candidate", _vp), ("geometry", _vp),
+                ("bond_radius", _vp), ("nb_ptr", _vp), ("nb_idx", _vp), ("metal", _i), ("n_vertices", _i),
+                ("template_xyz", _vp), ("radius", _d), ("distance", _d), ("weight", _d), ("min_atoms", _i),
+                ("flags", _i)]
+
+
+COORD_PREVENT_INTRUDERS, COORD_ENFORCE_ALL_RESIDUES, COORD_COM_CORRECTION, COORD_DISTANCE_CORRECTION = 1, 2, 4, 8
+
 # name -> (restype, argtypes); must list every symbol of include/gaudimm_b200.h
 SIGNATURES = {
     "gmm_create": (_i, [C.POINTER(_vp), _i]),
@@ -43,6 +54,8 @@ SIGNATURES = {
     "gmm_exchange_destroy": (_i, [_vp]),
     "gmm_set_geometry": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmm_geometry": (_i, [_vp, _i, _vp, _vp, _vp]),
+    "gmm_set_coordination": (_i, [_vp, _i, _vp]),
+    "gmm_coordination": (_i, [_vp, _i, _vp, _vp, _vp]),
     "gmm_rmsd_matrix": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _vp, _d, _vp]),
     "gmm_similar_lists": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, C.c_longlong, _vp]),
     "gmm_niching_host": (_i, [_i, _vp, _vp, _vp, _vp]),

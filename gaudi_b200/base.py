@@ -288,12 +288,15 @@ class BatchEvaluator(object):
         contacts = [(i, o) for i, o in enumerate(environment.objectives.values())
                     if o.__class__.__name__ == "Contacts"]
         self.geometry = [(i, o) for i, o in enumerate(environment.objectives.values())
-                         if getattr(o, "geometry", False)]
+                         if getattr(o, "geometry", False) is True]     # (Coordination.geometry is its template)
+        self.coordination = [(i, o) for i, o in enumerate(environment.objectives.values())
+                             if getattr(o, "coordination", False)]
         others = [o for o in environment.objectives.values()
-                  if o.__class__.__name__ != "Contacts" and not getattr(o, "geometry", False)]
+                  if o.__class__.__name__ != "Contacts" and getattr(o, "geometry", False) is not True
+                  and not getattr(o, "coordination", False)]
         if others:
-            raise NotImplementedError("only Contacts, Distance and Angle objectives run on the B200 path: %s"
-                                      % [o.name for o in others])
+            raise NotImplementedError("only Contacts, Distance, Angle and Coordination objectives run on the B200 "
+                                      "path: %s" % [o.name for o in others])
         grouped = OrderedDict()
         for i, o in contacts:
             placed = False
@@ -306,7 +309,7 @@ class BatchEvaluator(object):
             if not placed:
                 grouped[(o.model_key(), len(grouped))] = {"members": [(i, o)], "penalty": o.penalty_key()}
         self.engines = []
-        if not grouped and self.geometry:
+        if not grouped and (self.geometry or self.coordination):
             # restraints only: one context for the expression, with nothing in the Contacts zone
             grouped[(None, 0)] = {"members": [], "penalty": None}
         for key, g in grouped.items():
@@ -366,6 +369,34 @@ class BatchEvaluator(object):
                 for t in o.terms(resolve, covalent):
                     terms.append(dict(t, obj=col))
             self.engines[0][0].set_geometry(terms, len(self.geometry))
+        # ---- Coordination objectives: whole-job atom tables on the first context -------------
+        if self.coordination:
+            from types import SimpleNamespace
+            row = -np.ones(len(xyz), np.int32)
+            row[mobile_idx] = np.arange(len(mobile_idx), dtype=np.int32)
+            neighbours = [[] for _ in range(len(xyz))]
+            for a, b in bonds:                                  # atom.neighbors: in bond order
+                neighbours[int(a)].append(int(b)); neighbours[int(b)].append(int(a))
+            mol_of, resseq, atom_name, idatm = [], [], [], []
+            for name in mol_names:
+                mol = template._molecules[name].mol
+                adj = mol.adjacency()
+                mol_of += [name] * mol.n_atoms
+                resseq += [int(r) for r in mol.resseq]
+                atom_name += list(mol.name)
+                idatm += [molio.idatm_type(mol, i, adj) for i in range(mol.n_atoms)]
+
+            def locate_atom(spec):
+                molname, serial = spec
+                hit = np.flatnonzero(template._molecules[molname].mol.serial == int(serial))
+                if len(hit) != 1:
+                    raise ValueError("atom %s/%s not found" % (molname, serial))
+                return offsets[molname] + int(hit[0])
+
+            self.system = SimpleNamespace(xyz=np.asarray(xyz, np.float64), element=elements, idatm=idatm, name=atom_name,
+                                          molecule=mol_of, resseq=resseq, neighbours=neighbours, mobile_row=row,
+                                          locate=locate_atom)
+            self.engines[0][0].set_coordination([o.site(self.system) for _, o in self.coordination])
         self.centre = centre
         self._sim = None
 
@@ -401,6 +432,10 @@ class BatchEvaluator(object):
                 xyz = coords
             for i, col in members:
                 raw[:, i] = scores[:, col]
+        if self.coordination:
+            crd = self.engines[0][0].coordination(xyz).cpu().numpy()
+            for col, (i, o) in enumerate(self.coordination):
+                raw[:, i] = crd[:, col]
         if self.geometry:
             geo = self.engines[0][0].geometry(xyz).cpu().numpy()
             for col, (i, o) in enumerate(self.geometry):

@@ -98,6 +98,7 @@ int gmm_create(gmm_ctx** out, int device) {
 int gmm_destroy(gmm_ctx* c) {
     if (!c) return GMM_OK;
     gmm_exchange_destroy(c);
+    coordination_destroy(c);
     DeviceGuard g(c->device);
     cudaDeviceSynchronize();
     release(c->d_xyz0); release(c->d_mflags_atom); release(c->d_tfixed); release(c->d_tmoving);
@@ -800,6 +801,41 @@ int gmm_geometry(gmm_ctx* c, int P, const float* xyz_d, double* out_d, void* str
     REQUIRE((xyz_d && out_d) || P == 0, GMM_EINVAL, "gmm_geometry: NULL buffer");
     DeviceGuard g(c->device);
     return launch_geometry(c, P, xyz_d, out_d, (cudaStream_t)stream);
+}
+
+int gmm_set_coordination(gmm_ctx* c, int n_sites, const gmm_coord_site* sites_h) {
+    REQUIRE(c, GMM_EINVAL, "gmm_set_coordination: ctx is NULL");
+    REQUIRE(c->has_mobile, GMM_ESTATE, "gmm_set_coordination: call gmm_set_mobile first");
+    REQUIRE(n_sites >= 0 && n_sites <= 64 && (sites_h || n_sites == 0), GMM_EINVAL, "gmm_set_coordination: bad site list");
+    for (int k = 0; k < n_sites; ++k) {
+        const gmm_coord_site& h = sites_h[k];
+        REQUIRE(h.n_atoms >= 1 && h.mobile_row && h.xyz && h.candidate && h.geometry && h.bond_radius && h.nb_ptr &&
+                h.nb_idx && h.template_xyz, GMM_EINVAL, "gmm_set_coordination: site %d has a NULL table", k);
+        REQUIRE(h.metal >= 0 && h.metal < h.n_atoms, GMM_EINVAL, "gmm_set_coordination: site %d: metal %d not in [0,%d)",
+                k, h.metal, h.n_atoms);
+        REQUIRE(h.n_vertices >= 1 && h.n_vertices <= 8, GMM_EINVAL, "gmm_set_coordination: site %d: %d vertices (1..8)",
+                k, h.n_vertices);
+        REQUIRE(h.radius >= 0.0, GMM_EINVAL, "gmm_set_coordination: site %d: negative radius", k);
+        for (int i = 0; i < h.n_atoms; ++i) {
+            REQUIRE(h.mobile_row[i] < c->M, GMM_EINVAL, "gmm_set_coordination: site %d: atom %d maps to row %d of %d",
+                    k, i, h.mobile_row[i], c->M);
+            REQUIRE(h.nb_ptr[i] <= h.nb_ptr[i + 1], GMM_EINVAL, "gmm_set_coordination: site %d: nb_ptr not monotone", k);
+        }
+        for (int e = 0; e < h.nb_ptr[h.n_atoms]; ++e)
+            REQUIRE(h.nb_idx[e] >= 0 && h.nb_idx[e] < h.n_atoms, GMM_EINVAL, "gmm_set_coordination: site %d: bad neighbour", k);
+    }
+    DeviceGuard g(c->device);
+    return coordination_set(c, n_sites, sites_h);
+}
+
+int gmm_coordination(gmm_ctx* c, int P, const float* xyz_d, double* out_d, void* stream) {
+    REQUIRE(c, GMM_EINVAL, "gmm_coordination: ctx is NULL");
+    REQUIRE(c->has_mobile, GMM_ESTATE, "gmm_coordination: call gmm_set_mobile first");
+    REQUIRE(coordination_sites(c) > 0, GMM_ESTATE, "gmm_coordination: gmm_set_coordination has not been called");
+    REQUIRE(P >= 0, GMM_EINVAL, "gmm_coordination: P=%d", P);
+    REQUIRE((xyz_d && out_d) || P == 0, GMM_EINVAL, "gmm_coordination: NULL buffer");
+    DeviceGuard g(c->device);
+    return launch_coordination(c, P, xyz_d, out_d, (cudaStream_t)stream);
 }
 
 int gmm_rmsd_matrix(gmm_ctx* c, int N, int A, const float* xyz_d, int row0, int row1, float* out_rmsd_d,

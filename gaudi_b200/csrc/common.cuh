@@ -209,6 +209,8 @@ struct gmm_ctx {
     // geometric restraint objectives (gmm_set_geometry)
     gmm::GeoTerm* d_geo_terms = nullptr; int n_geo_terms = 0, n_geo_obj = 0;
 
+    void* coordination = nullptr;    // gmm::CoordState (coordination.cu)
+
     // scratch (grown on demand)
     void* d_scratch = nullptr; size_t scratch_bytes = 0;
     unsigned long long* d_counters = nullptr;   // [4] pair tests, ...
@@ -241,6 +243,10 @@ void prefilter_cutoffs(const gmm_ctx* c, float* thr_min, float* thr_tight);
 bool fused_applicable(const gmm_ctx* c);
 int launch_geometry(gmm_ctx* c, int P, const float* xyz, double* out, cudaStream_t s);
 int launch_rr_values(gmm_ctx* c, cudaStream_t s);
+int coordination_set(gmm_ctx* c, int n_sites, const gmm_coord_site* sites);
+int coordination_sites(const gmm_ctx* c);
+void coordination_destroy(gmm_ctx* c);
+int launch_coordination(gmm_ctx* c, int P, const float* xyz, double* out, cudaStream_t s);
 int launch_rmsd(gmm_ctx* c, int N, int A, const float* xyz, int row0, int row1, float* out_rmsd,
                 uint32_t* out_bits, double thr, cudaStream_t s);
 int reserve_rmsd_workspace(gmm_ctx* c, int N, int A);

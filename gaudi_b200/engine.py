@@ -271,6 +271,48 @@ class Engine(object):
         _lib.check(self._L.gmm_geometry(self._h, P, _dev_ptr(xyz), _dev_ptr(out), self._stream()))
         return out
 
+    def set_coordination(self, sites):
+        """``sites``: one dict per Coordination objective with the whole-job atom tables
+        (``mobile_row`` int32 [n], ``xyz`` float64 [n, 3], ``candidate`` / ``geometry`` uint8 [n],
+        ``bond_radius`` float64 [n], ``neighbours``: list of bonded-atom lists in bond order),
+        ``metal``, ``template`` [(v + 1), 3], ``radius``, ``distance``, ``weight``, ``min_atoms`` and the
+        booleans ``prevent_intruders``, ``enforce_all_residues``, ``center_of_mass_correction``,
+        ``distance_correction`` (gaudi/objectives/coordination.py:130-145)."""
+        import ctypes as C
+        arr = (_lib.CoordSite * max(1, len(sites)))()
+        keep = []
+        for k, s in enumerate(sites):
+            n = len(s["mobile_row"])
+            ptr = np.zeros(n + 1, np.int32)
+            ptr[1:] = np.cumsum([len(v) for v in s["neighbours"]])
+            idx = np.array([a for v in s["neighbours"] for a in v], np.int32)
+            tabs = [np.ascontiguousarray(s["mobile_row"], np.int32), np.ascontiguousarray(s["xyz"], np.float64),
+                    np.ascontiguousarray(s["candidate"], np.uint8), np.ascontiguousarray(s["geometry"], np.uint8),
+                    np.ascontiguousarray(s["bond_radius"], np.float64), ptr, idx if len(idx) else np.zeros(1, np.int32),
+                    np.ascontiguousarray(s["template"], np.float64)]
+            keep.append(tabs)
+            a = arr[k]
+            a.n_atoms = n
+            (a.mobile_row, a.xyz, a.candidate, a.geometry, a.bond_radius, a.nb_ptr, a.nb_idx,
+             a.template_xyz) = [_np_ptr(t) for t in tabs]
+            a.metal, a.n_vertices = int(s["metal"]), len(tabs[7]) - 1
+            a.radius, a.distance, a.weight = float(s["radius"]), float(s["distance"]), float(s["weight"])
+            a.min_atoms = int(s["min_atoms"])
+            a.flags = ((_lib.COORD_PREVENT_INTRUDERS if s.get("prevent_intruders", True) else 0) |
+                       (_lib.COORD_ENFORCE_ALL_RESIDUES if s.get("enforce_all_residues") else 0) |
+                       (_lib.COORD_COM_CORRECTION if s.get("center_of_mass_correction") else 0) |
+                       (_lib.COORD_DISTANCE_CORRECTION if s.get("distance_correction") else 0))
+        _lib.check(self._L.gmm_set_coordination(self._h, len(sites), C.cast(arr, C.c_void_p)))
+        self.n_coord_sites = len(sites)
+
+    def coordination(self, xyz):
+        """(P, n_sites) float64 Coordination scores of expressed coordinates (P, M, 3)."""
+        xyz = self._dev(xyz, torch.float32)
+        P = int(xyz.shape[0])
+        out = torch.empty((P, self.n_coord_sites), dtype=torch.float64, device=self.torch_device)
+        _lib.check(self._L.gmm_coordination(self._h, P, _dev_ptr(xyz), _dev_ptr(out), self._stream()))
+        return out
+
     # -- parity / measurement helpers --------------------------------------------------
     def contact_pairs(self, xyz_one, max_pairs=1 << 16):
         """Pairs behind the Contacts score of one individual: list of

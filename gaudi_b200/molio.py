@@ -46,6 +46,18 @@ SYBYL_TO_IDATM = {
     "S.O": "Sxd", "S.O2": "Son", "P.3": "P", "H": "H",
 }
 
+# chimera.idatm.typeInfo[type].geometry (4 tetrahedral, 3 planar, 2 linear, 1 single, 0 ion), restated
+# from Chimera's published IDATM table; types that are not listed count as planar, as
+# gaudi/objectives/coordination.py:307-308 does.  The Coordination goldens exercise O2- and Npl.
+IDATM_GEOMETRY = {
+    "C3": 4, "C2": 3, "Car": 3, "Cac": 3, "C1": 2, "C1-": 2,
+    "N3+": 4, "N3": 4, "N2+": 3, "N2": 3, "Npl": 3, "Ng+": 3, "Ntr": 3, "Nox": 4, "N1+": 2, "N1": 2,
+    "O3": 4, "O2": 3, "Oar": 3, "Oar+": 3, "O3-": 4, "O2-": 3, "O1": 2, "O1+": 2,
+    "S3+": 4, "S3": 4, "S2": 3, "Sar": 3, "Sac": 4, "Son": 4, "Sxd": 4, "S3-": 4,
+    "Pac": 4, "Pox": 4, "P3+": 4, "P": 4, "B": 3, "Bac": 4, "Box": 3,
+    "H": 1, "HC": 1, "D": 1, "DC": 1, "F": 1, "Cl": 1, "Br": 1, "I": 1,
+}
+
 
 @dataclass
 class Mol:

@@ -42,6 +42,7 @@ B200_MODULES = {
     "gaudi.objectives.contacts": "gaudi_b200.objectives.contacts",
     "gaudi.objectives.distance": "gaudi_b200.objectives.distance",
     "gaudi.objectives.angle": "gaudi_b200.objectives.angle",
+    "gaudi.objectives.coordination": "gaudi_b200.objectives.coordination",
     "gaudi.similarity.rmsd": "gaudi_b200.similarity.rmsd",
 }
 

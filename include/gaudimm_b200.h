@@ -277,6 +277,41 @@ int gmm_set_geometry(gmm_ctx* ctx, int n_terms, int n_obj, const int32_t* kind_h
 /*   xyz_d [P, M, 3] fp32 device-frame coordinates; out_d [P, n_obj] fp64 */
 int gmm_geometry(gmm_ctx* ctx, int P, const float* xyz_d, double* out_d, void* stream);
 
+/* Coordination objective on expressed coordinates ("next" row of the scope:
+ * gaudi/objectives/coordination.py:180-283 — sphere search around a metal, rigid coherent point
+ * drift of the ligand atoms onto a geometry template (gaudi/_cpdrift.py:45-93), directionality of
+ * the ligand atoms' free valences (:286-372) and the two optional corrections).  A site is one
+ * Coordination objective; its tables run over all atoms of the job (every Molecule gene, caller's
+ * numbering).  What Chimera supplies to the reference — bonded atoms in bond order, the geometry of
+ * each atom's IDATM type, covalent bond radii — comes in as plain arrays. */
+typedef struct gmm_coord_site {
+    int n_atoms;
+    const int32_t* mobile_row;     /* [n_atoms] row of the atom in the expressed poses, -1: static */
+    const double* xyz;             /* [n_atoms, 3] world coordinates (read for static atoms) */
+    const uint8_t* candidate;      /* [n_atoms] 1: passes atom_types / atom_elements / atom_names and
+                                      belongs to one of `residues` (coordination.py:244-252,258) */
+    const uint8_t* geometry;       /* [n_atoms] chimera.idatm geometry: 4 tetrahedral, 3 planar, 2 linear, 1 single */
+    const double* bond_radius;     /* [n_atoms] chimera.Element.bondLength(a, b) = radius[a] + radius[b] */
+    const int32_t* nb_ptr;         /* [n_atoms + 1] CSR of bonded atoms, in bond order (atom.neighbors) */
+    const int32_t* nb_idx;
+    int metal;                     /* `probe` */
+    int n_vertices;                /* <= 8 */
+    const double* template_xyz;    /* [(n_vertices + 1), 3] `geometry`, the metal's place last */
+    double radius, distance, weight;
+    int min_atoms;
+    int flags;                     /* GMM_COORD_* */
+} gmm_coord_site;
+#define GMM_COORD_PREVENT_INTRUDERS 1
+#define GMM_COORD_ENFORCE_ALL_RESIDUES 2   /* as in the reference, never satisfied: -1000 * weight */
+#define GMM_COORD_COM_CORRECTION 4
+#define GMM_COORD_DISTANCE_CORRECTION 8
+/* Copies everything it needs; n_sites = 0 clears.  gmm_set_mobile / gmm_set_params first. */
+int gmm_set_coordination(gmm_ctx* ctx, int n_sites, const gmm_coord_site* sites_h);
+/*   xyz_d [P, M, 3] fp32 device-frame coordinates; out_d [P, n_sites] fp64.  An individual with
+ *   more than 192 atoms within the radius of a metal gets NaN.  The first call for a larger P
+ *   allocates its scratch rows (synchronous); later calls only enqueue two kernels. */
+int gmm_coordination(gmm_ctx* ctx, int P, const float* xyz_d, double* out_d, void* stream);
+
 /* Parity / debugging: the pair lists the Contacts score of ONE individual is made of
  * (what Contacts.find_interactions returns, contacts.py:140-146).  Atom ids: mobile atoms
  * 0..M-1, static atoms M..M+R-1 (caller's receptor order).  kind: 0 = clash (volume),

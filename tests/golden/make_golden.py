@@ -8,8 +8,12 @@ Run in the build container (where /root/reference exists):
 It (1) converts the structure files the reference's hot-path tests use
 (/root/reference/tests/data/*) into compact .npz atom tables that travel to the GPU box,
 (2) records the golden values those tests assert and (3) imports the
-reference's own ``gaudi/similarity.py`` (the only reference module that runs under
-Python 3 without UCSF Chimera) to generate RMSD vectors on seeded random inputs.
+reference's own ``gaudi/similarity.py`` and ``gaudi/_cpdrift.py`` (the reference modules that run
+under Python 3 without UCSF Chimera) to generate RMSD vectors and rigid-CPD results on seeded
+random inputs.
+
+    python tests/golden/make_golden.py coordination      # only the Coordination fixtures (added later;
+                                                         # leaves the other files byte-identical)
 """
 import json
 import os
@@ -38,7 +42,52 @@ def dump(mol, out):
     np.savez_compressed(os.path.join(HERE, out), **kw)
 
 
+def coordination_fixtures():
+    """4c3w.mol2 (the complex of tests/test_objectives_coordination.py) and the reference's own
+    rigid CPD (gaudi/_cpdrift.py, loaded by path: the package's __init__ imports Chimera) on
+    seeded point sets: noisy, rotated, scaled picks of the geometry templates' vertices."""
+    import importlib.util
+    dump(molio.read_mol2(os.path.join(DATA, "4c3w.mol2")), "4c3w_mol2.npz")
+    spec = importlib.util.spec_from_file_location("ref_cpdrift", os.path.join(REF, "gaudi", "_cpdrift.py"))
+    cpd = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(cpd)
+    sys.path.insert(0, os.path.join(ROOT))
+    from oracle.coordination_oracle import GEOMETRIES
+    rng = np.random.default_rng(20261107)
+    names = sorted(GEOMETRIES)
+    X = np.zeros((240, 9, 3)); n_pts = np.zeros(240, np.int32); which = np.zeros(240, np.int32)
+    rmsd = np.zeros(240); ok = np.zeros(240, bool)
+    for k in range(240):
+        which[k] = k % len(names)
+        Y = np.array(GEOMETRIES[names[which[k]]])
+        n = int(rng.integers(2, len(Y) + 1))
+        q = rng.normal(size=4); q /= np.linalg.norm(q)
+        w, x, y, z = q
+        R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                      [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                      [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        pick = list(rng.permutation(len(Y) - 1)[:n - 1]) + [len(Y) - 1]
+        pts = 2.1 * Y[pick].dot(R.T) + rng.normal(size=3) * 5 + rng.normal(scale=rng.choice([0.0, 0.05, 0.3, 1.0]), size=(n, 3))
+        X[k, :n] = pts; n_pts[k] = n
+        try:
+            rmsd[k] = cpd.coherent_point_drift(pts, Y.copy(), method="rigid", guess_steps=2, max_iterations=10)[2]
+            ok[k] = True
+        except Exception:
+            rmsd[k] = np.nan
+    np.savez_compressed(os.path.join(HERE, "cpd_reference.npz"), points=X, n_points=n_pts, template=which,
+                        template_names=np.array(names), rmsd=rmsd, ok=ok)
+    with open(os.path.join(HERE, "coordination_values.json"), "w") as fh:
+        json.dump({"G11_coordination_4c3w": {"metal": 1005, "ligands": [1013, 1014, 1021, 1023, 1024, 408],
+                                             "geometry": "octahedron", "elements": ["C", "N", "O", "S"],
+                                             "score": 2.4696, "score_corrected": 3.2405, "tol": 1e-4,
+                                             "source": "tests/test_objectives_coordination.py:33-60"}},
+                  fh, indent=1, sort_keys=True)
+    print("wrote the Coordination fixtures to", HERE, "(CPD cases that failed in the reference: %d)" % int((~ok).sum()))
+
+
 def main():
+    if sys.argv[1:] == ["coordination"]:
+        return coordination_fixtures()
     for f in ("1amb.pdb", "5dfr_minimized.pdb", "3pk2_ligand.pdb", "3pk2_ligand_rotated.pdb"):
         dump(molio.read_pdb(os.path.join(DATA, f)), f.replace(".pdb", "_pdb.npz"))
     for f in ("3pk2_ligand.mol2", "4c3w_protein.mol2", "5er1_ligand.mol2", "5er1_protein.mol2"):
@@ -85,6 +134,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "similarity_reference.npz"), conformers=conf, rmsd_squared=sq,
                         similar=sim, threshold=2.5)
     print("wrote fixtures to", HERE)
+    coordination_fixtures()
 
 
 if __name__ == "__main__":

@@ -142,3 +142,30 @@ def rmsd_matrix(xyz, rows=None):
 
 def oracle():
     return O
+
+
+# --------------------------------------------------------------------------------------
+# Coordination objective (oracle/coordination_oracle.py)
+# --------------------------------------------------------------------------------------
+import coordination_oracle as CO  # noqa: E402
+
+
+def coordination(site, xyz_world):
+    """Oracle score of one individual for a site table (the dict ``Engine.set_coordination`` takes)
+    and the world coordinates of every atom of the job."""
+    return CO.coordination(xyz_world, int(site["metal"]), np.asarray(site["candidate"], bool), site["neighbours"],
+                           site["geometry"], site["bond_radius"], site["template"], radius=site["radius"],
+                           distance=site["distance"], min_atoms=site["min_atoms"],
+                           prevent_intruders=site.get("prevent_intruders", True),
+                           enforce_all_residues=site.get("enforce_all_residues", False),
+                           center_of_mass_correction=site.get("center_of_mass_correction", False),
+                           distance_correction=site.get("distance_correction", False), weight=site["weight"])
+
+
+def coordination_world(site, pose_world):
+    """World coordinates of all atoms: static ones from the site table, mobile ones from the
+    expressed pose (rows ``site['mobile_row']``)."""
+    xyz = np.array(site["xyz"], np.float64)
+    row = np.asarray(site["mobile_row"])
+    xyz[row >= 0] = pose_world[row[row >= 0]]
+    return xyz

@@ -128,3 +128,58 @@ def test_greedy_niching_restatement():
     fit = {0: 1.0, 1: 2.0, 2: 5.0, 3: 4.0}
     kept = O.greedy_niching([0, 1, 2, 3], lambda i, j: (i, j) in sim, lambda i, j: fit[i] <= fit[j])
     assert kept == [1, 2]
+
+
+# ---- Coordination objective ------------------------------------------
+def coordination_site_4c3w(mobile=(), **kw):
+    """Site table of the reference's Coordination test (tests/test_objectives_coordination.py:33-60)
+    from the fixture, typed by the product's host prep (molio)."""
+    import json
+    import os
+    from gaudi_b200.objectives.coordination import GEOMETRIES
+    mol = G.load("4c3w_mol2")
+    g = json.load(open(os.path.join(G.GOLDEN, "coordination_values.json")))["G11_coordination_4c3w"]
+    adj = mol.adjacency()
+    nbs = [[] for _ in range(mol.n_atoms)]
+    for a, b in mol.bonds:
+        nbs[int(a)].append(int(b)); nbs[int(b)].append(int(a))
+    idatm = [molio.idatm_type(mol, i, adj) for i in range(mol.n_atoms)]
+    row = -np.ones(mol.n_atoms, np.int32)
+    row[list(mobile)] = np.arange(len(mobile))
+    site = {"mobile_row": row, "xyz": mol.xyz.astype(np.float64),
+            "candidate": np.array([e.upper() in g["elements"] for e in mol.element], np.uint8),
+            "geometry": np.array([molio.IDATM_GEOMETRY.get(t, 3) for t in idatm], np.uint8),
+            "bond_radius": np.array([molio.BOND_RADIUS.get(e.upper(), 0.8) for e in mol.element]),
+            "neighbours": nbs, "metal": int(np.flatnonzero(mol.serial == g["metal"])[0]),
+            "template": np.array(GEOMETRIES[g["geometry"]]), "radius": 3.0, "distance": 0.0, "weight": -1.0,
+            "min_atoms": 1}
+    site.update(kw)
+    return mol, site, g
+
+
+def test_G11_coordination_goldens():
+    """2.4696 and, with both corrections, 3.2405; the six ligand atoms the reference's test names."""
+    mol, site, g = coordination_site_4c3w()
+    sphere = OA.CO.coordination_sphere(site["xyz"], site["metal"], site["candidate"].astype(bool))[:6]
+    assert sorted(int(mol.serial[i]) for _, i in sphere) == sorted(g["ligands"])
+    assert abs(OA.coordination(site, site["xyz"]) - g["score"]) < g["tol"]
+    site.update(center_of_mass_correction=True, distance_correction=True)
+    assert abs(OA.coordination(site, site["xyz"]) - g["score_corrected"]) < g["tol"]
+    # penalties of coordination.py:191-199
+    site.update(min_atoms=12)
+    assert OA.coordination(site, site["xyz"]) == -100.0 * 2 * -1.0        # ten atoms precede the first intruder
+    site.update(min_atoms=1, enforce_all_residues=True)
+    assert OA.coordination(site, site["xyz"]) == 1000.0
+
+
+def test_rigid_cpd_matches_reference_module():
+    """oracle rigid CPD == the reference's own gaudi/_cpdrift.py (outputs recorded in the build container)."""
+    z = np.load(G.GOLDEN + "/cpd_reference.npz")
+    names = [str(n) for n in z["template_names"]]
+    assert z["ok"].all()
+    worst = 0.0
+    for pts, n, t, want in zip(z["points"], z["n_points"], z["template"], z["rmsd"]):
+        got, ok = OA.CO.rigid_cpd_rmsd(pts[:n], np.array(OA.CO.GEOMETRIES[names[t]]))
+        assert ok
+        worst = max(worst, abs(got - want))
+    assert worst < 1e-9, worst
