@@ -322,37 +322,50 @@ coord_sphere_kernel(int P, int M, const float* xyz, const CoordSite* sites, int 
     }
 }
 
-// Top eigenvector of a symmetric 4 x 4 matrix (cyclic Jacobi): q = (w, x, y, z)
-__device__ void coord_top_eigenvector(double a[4][4], double* q) {
-    double v[4][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}};
+// Cyclic Jacobi on a symmetric 4 x 4 matrix held in registers (every index below is a compile-time
+// constant after unrolling).  `v` comes in as an orthogonal basis in which `a` is expressed and
+// leaves as the eigenvectors: an EM step starts from the eigenvectors of the step before, in which
+// the new matrix is nearly diagonal, so two or three sweeps do where a cold start needs six.
+__device__ __forceinline__ void coord_jacobi(double (&a)[4][4], double (&v)[4][4]) {
+#pragma unroll 1
     for (int sweep = 0; sweep < 30; ++sweep) {
         double off = 0.0, diag = 0.0;
-        for (int i = 0; i < 4; ++i) { diag += a[i][i] * a[i][i]; for (int j = i + 1; j < 4; ++j) off += a[i][j] * a[i][j]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            diag += a[i][i] * a[i][i];
+#pragma unroll
+            for (int j = i + 1; j < 4; ++j) off += a[i][j] * a[i][j];
+        }
         if (off <= 1e-32 * diag || off == 0.0) break;
-        for (int pi = 0; pi < 3; ++pi)
-            for (int qi = pi + 1; qi < 4; ++qi) {
-                const double apq = a[pi][qi];
-                if (apq == 0.0) continue;
-                const double theta = (a[qi][qi] - a[pi][pi]) / (2.0 * apq);
-                const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                const double c = 1.0 / sqrt(t * t + 1.0), sn = t * c;
-                for (int k = 0; k < 4; ++k) {
-                    const double akp = a[k][pi], akq = a[k][qi];
-                    a[k][pi] = c * akp - sn * akq; a[k][qi] = sn * akp + c * akq;
-                }
-                for (int k = 0; k < 4; ++k) {
-                    const double apk = a[pi][k], aqk = a[qi][k];
-                    a[pi][k] = c * apk - sn * aqk; a[qi][k] = sn * apk + c * aqk;
-                }
-                for (int k = 0; k < 4; ++k) {
-                    const double vkp = v[k][pi], vkq = v[k][qi];
-                    v[k][pi] = c * vkp - sn * vkq; v[k][qi] = sn * vkp + c * vkq;
+#pragma unroll
+        for (int p = 0; p < 3; ++p)
+#pragma unroll
+            for (int q = p + 1; q < 4; ++q) {
+                const double apq = a[p][q];
+                if (apq != 0.0) {
+                    // t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)), theta = (a_qq - a_pp) / (2 a_pq),
+                    // with numerator and denominator scaled by 2 |a_pq|: one square root, one division
+                    const double d = a[q][q] - a[p][p];
+                    const double t = (d >= 0.0 ? 2.0 * apq : -2.0 * apq) / (fabs(d) + sqrt(d * d + 4.0 * apq * apq));
+                    const double c = rsqrt(t * t + 1.0), sn = t * c;
+                    a[p][p] -= t * apq; a[q][q] += t * apq;
+                    a[p][q] = 0.0; a[q][p] = 0.0;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        if (r != p && r != q) {
+                            const double arp = a[r][p], arq = a[r][q];
+                            a[r][p] = c * arp - sn * arq; a[p][r] = a[r][p];
+                            a[r][q] = sn * arp + c * arq; a[q][r] = a[r][q];
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const double vkp = v[k][p], vkq = v[k][q];
+                        v[k][p] = c * vkp - sn * vkq; v[k][q] = sn * vkp + c * vkq;
+                    }
                 }
             }
     }
-    int best = 0;
-    for (int i = 1; i < 4; ++i) if (a[i][i] > a[best][best]) best = i;
-    for (int k = 0; k < 4; ++k) q[k] = v[k][best];
 }
 
 __device__ __forceinline__ void rot_apply(const double* R, const double* y, double* o) {
@@ -361,19 +374,11 @@ __device__ __forceinline__ void rot_apply(const double* R, const double* y, doub
     o[2] = R[6] * y[0] + R[7] * y[1] + R[8] * y[2];
 }
 
-// _cpdrift.py:156-157: sqrt of the mean over the axes of the variance over the points
-__device__ double coord_spread(const double (*pts)[3], int n) {
-    double tot = 0.0;
-    for (int k = 0; k < 3; ++k) {
-        double mean = 0.0, var = 0.0;
-        for (int i = 0; i < n; ++i) mean += pts[i][k];
-        mean /= n;
-        for (int i = 0; i < n; ++i) var += (pts[i][k] - mean) * (pts[i][k] - mean);
-        tot += var / n;
-    }
-    return sqrt(tot / 3.0);
-}
-
+// Rigid coherent point drift, one thread per (individual, start rotation) (_cpdrift.py:45-93,127-149
+// with w = 0).  Written in coordinates centred on the mean of X.  Every column of the reference's P
+// sums to one, so its row-sum vector over X, N_p and mu_x are N ones, N and the mean of X up to
+// rounding; they are still accumulated as sums here, but that is why A needs no stored P: with
+// q_m = sum_n P_mn (x_n - mean) the reference's X^T P^T Y (hats omitted) is sum_m q_m (y_m - mu_y)^T.
 __global__ void __launch_bounds__(128)
 coord_cpd_kernel(int P, const CoordSite* sites, int n_sites, const CoordWork* work, double* out) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -386,80 +391,117 @@ coord_cpd_kernel(int P, const CoordSite* sites, int n_sites, const CoordWork* wo
     bool ok = true;
     if (active && w.status == 0) {
         const int N = w.n_pts, Mv = s.n_vertices + 1;
-        double X[kCoordMaxPoints][3], Y[kCoordMaxPoints][3], TY[kCoordMaxPoints][3], Pm[kCoordMaxPoints][kCoordMaxPoints];
-        for (int i = 0; i < N; ++i) for (int k = 0; k < 3; ++k) X[i][k] = w.X[3 * i + k];
-        for (int i = 0; i < Mv; ++i) for (int k = 0; k < 3; ++k) Y[i][k] = s.tmpl[3 * i + k];
+        double X[kCoordMaxPoints][3], TY[kCoordMaxPoints][3], q[kCoordMaxPoints][3], p1[kCoordMaxPoints], o[kCoordMaxPoints];
+        double mean[3] = {0, 0, 0}, xvar = 0.0;
+        for (int i = 0; i < N; ++i) for (int k = 0; k < 3; ++k) { X[i][k] = w.X[3 * i + k]; mean[k] += X[i][k]; }
+        for (int k = 0; k < 3; ++k) mean[k] /= N;
+        for (int i = 0; i < N; ++i) for (int k = 0; k < 3; ++k) { X[i][k] -= mean[k]; xvar += X[i][k] * X[i][k]; }
+        const double* Y = s.tmpl;
+        const double sx = sqrt(xvar / (3.0 * N));           // _cpdrift.py:156-157 of X
         double R[9];
         for (int k = 0; k < 9; ++k) R[k] = s.start[9 * start + k];
-        const double sx = coord_spread(X, N);
-        for (int i = 0; i < Mv; ++i) rot_apply(R, Y[i], TY[i]);
-        double sc = sx / coord_spread(TY, Mv);
-        double t[3];
-        for (int k = 0; k < 3; ++k) {
-            double mx = 0.0, my = 0.0;
-            for (int i = 0; i < N; ++i) mx += X[i][k];
-            for (int i = 0; i < Mv; ++i) my += sc * TY[i][k];
-            t[k] = mx / N - my / Mv;
-        }
+        // s = std(X) / std(R Y); t = mean(X) - mean(s R Y); sigma^2 = mean squared distance / 3
+        double ym[3] = {0, 0, 0}, yvar = 0.0;
+        for (int m = 0; m < Mv; ++m) { rot_apply(R, Y + 3 * m, TY[m]); for (int k = 0; k < 3; ++k) ym[k] += TY[m][k]; }
+        for (int k = 0; k < 3; ++k) ym[k] /= Mv;
+        for (int m = 0; m < Mv; ++m) for (int k = 0; k < 3; ++k) yvar += (TY[m][k] - ym[k]) * (TY[m][k] - ym[k]);
+        double sc = sx / sqrt(yvar / (3.0 * Mv));
+        double t[3] = {-sc * ym[0], -sc * ym[1], -sc * ym[2]};
         double sigma2 = 0.0;
         for (int m = 0; m < Mv; ++m)
             for (int n = 0; n < N; ++n)
                 for (int k = 0; k < 3; ++k) { const double d = sc * TY[m][k] + t[k] - X[n][k]; sigma2 += d * d; }
         sigma2 /= 3.0 * Mv * N;
+        double V[4][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}};
         int done = 0;
+#pragma unroll 1
         for (int it = 0; it < kCoordIters; ++it) {
             if (!(sigma2 > 0.0)) break;          // the step's arithmetic would be invalid (_cpdrift.py:79-86)
-            for (int m = 0; m < Mv; ++m) { rot_apply(R, Y[m], TY[m]); for (int k = 0; k < 3; ++k) TY[m][k] = sc * TY[m][k] + t[k]; }
+            for (int m = 0; m < Mv; ++m) {
+                rot_apply(R, Y + 3 * m, TY[m]);
+                for (int k = 0; k < 3; ++k) { TY[m][k] = sc * TY[m][k] + t[k]; q[m][k] = 0.0; }
+                p1[m] = 0.0;
+            }
+            const double inv2s = -1.0 / (2.0 * sigma2);
             bool valid = true;
+            double e[3] = {0, 0, 0}, xv = 0.0;
+#pragma unroll 1
             for (int n = 0; n < N; ++n) {
                 double col = 0.0;
                 for (int m = 0; m < Mv; ++m) {
                     const double dx = TY[m][0] - X[n][0], dy = TY[m][1] - X[n][1], dz = TY[m][2] - X[n][2];
-                    Pm[m][n] = exp(-(dx * dx + dy * dy + dz * dz) / (2.0 * sigma2));
-                    col += Pm[m][n];
+                    o[m] = exp((dx * dx + dy * dy + dz * dz) * inv2s);
+                    col += o[m];
                 }
                 if (col == 0.0 || !isfinite(col)) { valid = false; break; }
-                for (int m = 0; m < Mv; ++m) Pm[m][n] /= col;
+                const double inv = 1.0 / col;
+                double pt = 0.0;
+                for (int m = 0; m < Mv; ++m) {
+                    const double pm = o[m] * inv;
+                    pt += pm; p1[m] += pm;
+                    q[m][0] += pm * X[n][0]; q[m][1] += pm * X[n][1]; q[m][2] += pm * X[n][2];
+                }
+                e[0] += pt * X[n][0]; e[1] += pt * X[n][1]; e[2] += pt * X[n][2];
+                xv += pt * (X[n][0] * X[n][0] + X[n][1] * X[n][1] + X[n][2] * X[n][2]);
             }
             if (!valid) break;
-            double Np = 0.0, p1[kCoordMaxPoints], pt1[kCoordMaxPoints], mux[3] = {0, 0, 0}, muy[3] = {0, 0, 0};
-            for (int m = 0; m < Mv; ++m) { p1[m] = 0.0; for (int n = 0; n < N; ++n) p1[m] += Pm[m][n]; Np += p1[m]; }
-            for (int n = 0; n < N; ++n) { pt1[n] = 0.0; for (int m = 0; m < Mv; ++m) pt1[n] += Pm[m][n]; }
-            for (int k = 0; k < 3; ++k) {
-                for (int n = 0; n < N; ++n) mux[k] += X[n][k] * pt1[n];
-                for (int m = 0; m < Mv; ++m) muy[k] += Y[m][k] * p1[m];
-                mux[k] /= Np; muy[k] /= Np;
+            double Np = 0.0, muy[3] = {0, 0, 0};
+            for (int m = 0; m < Mv; ++m) {
+                Np += p1[m];
+                for (int k = 0; k < 3; ++k) muy[k] += Y[3 * m + k] * p1[m];
             }
-            double A[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
-            for (int m = 0; m < Mv; ++m)
-                for (int n = 0; n < N; ++n)
-                    for (int a = 0; a < 3; ++a)
-                        for (int b = 0; b < 3; ++b) A[a][b] += Pm[m][n] * (X[n][a] - mux[a]) * (Y[m][b] - muy[b]);
-            // Horn: S = A^T (S_ab = sum w y_a x_b)
+            for (int k = 0; k < 3; ++k) { muy[k] /= Np; e[k] /= Np; }          // e: mu_x in the centred frame (~1e-17)
+            xv -= Np * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+            double A[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, den = 0.0;
+            for (int m = 0; m < Mv; ++m) {
+                const double y0 = Y[3 * m] - muy[0], y1 = Y[3 * m + 1] - muy[1], y2 = Y[3 * m + 2] - muy[2];
+                den += p1[m] * (y0 * y0 + y1 * y1 + y2 * y2);
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const double qa = q[m][a] - p1[m] * e[a];
+                    A[a][0] += qa * y0; A[a][1] += qa * y1; A[a][2] += qa * y2;
+                }
+            }
+            // Horn's quaternion matrix of S = A^T (S_ab = sum w y_a x_b), expressed in the basis V
             const double Sxx = A[0][0], Sxy = A[1][0], Sxz = A[2][0], Syx = A[0][1], Syy = A[1][1], Syz = A[2][1],
                          Szx = A[0][2], Szy = A[1][2], Szz = A[2][2];
-            double Nq[4][4] = {{Sxx + Syy + Szz, Syz - Szy, Szx - Sxz, Sxy - Syx},
-                               {Syz - Szy, Sxx - Syy - Szz, Sxy + Syx, Szx + Sxz},
-                               {Szx - Sxz, Sxy + Syx, -Sxx + Syy - Szz, Syz + Szy},
-                               {Sxy - Syx, Szx + Sxz, Syz + Szy, -Sxx - Syy + Szz}};
-            double q[4];
-            coord_top_eigenvector(Nq, q);
-            const double qn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-            const double qw = q[0] / qn, qx = q[1] / qn, qy = q[2] / qn, qz = q[3] / qn;
+            const double Nq[4][4] = {{Sxx + Syy + Szz, Syz - Szy, Szx - Sxz, Sxy - Syx},
+                                     {Syz - Szy, Sxx - Syy - Szz, Sxy + Syx, Szx + Sxz},
+                                     {Szx - Sxz, Sxy + Syx, -Sxx + Syy - Szz, Syz + Szy},
+                                     {Sxy - Syx, Szx + Sxz, Syz + Szy, -Sxx - Syy + Szz}};
+            double B[4][4], Wm[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    Wm[i][j] = Nq[i][0] * V[0][j] + Nq[i][1] * V[1][j] + Nq[i][2] * V[2][j] + Nq[i][3] * V[3][j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = i; j < 4; ++j) {
+                    B[i][j] = V[0][i] * Wm[0][j] + V[1][i] * Wm[1][j] + V[2][i] * Wm[2][j] + V[3][i] * Wm[3][j];
+                    B[j][i] = B[i][j];
+                }
+            coord_jacobi(B, V);
+            int top = 0;
+#pragma unroll
+            for (int i = 1; i < 4; ++i) if (B[i][i] > B[top][top]) top = i;
+            double qw = 0, qx = 0, qy = 0, qz = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) if (i == top) { qw = V[0][i]; qx = V[1][i]; qy = V[2][i]; qz = V[3][i]; }
+            const double qn = rsqrt(qw * qw + qx * qx + qy * qy + qz * qz);
+            qw *= qn; qx *= qn; qy *= qn; qz *= qn;
             R[0] = 1 - 2 * (qy * qy + qz * qz); R[1] = 2 * (qx * qy - qz * qw); R[2] = 2 * (qx * qz + qy * qw);
             R[3] = 2 * (qx * qy + qz * qw); R[4] = 1 - 2 * (qx * qx + qz * qz); R[5] = 2 * (qy * qz - qx * qw);
             R[6] = 2 * (qx * qz - qy * qw); R[7] = 2 * (qy * qz + qx * qw); R[8] = 1 - 2 * (qx * qx + qy * qy);
-            double tr = 0.0, den = 0.0, xvar = 0.0;
-            for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) tr += A[a][b] * R[3 * a + b];
-            for (int m = 0; m < Mv; ++m)
-                for (int k = 0; k < 3; ++k) den += p1[m] * (Y[m][k] - muy[k]) * (Y[m][k] - muy[k]);
-            for (int n = 0; n < N; ++n)
-                for (int k = 0; k < 3; ++k) xvar += pt1[n] * (X[n][k] - mux[k]) * (X[n][k] - mux[k]);
+            double tr = 0.0;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) tr += A[a][0] * R[3 * a] + A[a][1] * R[3 * a + 1] + A[a][2] * R[3 * a + 2];
             sc = tr / den;
             double rm[3];
             rot_apply(R, muy, rm);
-            for (int k = 0; k < 3; ++k) t[k] = mux[k] - sc * rm[k];
-            sigma2 = (xvar - sc * tr) / (Np * 3.0);
+            for (int k = 0; k < 3; ++k) t[k] = e[k] - sc * rm[k];
+            sigma2 = (xv - sc * tr) / (Np * 3.0);
             if (!isfinite(sc) || !isfinite(t[0]) || !isfinite(t[1]) || !isfinite(t[2])) { done = 0; break; }
             ++done;
         }
@@ -467,7 +509,7 @@ coord_cpd_kernel(int P, const CoordSite* sites, int n_sites, const CoordWork* wo
             ok = false;            // the reference fails in last() of an empty sequence: evaluate's penalty
         } else {
             double acc = 0.0;
-            for (int m = 0; m < Mv; ++m) { rot_apply(R, Y[m], TY[m]); for (int k = 0; k < 3; ++k) TY[m][k] = sc * TY[m][k] + t[k]; }
+            for (int m = 0; m < Mv; ++m) { rot_apply(R, Y + 3 * m, TY[m]); for (int k = 0; k < 3; ++k) TY[m][k] = sc * TY[m][k] + t[k]; }
             for (int n = 0; n < N; ++n) {
                 double best = 1.79e308;
                 for (int m = 0; m < Mv; ++m) {
@@ -485,8 +527,8 @@ coord_cpd_kernel(int P, const CoordSite* sites, int n_sites, const CoordWork* wo
     bool all_ok = true;
     for (int r = 0; r < kCoordStarts; ++r) {
         const double v = __shfl_sync(0xffffffffu, rmsd, base + r);
-        const int o = __shfl_sync(0xffffffffu, (int)ok, base + r);
-        all_ok = all_ok && o;
+        const int o2 = __shfl_sync(0xffffffffu, (int)ok, base + r);
+        all_ok = all_ok && o2;
         if (v < best) best = v;
     }
     if (active && start == 0) {
