@@ -426,11 +426,30 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     for (int s = 0; s < R; ++s) {
         const int o = s2o[s];
         rec[s] = make_float4(fx[(size_t)o * 3], fx[(size_t)o * 3 + 1], fx[(size_t)o * 3 + 2], radius_h[o]);
-        rfl[s] = flags_h[o];
+        rfl[s] = flags_h[o] & 0x1f;
         rmax = std::max(rmax, radius_h[o]);
         if (flags_h[o] & GMM_F_SEED) sseed.push_back(rec[s]);
     }
     c->rmax_static = rmax;
+    if (c->n_seed < c->M) {
+        // Receptor atoms a mobile atom that is not a zone seed (a flexible side chain) can ever touch:
+        // the fused Contacts kernel makes them candidates without sweeping those atoms.  The ball of a
+        // side-chain atom (gmm_set_mobile) bounds where it can be; an atom the Search gene moves can be
+        // anywhere, and then every receptor atom is flagged.
+        float thr_min, thr_tight;
+        prefilter_cutoffs(c, &thr_min, &thr_tight);
+        for (int s = 0; s < R; ++s) {
+            const int o = s2o[s];
+            bool near = false;
+            for (int slot = c->n_seed; slot < c->M && !near; ++slot) {
+                const float4 b = c->h_ball[slot];
+                if (b.w > 1.0e30f) { near = true; break; }
+                const double dx = xyz_h[(size_t)o * 3] - b.x, dy = xyz_h[(size_t)o * 3 + 1] - b.y, dz = xyz_h[(size_t)o * 3 + 2] - b.z;
+                near = std::sqrt(dx * dx + dy * dy + dz * dz) - b.w <= (double)radius_h[o] + c->h_mrad[slot] - thr_min + 0.05;
+            }
+            if (near) rfl[s] |= (uint8_t)kRflagNearFlex;
+        }
+    }
     for (int t = 0; t < c->n_tiles; ++t) {
         float* b = &box[(size_t)t * 8];
         b[0] = b[1] = b[2] = 3e38f; b[3] = b[4] = b[5] = -3e38f; b[6] = 0.f; b[7] = 0.f;

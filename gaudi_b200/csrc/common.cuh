@@ -50,6 +50,7 @@ constexpr int kCandQ = 256;          // per-warp candidate queue entries
 constexpr int kPairQ = 128;          // per-warp pair queue entries
 constexpr double kFxScale = 4294967296.0;  // 2^32 fixed-point scale of score sums
 constexpr float kFar = 1.0e15f;      // coordinate of padding atoms
+constexpr unsigned kRflagNearFlex = 128;   // internal bit of d_rflags: the atom is within contact reach of where a non-seed mobile atom can be
 
 // Contacts settings (gaudi/objectives/contacts.py:101-121,142-145), device copy.
 struct Params {

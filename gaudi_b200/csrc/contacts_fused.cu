@@ -483,7 +483,11 @@ contacts_fused_kernel(const FusedArgs f) {
                 nr[k] = fmaf(z, z, fmaf(y, y, x * x));
                 // candidate reach of this atom: its radius minus the overlap cutoff it can reach at
                 // all (an atom that is not hydrophobic only takes part in clashes)
-                rw[k] = r.w - ((a.rflags[stv[k] * kSubTile + lane] & GMM_F_HYDROPHOBIC) ? a.thr_min : a.thr_tight);
+                const unsigned rf = a.rflags[stv[k] * kSubTile + lane];
+                rw[k] = r.w - ((rf & GMM_F_HYDROPHOBIC) ? a.thr_min : a.thr_tight);
+                // within reach of where a mobile atom that is not a zone seed (a flexible side chain) can
+                // ever be, decided once per receptor (kRflagNearFlex): rides on the sign of rw
+                if (!PLAIN && (rf & kRflagNearFlex)) rw[k] = -rw[k];
                 ms[k] = 3e38f;
                 swept_leaves += (stv[k] < (uint32_t)f.NST) ? 1 : 0;
             }
@@ -525,23 +529,6 @@ contacts_fused_kernel(const FusedArgs f) {
                 if (!PLAIN && a.n_sseed > 0) near = near || ((zone[stv[0]] | zone[stv[1]] | zone[stv[2]] | zone[stv[3]]) != 0u);
                 if (!__any_sync(0xffffffffu, near)) continue;
             }
-            float ma[4] = {ms[0], ms[1], ms[2], ms[3]};
-            if (!PLAIN) {
-#pragma unroll 2
-            for (s = a.n_seed; s + 1 < a.M; s += 2) {      // mobile atoms that are not zone seeds
-                const float4 m = ligc[s], q = ligc[s + 1];
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    ma[k] = fminf(ma[k], fminf(fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))),
-                                               fmaf(ax[k], q.x, fmaf(ay[k], q.y, fmaf(az[k], q.z, q.w)))));
-            }
-            if (s < a.M) {
-                const float4 m = ligc[s];
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    ma[k] = fminf(ma[k], fmaf(ax[k], m.x, fmaf(ay[k], m.y, fmaf(az[k], m.z, m.w))));
-            }
-            }
             bool in[4], band[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -571,8 +558,11 @@ contacts_fused_kernel(const FusedArgs f) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float margin = 2e-4f + 1e-6f * (nr[k] + wmax);
-                const float c = rw[k] + a.rmax_mobile;
-                const bool cand = in[k] && (ma[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin);
+                // candidate: in the zone and within contact reach of a seed, or flagged as within reach of
+                // a side chain's range of motion (no sweep over the non-seed atoms: the expansion's
+                // pre-filter sorts those out)
+                const float c = (PLAIN ? rw[k] : fabsf(rw[k])) + a.rmax_mobile;
+                const bool cand = in[k] && ((ms[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin) || (!PLAIN && rw[k] < 0.f));
                 const unsigned zb = __ballot_sync(0xffffffffu, in[k]);
                 const unsigned cb = __ballot_sync(0xffffffffu, cand);
                 __syncwarp();
@@ -658,7 +648,7 @@ contacts_fused_kernel(const FusedArgs f) {
         team_sync<S>();
         cfx = accs[0]; hfx = accs[1]; nc = accs[2]; nh = accs[3];
     }
-    if (f.count_tests && lane == 0 && swept_leaves) atomicAdd(a.counters, (unsigned long long)swept_leaves * kSubTile * a.M);
+    if (f.count_tests && lane == 0 && swept_leaves) atomicAdd(a.counters, (unsigned long long)swept_leaves * kSubTile * (PLAIN ? a.M : a.n_seed));
     if (tlane == 0) {
         if (f.count_tests && f.n_mm) atomicAdd(a.counters, (unsigned long long)f.n_mm);
         double clash = 2.0 * ((double)cfx / kFxScale);          // contacts.py:176-177
