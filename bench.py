@@ -675,6 +675,31 @@ def bench_dense_and_c2(ctx, state):
     return res
 
 
+def bench_coordination(ctx):
+    """N = 1 only: the Coordination objective on the reference's own test complex
+    (tests/golden/4c3w_mol2.npz: vanadium site, octahedral template), 65,536 poses of the metal complex
+    near the crystal pose; device-resident coordinates in, scores out.  CPU leg: the numpy oracle on a sample."""
+    import time
+    torch = ctx.torch
+    import oracle_adapter as OA
+    import test_gpu_coordination as TC
+    mol, site, g, eng, mob = TC.complex_engine()
+    pop = 65536
+    xyz = eng.express(np.zeros((pop, 0)), TC.poses(mob, pop, seed=7))
+    ms = float(np.mean(ctx.time_steps(lambda: eng.coordination(xyz), 10, warmup=3)))
+    out = {"metric": "individuals scored/sec (Coordination objective)", "value": pop / (ms * 1e-3), "unit": "individuals/s",
+           "ms_per_step": ms, "config": {"workload": "4c3w vanadium site, octahedron, radius 3.0, %d poses" % pop,
+                                         "kernels": "coord_sphere_kernel + coord_cpd_kernel, fp64"}}
+    x64 = xyz[:200].cpu().numpy().astype(np.float64) + eng.centre
+    t0 = time.perf_counter()
+    for p in range(200):
+        OA.coordination(site, OA.coordination_world(site, x64[p]))
+    out["cpu_baseline"] = {"value": 200 / (time.perf_counter() - t0), "unit": "individuals/s", "cores": 1, "kind": "port",
+                           "sample": "200 poses, numpy restatement (oracle/coordination_oracle.py)"}
+    eng.close()
+    return out
+
+
 def run_b200(args):
     ctx = Ctx(args)
     out, state = bench_c3(ctx)
@@ -692,6 +717,11 @@ def run_b200(args):
                 out.update(bench_dense_and_c2(ctx, state))
             except Exception as exc:
                 out["dense"] = {"error": repr(exc)[:300]}
+            if not args.no_cpu:
+                try:
+                    out["coordination"] = bench_coordination(ctx)
+                except Exception as exc:
+                    out["coordination"] = {"error": repr(exc)[:300]}
     if first and not args.no_cpu:
         co = c_oracle_module().COracle(state["lig"], state["rec"], state["params"])
         n = min(args.cpu_sample, len(state["tors"]))

@@ -54,7 +54,7 @@ def phases():
              ("kernel_head", find("contacts_fused_kernel(const FusedArgs f)")), ("stage", find("---- 0. stage")),
              ("cull", find("---- 1. surviving")), ("refine", find("Refine: a leaf stays only")),
              ("sweep_prep", find("---- 2. sweep")), ("sweep_loop", find("two mobile atoms per step")),
-             ("post_sweep", find("float ma[4]")), ("static_pairs", find("---- 3. static-static")),
+             ("post_sweep", find("bool in[4], band[4];")), ("static_pairs", find("---- 3. static-static")),
              ("intra_mobile", find("---- 4. pairs inside")), ("finish", find("---- 5. finish")), ("end", len(src) + 1)]
     return [(marks[i][1], marks[i + 1][1] - 1, marks[i][0]) for i in range(len(marks) - 1)]
 
