@@ -110,7 +110,7 @@ int gmm_destroy(gmm_ctx* c) {
     release(c->d_rr_ptr); release(c->d_rr_idx); release(c->d_rr_val); release(c->d_rr_kind);
     release(c->d_edge); release(c->d_sub_box); release(c->d_geo_terms);
     if (c->d_rmsd_ws) { cudaFree(c->d_rmsd_ws); c->d_rmsd_ws = nullptr; c->rmsd_ws_bytes = 0; }
-    release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx);
+    release(c->d_sseed); release(c->d_ms_ptr); release(c->d_ms_idx); release(c->d_flex_mask); release(c->d_body_range);
     release(c->d_counters);
     if (c->d_scratch) cudaFree(c->d_scratch);
     if (c->d_stage) cudaFree(c->d_stage);
@@ -431,23 +431,50 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
         if (flags_h[o] & GMM_F_SEED) sseed.push_back(rec[s]);
     }
     c->rmax_static = rmax;
+    c->n_bodies = 0;
+    std::vector<uint32_t> flex_mask, body_range;
     if (c->n_seed < c->M) {
         // Receptor atoms a mobile atom that is not a zone seed (a flexible side chain) can ever touch:
         // the fused Contacts kernel makes them candidates without sweeping those atoms.  The ball of a
         // side-chain atom (gmm_set_mobile) bounds where it can be; an atom the Search gene moves can be
-        // anywhere, and then every receptor atom is flagged.
+        // anywhere, and then every receptor atom is within its reach.  Non-seed slots are grouped into
+        // bodies — runs of consecutive slots that share the pivot of their ball (one side chain), at most
+        // 32 slots and at most 32 bodies (beyond that: plain runs of 32 slots) — and every receptor atom
+        // gets the mask of the bodies it is within reach of; the expansion skips the other bodies' slots.
         float thr_min, thr_tight;
         prefilter_cutoffs(c, &thr_min, &thr_tight);
+        auto same_pivot = [&](int s, int t) {
+            const float4 a = c->h_ball[s], b = c->h_ball[t];
+            return a.x == b.x && a.y == b.y && a.z == b.z && (a.w > 1.0e30f) == (b.w > 1.0e30f);
+        };
+        for (int pass = 0; pass < 2; ++pass) {
+            body_range.clear();
+            int lo = c->n_seed;
+            for (int slot = c->n_seed + 1; slot <= c->M; ++slot)
+                if (slot == c->M || slot - lo >= 32 || (pass == 0 && !same_pivot(slot, lo))) {
+                    body_range.push_back((uint32_t)lo | ((uint32_t)slot << 16));
+                    lo = slot;
+                }
+            if (body_range.size() <= 32) break;
+        }
+        c->n_bodies = (int)body_range.size();
+        flex_mask.assign((size_t)c->Rpad + kSubTile, 0u);
         for (int s = 0; s < R; ++s) {
             const int o = s2o[s];
-            bool near = false;
-            for (int slot = c->n_seed; slot < c->M && !near; ++slot) {
-                const float4 b = c->h_ball[slot];
-                if (b.w > 1.0e30f) { near = true; break; }
-                const double dx = xyz_h[(size_t)o * 3] - b.x, dy = xyz_h[(size_t)o * 3 + 1] - b.y, dz = xyz_h[(size_t)o * 3 + 2] - b.z;
-                near = std::sqrt(dx * dx + dy * dy + dz * dz) - b.w <= (double)radius_h[o] + c->h_mrad[slot] - thr_min + 0.05;
+            uint32_t mask = 0;
+            for (int b = 0; b < c->n_bodies; ++b) {
+                bool near = false;
+                for (int slot = (int)(body_range[b] & 0xffff); slot < (int)(body_range[b] >> 16) && !near; ++slot) {
+                    const float4 ball = c->h_ball[slot];
+                    if (ball.w > 1.0e30f) { near = true; break; }
+                    const double dx = xyz_h[(size_t)o * 3] - ball.x, dy = xyz_h[(size_t)o * 3 + 1] - ball.y,
+                                 dz = xyz_h[(size_t)o * 3 + 2] - ball.z;
+                    near = std::sqrt(dx * dx + dy * dy + dz * dz) - ball.w <= (double)radius_h[o] + c->h_mrad[slot] - thr_min + 0.05;
+                }
+                if (near) mask |= 1u << b;
             }
-            if (near) rfl[s] |= (uint8_t)kRflagNearFlex;
+            flex_mask[s] = mask;
+            if (mask) rfl[s] |= (uint8_t)kRflagNearFlex;
         }
     }
     for (int t = 0; t < c->n_tiles; ++t) {
@@ -479,6 +506,8 @@ int gmm_set_receptor(gmm_ctx* c, int R, const double* xyz_h, const float* radius
     if ((rc = upload(&c->d_sub_box, sbox.data(), sbox.size()))) return rc;
     if ((rc = upload(&c->d_rec4, rec.data(), rec.size()))) return rc;
     if ((rc = upload(&c->d_rflags, rfl.data(), rfl.size()))) return rc;
+    if ((rc = upload(&c->d_flex_mask, flex_mask.data(), flex_mask.size()))) return rc;
+    if ((rc = upload(&c->d_body_range, body_range.data(), body_range.size()))) return rc;
     if ((rc = upload(&c->d_tile_box, box.data(), box.size()))) return rc;
     c->n_sseed = (int)sseed.size();
     if ((rc = upload(&c->d_sseed, sseed.data(), sseed.size()))) return rc;

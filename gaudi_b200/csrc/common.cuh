@@ -200,6 +200,7 @@ struct gmm_ctx {
                                      //         (clash or hydrophobic, never both) as int64 fixed point (fused kernel)
     float* d_sub_box = nullptr;      // [Rpad/32 + 1, 8] sub-tile boxes (last = dummy leaf)
     int rr_nnz = 0;
+    uint32_t* d_flex_mask = nullptr; uint32_t* d_body_range = nullptr; int n_bodies = 0;   // see SweepArgs
     float4* d_sseed = nullptr; int n_sseed = 0;                  // static zone seeds (CB atoms)
     int32_t* d_ms_ptr = nullptr; int32_t* d_ms_idx = nullptr;   // CSR over slots -> sorted static idx
     int ms_nnz = 0;

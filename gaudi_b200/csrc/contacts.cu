@@ -489,6 +489,7 @@ void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a) {
     a.xyz = xyz; a.slot2atom = c->d_slot2atom; a.mrad = c->d_mrad_slot; a.mflags = c->d_mflags_slot;
     a.rec4 = c->d_rec4; a.rflags = c->d_rflags; a.tile_box = c->d_tile_box; a.always = c->d_always;
     a.ms_ptr = c->ms_nnz ? c->d_ms_ptr : nullptr; a.ms_idx = c->d_ms_idx;
+    a.flex_mask = c->d_flex_mask; a.body_range = c->d_body_range; a.n_bodies = c->n_bodies;
     a.counters = c->d_counters;
     a.prm = c->prm;
     a.rad2 = (float)(c->prm.zone_radius * c->prm.zone_radius);

@@ -12,6 +12,9 @@ struct SweepArgs {
     const float4* rec4; const uint8_t* rflags; const float* tile_box; const uint32_t* always;
     const float4* sseed;
     const int32_t* ms_ptr; const int32_t* ms_idx;
+    // flexible side chains (fused kernel): runs of non-seed slots that move together ("bodies", lo | hi << 16,
+    // at most 32 slots each) and per receptor atom the bodies whose range of motion it is within reach of
+    const uint32_t* flex_mask; const uint32_t* body_range; int n_bodies;
     uint32_t* zone; long long* partial; unsigned long long* counters;
     Params prm;
     float rad2, thr_min, thr_tight, rmax_mobile, reach_extra;

@@ -110,9 +110,15 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
     for (int base = 0; base < ncq; base += 32) {
         const int e = base + lane;
         int j = 0;
+        unsigned near_seed = 0, bodies = 0;
         float ax = 0.f, ay = 0.f, az = 0.f, cr_h = 0.f, cr_c = 0.f, slack = -3e38f;   // idle lane: nothing passes
         if (e < ncq) {
             j = (int)cq[e];
+            if (!PLAIN) {
+                near_seed = (unsigned)j >> 31;          // set by the sweep: within contact reach of a zone seed
+                j &= 0x3fffff;
+                bodies = a.n_bodies ? a.flex_mask[j] : 0u;      // no non-seed atoms: no table
+            }
             const float4 r = a.rec4[j];
             const bool rh = (a.rflags[j] & GMM_F_HYDROPHOBIC) != 0;
             const float x = r.x - sph.x, y = r.y - sph.y, z = r.z - sph.z;
@@ -122,8 +128,27 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
             cr_h = rh ? r.w - a.thr_min : cr_c;          // partner that can (if this atom can)
             slack = 2e-4f + 2e-6f * (nr + sph.w) - nr;   // error bound of the form, minus n
         }
-        for (int s0 = 0; s0 < a.M; s0 += 32) {
-            const int n = min(32, a.M - s0);
+        // PLAIN: every slot, in chunks of 32.  Otherwise: the seed slots in chunks of 32 if some
+        // candidate of this batch is near a seed, then only the bodies (side chains) some candidate
+        // is within reach of — a batch comes from one or two leaves, i.e. from one corner of the zone.
+        const unsigned any_seed = PLAIN ? 1u : __ballot_sync(0xffffffffu, near_seed != 0u);
+        const unsigned any_body = PLAIN ? 0u : __reduce_or_sync(0xffffffffu, bodies);
+        const int n_schunks = ((PLAIN ? a.M : a.n_seed) + 31) >> 5;
+        for (int c = 0; c < n_schunks + (PLAIN ? 0 : a.n_bodies); ++c) {
+            int s0, n;
+            unsigned zbits = 0xffffffffu;
+            if (PLAIN || c < n_schunks) {
+                if (!PLAIN && !any_seed) continue;
+                s0 = c << 5;
+                n = min(32, (PLAIN ? a.M : a.n_seed) - s0);
+                if (!PLAIN) zbits = zm[c];
+            } else {
+                if (!((any_body >> (c - n_schunks)) & 1u)) continue;
+                const uint32_t br = a.body_range[c - n_schunks];
+                s0 = (int)(br & 0xffffu);
+                n = (int)(br >> 16) - s0;
+                zbits = __funnelshift_r(zm[s0 >> 5], zm[(s0 >> 5) + 1], s0 & 31);   // zm has one spare word
+            }
             unsigned hits = 0;
             // slots [0, n_hseed) are hydrophobic seeds, [n_hseed, n_seed) the other seeds; mobile
             // atoms that are not seeds (flexible side chains) are not sorted and keep the wide cutoff
@@ -135,7 +160,7 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
                 const float dot = fmaf(ax, m.x, fmaf(ay, m.y, fmaf(az, m.z, m.w)));
                 if (dot <= fmaf(t * 1.000004f, t, slack)) hits |= 1u << k;
             }
-            if (!PLAIN) hits &= zm[s0 >> 5];
+            if (!PLAIN) hits &= zbits;
             unsigned live = __ballot_sync(0xffffffffu, hits != 0u);
             while (live) {
                 if (hits) {
@@ -259,7 +284,7 @@ contacts_fused_kernel(const FusedArgs f) {
         }
     }
     if (tlane < 4) accs[tlane] = 0;
-    if (tlane == 0) nlist_p[0] = 0;
+    if (tlane == 0) { nlist_p[0] = 0; if (!PLAIN) zm[a.MW] = 0u; }
     team_sync<S>();
     const bool internal = a.prm.options & GMM_OPT_ONLY_INTERNAL;
     // mobile atoms in the zone: seeds always, the others (flexible side chains) iff within radius
@@ -562,13 +587,15 @@ contacts_fused_kernel(const FusedArgs f) {
                 // a side chain's range of motion (no sweep over the non-seed atoms: the expansion's
                 // pre-filter sorts those out)
                 const float c = (PLAIN ? rw[k] : fabsf(rw[k])) + a.rmax_mobile;
-                const bool cand = in[k] && ((ms[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin) || (!PLAIN && rw[k] < 0.f));
+                const bool near_seed = ms[k] + nr[k] <= c * c * 1.000004f + 1e-6f + margin;
+                const bool cand = in[k] && (near_seed || (!PLAIN && rw[k] < 0.f));
                 const unsigned zb = __ballot_sync(0xffffffffu, in[k]);
                 const unsigned cb = __ballot_sync(0xffffffffu, cand);
                 __syncwarp();
                 if (lane == 0 && stv[k] < (uint32_t)f.NST) zone[stv[k]] = zb;
                 if (cb) {
-                    if (cand) cq[ncq + __popc(cb & ((1u << lane) - 1u))] = stv[k] * kSubTile + lane;
+                    if (cand) cq[ncq + __popc(cb & ((1u << lane) - 1u))] =
+                        (stv[k] * kSubTile + lane) | ((!PLAIN && near_seed) ? 0x80000000u : 0u);
                     ncq += __popc(cb);
                 }
             }
@@ -680,7 +707,7 @@ void fill_sweep_args(const gmm_ctx* c, int P, const float* xyz, SweepArgs& a);
 static size_t fused_ind_bytes(const gmm_ctx* c) {
     const int NST = c->Rpad / kSubTile, MW = (c->Mp + 31) / 32;
     size_t ind = (size_t)2 * c->Mp * sizeof(float4) + 3 * sizeof(float4) + 4 * sizeof(long long) + 4 * sizeof(int) +
-                 (size_t)(NST + 4) * 2 + (size_t)(NST + 1) * 4 + (size_t)MW * 4;
+                 (size_t)(NST + 4) * 2 + (size_t)(NST + 1) * 4 + (size_t)(MW + 1) * 4;     // zm: one spare word
     return (ind + 15) / 16 * 16;
 }
 static const size_t kFusedQueues = (size_t)4 * (kFCandQ + kPairQ) * sizeof(uint32_t);
