@@ -434,6 +434,9 @@ class BatchEvaluator(object):
                 raw[:, i] = scores[:, col]
         if self.coordination:
             crd = self.engines[0][0].coordination(xyz).cpu().numpy()
+            if np.isnan(crd).any():
+                raise RuntimeError("Coordination: more than 192 atoms within the radius of a probe "
+                                   "(gmm_coordination's per-individual limit); reduce `radius`")
             for col, (i, o) in enumerate(self.coordination):
                 raw[:, i] = crd[:, col]
         if self.geometry:
