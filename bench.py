@@ -498,7 +498,7 @@ def bench_rmsd(ctx, state, cpu=False):
     sim = parallel.ShardedSimilarity(eng, counts, RMSD_A, threshold=RMSD_THR)
 
     def step():
-        res["lists"] = sim.step(mine)
+        res["lists"] = sim.step(mine, root_only=True)      # the niching pass that reads them runs on rank 0
 
     l0 = launch_count()
     ms = ctx.time_steps(step, 10, warmup=3)
@@ -528,7 +528,8 @@ def bench_rmsd(ctx, state, cpu=False):
                "n_gpus": ctx.world, "ms_per_step": step_ms, "scaling": "strong",
                "config": {"workload": RMSD_TEXT,
                           "step": ("all-gather of conformers (NCCL) + row-block bitmask + partner-list compaction + all-gather "
-                                   "of the packed lists + copy to the host (parallel.ShardedSimilarity)") if ctx.world > 1
+                                   "of the packed lists + copy of the counts, then of the entries, to rank 0's host memory "
+                                   "(parallel.ShardedSimilarity, root_only)") if ctx.world > 1
                                   else "bitmask + partner-list compaction + copy of the lists to the host",
                           "l2": "192 MiB buffer written between timed iterations"},
                "partner_entries": int(idx.shape[0]),
@@ -582,14 +583,14 @@ def rmsd_large(ctx, eng, n=131072):
     res = {}
 
     def step():
-        res["lists"] = sim.step(mine)
+        res["lists"] = sim.step(mine, root_only=True)
     ms = ctx.time_steps(step, 3, warmup=2)
     ptr, idx = res["lists"]
     step_ms = float(np.mean(ms))
     del sim
     torch.cuda.empty_cache()
     return {"n_conformers": n, "value": (n * (n - 1) // 2) / (step_ms * 1e-3), "unit": "unique pairs/s",
-            "ms_per_step": step_ms, "partner_entries": int(len(idx)), "n_gpus": ctx.world}
+            "ms_per_step": step_ms, "partner_entries": int(len(idx)) if idx is not None else None, "n_gpus": ctx.world}
 
 
 def bench_c5(ctx, state, cpu=False):

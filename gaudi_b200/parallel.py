@@ -152,9 +152,12 @@ def sharded_similar_lists(engine, coords, counts, threshold=2.5, group=None):
 
 class ShardedSimilarity(object):
     """``sharded_similar_lists`` for a generational loop: every buffer is allocated once, a step is
-    two collectives (conformers in, packed partner lists out), nine kernel launches and ONE
-    host synchronisation, and the partner lists arrive as HOST arrays on every rank (the greedy
-    niching pass that consumes them, gaudi/algorithms.py:139-155, runs on the host).
+    two collectives (conformers in, packed partner lists out), nine kernel launches and two host
+    synchronisations (the per-row counts first, then exactly the entries they announce, copied
+    straight to their final place in one page-locked array), and the partner lists arrive as HOST
+    arrays (the greedy niching pass that consumes them, gaudi/algorithms.py:139-155, runs on the
+    host) — on every rank, or with ``root_only`` on rank 0 alone.  The arrays returned are views of
+    buffers the next ``step`` reuses.
 
     ``counts[r]`` conformers of ``atoms`` atoms live on rank r.  ``cap``: room for partner entries per
     rank (default 8 per row: the whole packed buffer crosses PCIe every step, so it is kept small); a
@@ -183,11 +186,13 @@ class ShardedSimilarity(object):
         self.cap = cap
         self.packed = torch.zeros(self.m + cap, dtype=torch.int32, device=dev)      # [per-row counts | entries]
         self.gathered = torch.empty(self.world * (self.m + cap), dtype=torch.int32, device=dev)
-        self.host = torch.empty(self.world * (self.m + cap), dtype=torch.int32).pin_memory()
+        self.host_counts = torch.empty((self.world, self.m), dtype=torch.int32).pin_memory()
+        self.host_idx = torch.empty(self.world * cap, dtype=torch.int32).pin_memory()
 
-    def step(self, coords):
+    def step(self, coords, root_only=False):
         """``coords``: this rank's ``(counts[rank], atoms, 3)`` float32 device block.  Returns host
-        ``(ptr int64 (N + 1,), idx int32)`` for all N conformers."""
+        ``(ptr int64 (N + 1,), idx int32)`` for all N conformers; with ``root_only`` the ranks other
+        than 0 return ``(None, None)`` and skip the copy of the entries."""
         import ctypes as C
         from . import _lib
         eng, np = self.engine, self._np
@@ -215,24 +220,32 @@ class ShardedSimilarity(object):
                                        C.c_void_p(self.packed.data_ptr() + 4 * self.m), self.cap, stream))
         if self.world > 1:
             _all_gather_into(self.gathered, self.packed, self.group)
-            self.host.copy_(self.gathered, non_blocking=True)
-        else:
-            self.host.copy_(self.packed, non_blocking=True)
-        torch.cuda.current_stream(eng.torch_device).synchronize()
-        host = self.host.numpy().reshape(self.world, self.m + self.cap)
-        per_row = [host[r, :self.counts[r]] for r in range(self.world)]
+        rows = (self.gathered if self.world > 1 else self.packed).view(self.world, self.m + self.cap)
+        self.host_counts.copy_(rows[:, :self.m], non_blocking=True)
+        stream_t = torch.cuda.current_stream(eng.torch_device)
+        stream_t.synchronize()
+        counts_h = self.host_counts.numpy()
+        per_row = [counts_h[r, :self.counts[r]] for r in range(self.world)]
         totals = [int(c.sum()) for c in per_row]
-        if max(totals) > self.cap:
+        if max(totals) > self.cap:                            # every rank sees the same counts and retries
             self._alloc(2 * max(totals))
-            return self.step(coords)
-        if self.cap > 4 * max(max(totals), self.m):          # far too roomy: every step pays for it on PCIe
-            self._shrink_to = 2 * max(max(totals), self.m)
-        ptr = np.zeros(self.n + 1, np.int64)
-        np.cumsum(np.concatenate(per_row), out=ptr[1:])
-        idx = np.concatenate([host[r, self.m:self.m + totals[r]] for r in range(self.world)])
-        if getattr(self, "_shrink_to", None):                 # (after the results have left the old buffer)
-            self._alloc(self._shrink_to)
-            self._shrink_to = None
+            return self.step(coords, root_only)
+        shrink = self.cap > 4 * max(max(totals), self.m)      # far too roomy: the all-gather pays for it
+        ptr = idx = None
+        if not (root_only and self.rank != 0):
+            at = 0
+            for r in range(self.world):
+                if totals[r]:
+                    self.host_idx[at:at + totals[r]].copy_(rows[r, self.m:self.m + totals[r]], non_blocking=True)
+                at += totals[r]
+            ptr = np.zeros(self.n + 1, np.int64)
+            np.cumsum(np.concatenate(per_row), out=ptr[1:])
+            stream_t.synchronize()
+            idx = self.host_idx.numpy()[:at]
+        if shrink:
+            if idx is not None:
+                idx = idx.copy()                              # (the results leave the old buffer first)
+            self._alloc(2 * max(max(totals), self.m))
         return ptr, idx
 
 
