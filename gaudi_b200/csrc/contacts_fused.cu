@@ -48,6 +48,16 @@ constexpr int kFCandQ = 192;
 
 struct Acc { long long cfx, hfx; int nc, nh; };
 
+// Warps per CTA.  A team of four needs its four.  The warp-per-individual PLAIN variants run ONE warp
+// per CTA: with `warp`, `team` and every per-warp shared-memory offset compile-time zeros the kernel
+// drops to 63 registers without a spill and the 65,536-individual step is 4 % faster (8,192: 7 %);
+// the gain is the code, not the scheduling granularity — the same kernel compiled for four warps and
+// launched with one is slower than either.  The variants with flexible side
+// chains stay at four warps: built for one they hit an illegal address in the candidate expansion on
+// configs[4] that no bounds check of ours explains (the same source with printf-carrying checks, or
+// compiled for four warps, is clean), so that build is not used.
+__host__ __device__ constexpr int fused_warps(int S, bool plain) { return (S == 1 && plain) ? 1 : 4; }
+
 // Warp reductions on the REDUX unit (one instruction per 32-bit word) instead of five rounds of
 // shuffles: floats through the usual order-preserving map to unsigned integers, 64-bit sums in
 // three pieces of at most 24 bits so that 32 lanes cannot overflow a word.
@@ -187,10 +197,10 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
 // the mobile set: the mobile-zone bits, the always-in-zone words, the non-seed sweep and the
 // exclusion lookups are compiled out.
 template <int S, bool CULL, bool PLAIN>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(fused_warps(S, PLAIN) * 32, 32 / fused_warps(S, PLAIN))
 contacts_fused_kernel(const FusedArgs f) {
     const SweepArgs& a = f.s;
-    constexpr int IPC = 4 / S;            // individuals per CTA
+    constexpr int IPC = fused_warps(S, PLAIN) / S;            // individuals per CTA
     constexpr int TL = 32 * S;            // lanes per team
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -751,7 +761,8 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     int S = (P >= kTeamSwitch) ? 1 : 4;
     if (S == 1 && 4 * ind + queues > limit) S = 4;
     if (ind + queues > limit) return GMM_OK;    // not handled
-    const size_t smem = (S == 1 ? 4 : 1) * ind + queues;
+    const int warps = fused_warps(S, plain);
+    const size_t smem = (size_t)(warps / S) * ind + queues * warps / 4;
     if (c->prof) GMM_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), s));   // the pair-test tally
     const bool cull = f.s.cull != 0;
     void (*const variants[8])(const FusedArgs) = {
@@ -762,7 +773,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     void (*kernel)(const FusedArgs) = variants[(S == 1 ? 0 : 4) + (cull ? 2 : 0) + (plain ? 1 : 0)];
     { const int rc = allow_dynamic_smem((const void*)kernel, c->device, limit); if (rc) return rc; }
     if (c->prof) GMM_CUDA(cudaEventRecord(c->ev[2], s));
-    kernel<<<S == 1 ? (P + 3) / 4 : P, 128, smem, s>>>(f);
+    kernel<<<(P + warps / S - 1) / (warps / S), warps * 32, smem, s>>>(f);
     GMM_LAUNCH_CHECK("contacts_fused_kernel");
     if (c->prof) { GMM_CUDA(cudaEventRecord(c->ev[3], s)); c->ev_used[1] = true; c->ev_used[2] = false; }
     c->pub_done = f.mirror != nullptr;
