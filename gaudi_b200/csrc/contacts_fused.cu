@@ -53,9 +53,11 @@ struct Acc { long long cfx, hfx; int nc, nh; };
 // drops to 63 registers without a spill and the 65,536-individual step is 4 % faster (8,192: 7 %);
 // the gain is the code, not the scheduling granularity — the same kernel compiled for four warps and
 // launched with one is slower than either.  The variants with flexible side
-// chains stay at four warps: built for one they hit an illegal address in the candidate expansion on
-// configs[4] that no bounds check of ours explains (the same source with printf-carrying checks, or
-// compiled for four warps, is clean), so that build is not used.
+// chains stay at four warps: one warp per CTA costs them occupancy (22 resident warps instead of 24 on
+// configs[4]: 5.92 ms against 5.75).  Built for one warp they also hit an illegal address in the
+// candidate expansion on configs[4] for as long as the OR over the lanes' body masks was a
+// __reduce_or_sync (REDUX); with a shuffle butterfly in its place the build is clean — cause not found,
+// the shuffles stay.
 __host__ __device__ constexpr int fused_warps(int S, bool plain) { return (S == 1 && plain) ? 1 : 4; }
 
 // Warp reductions on the REDUX unit (one instruction per 32-bit word) instead of five rounds of
@@ -142,7 +144,14 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
         // candidate of this batch is near a seed, then only the bodies (side chains) some candidate
         // is within reach of — a batch comes from one or two leaves, i.e. from one corner of the zone.
         const unsigned any_seed = PLAIN ? 1u : __ballot_sync(0xffffffffu, near_seed != 0u);
-        const unsigned any_body = PLAIN ? 0u : __reduce_or_sync(0xffffffffu, bodies);
+        // (a butterfly of shuffles, not __reduce_or_sync: built for one warp per CTA, the variant with the
+        // REDUX here faulted on configs[4] and the one with the shuffles does not — see fused_warps)
+        unsigned any_body = 0u;
+        if (!PLAIN) {
+            any_body = bodies;
+#pragma unroll
+            for (int sh = 16; sh > 0; sh >>= 1) any_body |= __shfl_xor_sync(0xffffffffu, any_body, sh);
+        }
         const int n_schunks = ((PLAIN ? a.M : a.n_seed) + 31) >> 5;
         for (int c = 0; c < n_schunks + (PLAIN ? 0 : a.n_bodies); ++c) {
             int s0, n;
