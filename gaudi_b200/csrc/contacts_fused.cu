@@ -540,7 +540,7 @@ contacts_fused_kernel(const FusedArgs f) {
             // two mobile atoms per step: 6 FFMA + one 3-input FMNMX3 per receptor atom
             int s = 0;
             if (CULL) {
-#pragma unroll 4
+#pragma unroll 2
                 for (; s + 1 < a.n_seed; s += 2) {
                     const float4 m = ligc[s], q = ligc[s + 1];
 #pragma unroll
