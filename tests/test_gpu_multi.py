@@ -94,6 +94,12 @@ def _exchange_worker(rank, world, port, out):
     for _ in range(2):
         ptr2, idx2 = sim.step(mine)
         results["lists_prealloc"] = bool(np.array_equal(ptr2, ptr1) and np.array_equal(idx2, idx1)) and results.get("lists_prealloc", True)
+    # the lists on rank 0 alone (where the niching pass runs): the other ranks skip the copy of the entries
+    ptr3, idx3 = sim.step(mine, root_only=True)
+    if rank == 0:
+        results["lists_root_only"] = bool(np.array_equal(ptr3, ptr1) and np.array_equal(idx3, idx1))
+    else:
+        assert ptr3 is None and idx3 is None
     dist.barrier()
     # host-resident population: shared page-locked table, each rank uploads and downloads its rows
     hs = parallel.HostShardedEvaluator(eng, 6000, want_xyz=True)
