@@ -537,7 +537,9 @@ def bench_rmsd(ctx, state, cpu=False):
                "bitmask_bytes": RMSD_N * ((RMSD_N + 31) // 32) * 4,
                "roofline": {"bound": "tensor", "kernel": "rmsd_bits kernel", "achieved": ach_t, "peak": peak_t,
                             "unit": "TFLOP/s", "frac": ach_t / peak_t, "peak_source": src, "flops_per_pair": 2 * kp,
-                            "kernel_ms": kernel_ms, "pairs_computed_per_rank": computed // ctx.world, "traffic": None,
+                            "kernel_ms": kernel_ms, "pairs_computed_per_rank": computed // ctx.world,
+                            "traffic": committed_dram_traffic("rmsd_bits_tc")[0] if ctx.world == 1 else None,
+                            "traffic_source": committed_dram_traffic("rmsd_bits_tc")[1] if ctx.world == 1 else None,
                             "note": "MMA flops of the pairs this rank's tiles compute over the kernel's own duration "
                                     "(centring kernels included); the product is a pre-filter, pairs inside its error "
                                     "bound are re-decided by the exact f32 sum (bits identical to the FP32 kernel)"},
@@ -635,7 +637,9 @@ def bench_c5(ctx, state, cpu=False):
                "roofline": {"bound": "fp32", "kernel": "contacts_fused_kernel", "achieved": ach, "peak": state["peak32"],
                             "unit": "TFLOP/s", "frac": ach / state["peak32"], "kernel_ms": kernel_ms,
                             "express_ms": float(np.mean(em)), "pair_tests_per_launch": tests,
-                            "flops_per_pair_test": FLOPS_PER_PAIR_TEST, "traffic": None,
+                            "flops_per_pair_test": FLOPS_PER_PAIR_TEST,
+                            "traffic": committed_dram_traffic("contacts_fused_configs4")[0] if ctx.world == 1 else None,
+                            "traffic_source": committed_dram_traffic("contacts_fused_configs4")[1] if ctx.world == 1 else None,
                             "note": "pair tests = mobile atoms x receptor atoms of the swept leaves + intra-mobile pairs"}}
         out.update(spread(ms))
         if cpu:
