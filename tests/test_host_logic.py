@@ -367,3 +367,48 @@ def test_results_writer_round_trip(tmp_path):
         assert np.abs(back.xyz - lig._expressed_coordinates).max() < 1e-6
         assert np.array_equal(back.bonds, lig.mol.bonds) and back.sybyl == lig.mol.sybyl
     assert not [f for f in os.listdir(os.path.join(cfg.output.path, "check7")) if f.endswith((".mol2", ".txt"))]
+
+
+def test_coordination_plugin_site_tables():
+    """The Coordination plugin's host prep (no GPU): key precedence atom_types > atom_elements > atom_names
+    (gaudi/objectives/coordination.py:244-252), residue filters ('*' or a position), the reference's
+    defaults and its constructor checks."""
+    from types import SimpleNamespace
+    import golden_util as G
+    from gaudi_b200 import molio
+    from gaudi_b200.objectives import coordination as CO
+    mol = G.load("4c3w_mol2")
+    adj = mol.adjacency()
+    nbs = [[] for _ in range(mol.n_atoms)]
+    for a, b in mol.bonds:
+        nbs[int(a)].append(int(b)); nbs[int(b)].append(int(a))
+    system = SimpleNamespace(
+        xyz=mol.xyz.astype(np.float64), element=list(mol.element), name=list(mol.name),
+        idatm=[molio.idatm_type(mol, i, adj) for i in range(mol.n_atoms)], molecule=["Molecule"] * mol.n_atoms,
+        resseq=[int(r) for r in mol.resseq], neighbours=nbs, mobile_row=-np.ones(mol.n_atoms, np.int32),
+        locate=lambda spec: int(np.flatnonzero(mol.serial == int(spec[1]))[0]))
+    o = CO.enable(probe="Molecule/1005", residues=["Molecule/*"], atom_elements=["C", "N", "O", "S"],
+                  geometry="octahedron", weight=-1.0, name="site")
+    s = o.site(system)
+    assert s["metal"] == int(np.flatnonzero(mol.serial == 1005)[0]) and s["template"].shape == (7, 3)
+    assert (s["radius"], s["distance"], s["min_atoms"], s["prevent_intruders"]) == (3.0, 0.0, 1, True)
+    want = np.array([e.upper() in ("C", "N", "O", "S") for e in mol.element])
+    assert np.array_equal(s["candidate"].astype(bool), want) and not s["candidate"][s["metal"]]
+    assert s["geometry"][int(np.flatnonzero(mol.serial == 408)[0])] == 3          # carboxylate O: planar
+    assert abs(s["bond_radius"][s["metal"]] - 1.33) < 1e-12                       # vanadium
+    # one residue only; atom_types wins over atom_elements, which wins over atom_names
+    o = CO.enable(probe=["Molecule", 1005], residues=[["Molecule", 52]], atom_types=["O2-"], atom_elements=["N"],
+                  atom_names=["CA"], weight=-1.0, name="site")
+    s = o.site(system)
+    picked = np.flatnonzero(s["candidate"])
+    assert len(picked) and all(int(mol.resseq[i]) == 52 and system.idatm[i] == "O2-" for i in picked)
+    o = CO.enable(probe="Molecule/1005", residues=["Molecule/130"], atom_names=["O2", "N2"], weight=-1.0, name="site")
+    picked = np.flatnonzero(o.site(system)["candidate"])
+    assert sorted(mol.name[i] for i in picked) == ["N2", "O2"]
+    with pytest.raises(ValueError):
+        CO.enable(probe="Molecule/1005", residues=["Molecule/*"], weight=-1.0, name="site")      # no atom filter
+    with pytest.raises(ValueError):
+        CO.enable(probe="Molecule/1005", residues=["Molecule/*"], atom_elements=["O"], bogus=1, name="site")
+    assert sorted(CO.GEOMETRIES) == sorted(["cube", "hexagonal bipyramid", "linear", "octahedron", "pentagonal bipyramid",
+                                            "square planar", "square pyramid", "tetrahedral", "trigonal planar",
+                                            "trigonal bipyramid", "trigonal prism"])
