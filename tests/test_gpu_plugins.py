@@ -161,6 +161,50 @@ def test_rotamers_flexible_side_chains(cuda):
     tiled.close()
 
 
+def test_many_flexible_side_chains(cuda):
+    """36 flexible side chains: more than the 32 bodies the candidate expansion keeps masks for, so the
+    non-seed slots fall back to plain runs of 32 (gmm_set_receptor); fused == tiled bit for bit in both
+    the CTA-per-individual and the warp-per-individual regime, and the oracle agrees."""
+    import dataclasses
+    from gaudi_b200 import base
+    from gaudi_b200.engine import Engine
+    rng = np.random.default_rng(12)
+    prot = G.load("5er1_protein_mol2")
+    lig = G.load("5er1_ligand_mol2")
+    d = np.linalg.norm(prot.xyz[:, None, :] - lig.xyz[None, ::4, :], axis=2).min(axis=1)
+    near = []
+    for a in np.argsort(d):
+        r, nm = int(prot.resseq[a]), prot.resname[a][:3].upper()
+        if nm not in ("ALA", "GLY", "PRO") and r not in near:
+            near.append(r)
+        if len(near) == 36:
+            break
+    library = {nm: rng.uniform(-180, 180, size=(int(rng.integers(3, 9)), 4)).tolist()
+               for nm in set(prot.resname[a][:3].upper() for a in range(prot.n_atoms))}
+    cfg = job(40, 0, rotamers=([("Protein", str(r)) for r in near], library))
+    random.seed(5)
+    pop = [base.MolecularIndividual(cfg) for _ in range(40)]
+    env = base.Environment(cfg)
+    cfg._environment = env
+    scores = env.evaluate_population(pop)
+    batch = env.batch
+    eng = batch.engines[0][0]
+    assert batch.n_rot_res == 36 and eng.mobile.n_atoms - lig.n_atoms > 32 * 8
+    for ind, got in list(zip(pop, scores))[::8]:
+        res, _ = oracle_scores(batch, ind)
+        assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash), (got, res.clash)
+        assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro), (got, res.hydro)
+    tiled = Engine(eng.mobile, eng.receptor, dataclasses.replace(eng.params, tiled=True), device=0)
+    reps = -(-2700 // 40)
+    T, X, R = (np.tile(v, (reps, 1))[:2700] for v in batch.pack(pop))
+    T = T + rng.uniform(-20, 20, size=T.shape)
+    for n in (2700, 40):
+        s1, c1, x1 = eng.evaluate(T[:n], X[:n], R[:n], want_xyz=True)
+        s2, c2 = tiled.contacts(x1)
+        assert cuda.equal(s1, s2) and cuda.equal(c1, c2), n
+    tiled.close()
+
+
 def test_tensor_ga_configs0(cuda):
     """The array-population loop on the same job: fitness of the evolved population equals the
     oracle's for the same alleles, and a 2,000-individual population runs generations in a
