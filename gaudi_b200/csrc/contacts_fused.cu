@@ -207,8 +207,11 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
 // exclusion lookups are compiled out.
 template <int S, bool CULL, bool PLAIN>
 // (one-warp CTAs: 28 resident instead of 32, i.e. 72 registers instead of 64 — 2 % faster; shared
-// memory allows 31 on configs[2] anyway; 80 registers / 25 CTAs is no better than 64 / 32)
-__global__ void __launch_bounds__(fused_warps(S, PLAIN) * 32, fused_warps(S, PLAIN) == 1 ? 28 : 8)
+// memory allows 31 on configs[2] anyway; 80 registers / 25 CTAs is no better than 64 / 32.  The
+// four-warp variants with flexible side chains are bound by shared memory to 6-7 CTAs per SM, so they
+// get 72 registers as well (7 CTAs): no spills, configs[4] 4 % faster; 80 registers / 6 CTAs gives 1 % more
+// on configs[4] but would cost the mid-sized jobs a CTA)
+__global__ void __launch_bounds__(fused_warps(S, PLAIN) * 32, fused_warps(S, PLAIN) == 1 ? 28 : ((S == 1 && !PLAIN) ? 7 : 8))
 contacts_fused_kernel(const FusedArgs f) {
     const SweepArgs& a = f.s;
     constexpr int IPC = fused_warps(S, PLAIN) / S;            // individuals per CTA
