@@ -771,7 +771,7 @@ int launch_contacts_fused(gmm_ctx* c, int P, const float* xyz, double* scores, i
     const size_t queues = kFusedQueues;
     const size_t limit = kFusedSmemLimit;
     // warp-per-individual from this population on; below it a CTA per individual fills the GPU better
-    constexpr int kTeamSwitch = 148 * 18;       // measured: tools/latency_small_pop.py
+    constexpr int kTeamSwitch = 148 * 7;        // measured (tools/latency_small_pop.py): 900 individuals 0.062 ms as teams, 0.067 as warps; 1,200: 0.075 / 0.071
     int S = (P >= kTeamSwitch) ? 1 : 4;
     if (S == 1 && 4 * ind + queues > limit) S = 4;
     if (ind + queues > limit) return GMM_OK;    // not handled
