@@ -15,8 +15,9 @@
 //               receptor atoms whose min d^2 lands within a margin of radius^2 get their zone
 //               membership re-decided with exact differences (rare), so zone bits are identical
 //               to the direct-difference definition.  Candidates (atoms that can have a contact
-//               at all) are expanded against the mobile atoms with exact differences and the
-//               surviving pairs scored with all lanes busy (score_pair), as in contacts.cu;
+//               at all: in the zone and within contact reach of a seed, or flagged at set-up as within
+//               reach of a flexible side chain's range of motion) are expanded against the mobile atoms
+//               and the surviving pairs scored with all lanes busy (score_pair), as in contacts.cu;
 //   3  static   static-static pairs are stored as per-leaf edge lists of 16-byte records (partner,
 //               kind, precomputed value); leaves with a non-empty zone word walk their edges with
 //               coalesced 128-bit loads and test both zone bits in shared memory;
@@ -203,8 +204,8 @@ __device__ __forceinline__ void fused_drain_candidates(const SweepArgs& a, uint3
 // parameter rather than a run-time flag: the kernel is sensitive to its instruction footprint
 // and each variant carries only its own code.  PLAIN: the common docking job — every mobile atom is a
 // zone seed (a ligand, no flexible side chains), the receptor holds no seeds and no atom bonded to
-// the mobile set: the mobile-zone bits, the always-in-zone words, the non-seed sweep and the
-// exclusion lookups are compiled out.
+// the mobile set: the mobile-zone bits, the always-in-zone words, the side-chain ("body") masks of
+// the candidate expansion and the exclusion lookups are compiled out.
 template <int S, bool CULL, bool PLAIN>
 // (one-warp CTAs: 28 resident instead of 32, i.e. 72 registers instead of 64 — 2 % faster; shared
 // memory allows 31 on configs[2] anyway; 80 registers / 25 CTAs is no better than 64 / 32.  The
