@@ -364,9 +364,13 @@ class BatchEvaluator(object):
                 ea, eb = elements[locate(a)], elements[locate(b)]
                 return molio.BOND_RADIUS.get(ea, 0.8) + molio.BOND_RADIUS.get(eb, 0.8)
 
+            def mass(a):
+                return molio.ATOMIC_MASS.get(elements[locate(a)], 12.011)
+
             terms = []
             for col, (i, o) in enumerate(self.geometry):
-                for t in o.terms(resolve, covalent):
+                kw = {"mass": mass} if getattr(o, "center_of_mass", False) else {}
+                for t in o.terms(resolve, covalent, **kw):
                     terms.append(dict(t, obj=col))
             self.engines[0][0].set_geometry(terms, len(self.geometry))
         # ---- Coordination objectives: whole-job atom tables on the first context -------------

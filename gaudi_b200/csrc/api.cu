@@ -822,7 +822,7 @@ int gmm_set_geometry(gmm_ctx* c, int n_terms, int n_obj, const int32_t* kind_h, 
     std::vector<GeoTerm> terms(n_terms);
     for (int k = 0; k < n_terms; ++k) {
         GeoTerm& t = terms[k];
-        REQUIRE(kind_h[k] >= 0 && kind_h[k] <= 2, GMM_EINVAL, "gmm_set_geometry: term %d has kind %d", k, kind_h[k]);
+        REQUIRE(kind_h[k] >= 0 && kind_h[k] <= 3, GMM_EINVAL, "gmm_set_geometry: term %d has kind %d", k, kind_h[k]);
         REQUIRE(obj_h[k] >= 0 && obj_h[k] < n_obj, GMM_EINVAL, "gmm_set_geometry: term %d objective out of range", k);
         t.kind = kind_h[k]; t.obj = obj_h[k];
         for (int j = 0; j < 4; ++j) {

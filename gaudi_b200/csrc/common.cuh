@@ -67,7 +67,7 @@ struct Params {
 
 // One term of a geometric restraint objective (geometry.cu)
 struct GeoTerm {
-    int kind;            // 0 distance, 1 angle (3 points), 2 dihedral (4 points)
+    int kind;            // 0 distance, 1 angle (3 points), 2 dihedral (4 points), 3 mass-weighted centre (threshold = mass)
     int obj;             // which output column this term averages into
     int atom[4];         // mobile atom index, or -1 = use point[k]
     double point[4][3];  // world-frame coordinates of static atoms / literal points

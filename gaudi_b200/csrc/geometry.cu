@@ -3,7 +3,8 @@
 // (gaudi/objectives/angle.py:86-96).  They read a handful of atoms per individual, so this is a
 // trivially HBM-bound kernel: one thread per (individual, objective), each term is a distance,
 // an angle or a dihedral between expressed mobile atoms and/or fixed points (static atoms or
-// literal coordinates), combined the way the reference combines them.
+// literal coordinates), combined the way the reference combines them; kind 3 terms accumulate a
+// mass-weighted centre (Distance with center_of_mass).
 #include "common.cuh"
 
 namespace gmm {
@@ -26,12 +27,21 @@ __global__ void geometry_kernel(int P, int M, const float* xyz, int n_terms, con
     const float* pose = xyz + (size_t)p * M * 3;
     double sum = 0.0;
     int n = 0;
+    double com[3] = {0.0, 0.0, 0.0}, mass = 0.0, com_target[3] = {0.0, 0.0, 0.0};   // kind 3
     for (int k = 0; k < n_terms; ++k) {
         const GeoTerm t = terms[k];
         if (t.obj != obj) continue;
         double a[3], b[3], c[3], d[3], v;
         geo_point(t, 0, pose, cx, cy, cz, a);
         geo_point(t, 1, pose, cx, cy, cz, b);
+        if (t.kind == 3) {
+            // distance.py:131-148 (center_of_mass): point 0 is a probe atom, `threshold` carries its mass,
+            // point 1 the target; the objective is the distance of the mass-weighted centre to the target
+            com[0] += t.threshold * a[0]; com[1] += t.threshold * a[1]; com[2] += t.threshold * a[2];
+            mass += t.threshold;
+            com_target[0] = b[0]; com_target[1] = b[1]; com_target[2] = b[2];
+            continue;
+        }
         if (t.kind == 0) {
             // distance.py:112-127: d - threshold; below `tolerance` -> -1000 * weight; mean of |.|
             const double dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
@@ -67,6 +77,11 @@ __global__ void geometry_kernel(int P, int M, const float* xyz, int n_terms, con
         }
         sum += v;
         ++n;
+    }
+    if (mass > 0.0) {
+        const double dx = com[0] / mass - com_target[0], dy = com[1] / mass - com_target[1], dz = com[2] / mass - com_target[2];
+        out[idx] = sqrt(dx * dx + dy * dy + dz * dz);
+        return;
     }
     out[idx] = n ? sum / n : 0.0;
 }

@@ -237,7 +237,8 @@ class Engine(object):
 
     # -- geometric restraint objectives (Distance / Angle) -----------------------------------
     def set_geometry(self, terms, n_obj):
-        """``terms``: dicts with ``kind`` (0 distance, 1 angle, 2 dihedral), ``obj`` (output column),
+        """``terms``: dicts with ``kind`` (0 distance, 1 angle, 2 dihedral, 3 mass-weighted centre: point 0 a
+        probe atom, ``threshold`` its mass, point 1 the target), ``obj`` (output column),
         ``points``: up to 4 entries, each a mobile atom index (int) or world coordinates (3 floats),
         ``threshold`` (float or ``'planar'`` for angles), optional ``tolerance``, ``weight``."""
         n = len(terms)

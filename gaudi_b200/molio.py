@@ -27,6 +27,14 @@ BOND_RADIUS = {
     "PT": 1.50, "PD": 1.50, "OS": 1.37, "MO": 1.47, "W": 1.37,
 }
 BOND_TOLERANCE = 0.4
+# chimera.Element.mass: standard atomic weights (Distance with center_of_mass); restated, unpinned
+ATOMIC_MASS = {
+    "H": 1.008, "C": 12.011, "N": 14.007, "O": 15.999, "S": 32.06, "P": 30.974, "F": 18.998, "CL": 35.45,
+    "BR": 79.904, "I": 126.904, "SE": 78.971, "B": 10.81, "SI": 28.085, "FE": 55.845, "ZN": 65.38, "MG": 24.305,
+    "CA": 40.078, "MN": 54.938, "CU": 63.546, "NI": 58.693, "CO": 58.933, "IR": 192.217, "V": 50.942,
+    "NA": 22.990, "K": 39.098, "RU": 101.07, "RH": 102.906, "PT": 195.084, "PD": 106.42, "OS": 190.23,
+    "MO": 95.95, "W": 183.84,
+}
 METALS = {"FE", "ZN", "MG", "CA", "MN", "CU", "NI", "CO", "IR", "V", "NA", "K", "RU", "RH", "PT",
           "PD", "OS", "MO", "W", "LI", "AL", "CD", "HG", "AU", "AG"}
 

@@ -32,18 +32,21 @@ class Distance(ObjectiveProvider):
 
     def __init__(self, threshold=None, tolerance=None, target=None, probes=None, center_of_mass=False, **kwargs):
         ObjectiveProvider.__init__(self, **kwargs)
-        if center_of_mass:
-            raise NotImplementedError("Distance(center_of_mass=True) is not on the B200 path")
+        self.center_of_mass = bool(center_of_mass)
         self.threshold = threshold if threshold == "covalent" else float(threshold)
         self.tolerance = None if tolerance is None else float(tolerance)
         self._probes = [_spec(p) for p in ([probes] if _is_atom(probes) else probes)]
         self._target = _spec(target)
 
-    def terms(self, resolve, covalent):
+    def terms(self, resolve, covalent, mass=None):
         """``resolve((mol, serial))`` -> mobile row (int) or world xyz of a static atom;
-        ``covalent(a, b)`` -> bond length."""
+        ``covalent(a, b)`` -> bond length; ``mass(atom)`` -> atomic mass (``center_of_mass``)."""
         target = resolve(self._target) if isinstance(self._target[0], str) else [float(v) for v in self._target]
         out = []
+        if self.center_of_mass:
+            # distance.py:131-148: distance of the target to the mass-weighted centre of the probes
+            return [{"kind": 3, "points": [resolve(p), target], "threshold": mass(p), "tolerance": None,
+                     "weight": self.weight} for p in self._probes]
         for p in self._probes:
             thr = covalent(p, self._target) if self.threshold == "covalent" else self.threshold
             out.append({"kind": 0, "points": [resolve(p), target], "threshold": thr, "tolerance": self.tolerance,

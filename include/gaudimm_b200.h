@@ -269,7 +269,10 @@ int gmm_niching_host(int N, const int64_t* ptr_h, const int32_t* idx_h, const in
  * (kind 2, points 0-3); a point is a mobile atom (atoms_h >= 0) or fixed world coordinates
  * (atoms_h == -1, points_h).  Terms with the same obj_h are averaged into one output column:
  * distance terms contribute |d - threshold| (or |-1000 * weight| when d - threshold < tolerance;
- * tolerance NaN = none), angle terms |threshold - angle| in degrees, or |sin(angle)| if planar. */
+ * tolerance NaN = none), angle terms |threshold - angle| in degrees, or |sin(angle)| if planar.
+ * Kind 3 (Distance with center_of_mass, distance.py:131-148): point 0 is a probe atom, threshold_h
+ * its mass, point 1 the target; a column made of kind-3 terms is the distance between the
+ * mass-weighted centre of its probes and the target. */
 int gmm_set_geometry(gmm_ctx* ctx, int n_terms, int n_obj, const int32_t* kind_h, const int32_t* obj_h,
                      const int32_t* atoms_h /*[n,4]*/, const double* points_h /*[n,4,3]*/,
                      const double* threshold_h, const double* tolerance_h, const double* weight_h,

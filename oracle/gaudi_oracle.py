@@ -371,6 +371,13 @@ def distance_objective(probe_xyz, target_xyz, threshold, tolerance=None, weight=
     return float(np.mean(np.absolute(distances)))
 
 
+def distance_center_of_mass(probe_xyz, masses, target_xyz):
+    """gaudi/objectives/distance.py:131-148 (``evaluate_center_of_mass``): distance between the target
+    and the mass-weighted centre of the probe atoms (no threshold, no tolerance)."""
+    centre = np.average(np.asarray(probe_xyz, dtype=np.float64).reshape(-1, 3), axis=0, weights=masses)
+    return float(np.sqrt(((centre - np.asarray(target_xyz, dtype=np.float64)) ** 2).sum()))
+
+
 def angle_objective(points, threshold):
     """gaudi/objectives/angle.py:86-96: three points -> ``chimera.angle`` (angle at the middle
     point), four -> ``chimera.dihedral``; ``'planar'`` -> |sin(angle)|, else |threshold - angle|."""

@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 import golden_util as G
+from gaudi_b200 import molio
 import oracle_adapter as OA
 from oracle import gaudi_oracle as O
 
@@ -32,6 +33,12 @@ def test_oracle_angle_cases():
     assert abs(O.dihedral(*[np.array(x) for x in q])) == pytest.approx(60.0)
 
 
+def test_distance_center_of_mass_oracle():
+    pts = np.array([[1.0, 0, 0], [3.0, 0, 0]])
+    assert O.distance_center_of_mass(pts, [1.0, 1.0], [2.0, 0, 0]) == 0.0
+    assert O.distance_center_of_mass(pts, [3.0, 1.0], [0.0, 0, 0]) == pytest.approx(1.5)
+
+
 @pytest.mark.gpu
 def test_geometry_kernel_matches_oracle(built_lib):
     import torch
@@ -56,8 +63,12 @@ def test_geometry_kernel_matches_oracle(built_lib):
         {"kind": 2, "obj": 3, "points": [0, 1, 2, 3], "threshold": 60.0},
         {"kind": 2, "obj": 4, "points": [list(fixed), 4, 5, 6], "threshold": "planar"},
         {"kind": 0, "obj": 5, "points": [9, 11], "threshold": 1.0},
+        # Distance(center_of_mass=True): mass-weighted centre of three probes against a fixed target
+        {"kind": 3, "obj": 6, "points": [2, list(fixed)], "threshold": 12.011},
+        {"kind": 3, "obj": 6, "points": [8, list(fixed)], "threshold": 15.999},
+        {"kind": 3, "obj": 6, "points": [13, list(fixed)], "threshold": 1.008},
     ]
-    eng.set_geometry(terms, 6)
+    eng.set_geometry(terms, 7)
     got = eng.geometry(xyz).cpu().numpy()
     world = xyz.cpu().numpy().astype(np.float64) + eng.centre
     for p in range(P):
@@ -69,6 +80,7 @@ def test_geometry_kernel_matches_oracle(built_lib):
             O.angle_objective([x[0], x[1], x[2], x[3]], 60.0),
             O.angle_objective([fixed, x[4], x[5], x[6]], "planar"),
             O.distance_objective(x[[9]], x[11], 1.0),
+            O.distance_center_of_mass(x[[2, 8, 13]], [12.011, 15.999, 1.008], fixed),
         ]
         # same fp32 coordinates on both sides: fp64 arithmetic agrees to rounding, except that
         # acos near 0/180 degrees amplifies it
@@ -106,6 +118,8 @@ def test_distance_and_angle_plugins(built_lib):
              "target": [float(v) for v in lig.xyz.mean(axis=0)], "threshold": 1.0, "tolerance": -0.5, "weight": -1.0},
             {"name": "Dihedral", "module": "gaudi_b200.objectives.angle",
              "probes": [["Ligand", s] for s in s_lig], "threshold": "planar", "weight": -1.0},
+            {"name": "Centre", "module": "gaudi_b200.objectives.distance", "probes": [["Ligand", s] for s in s_lig[:3]],
+             "target": ["Protein", s_prot], "threshold": 0.0, "center_of_mass": True, "weight": -1.0},
         ],
         "similarity": {"module": "gaudi_b200.similarity.rmsd", "args": [["Ligand"], 2.5], "kwargs": {}},
     })
@@ -119,6 +133,8 @@ def test_distance_and_angle_plugins(built_lib):
         assert got[2] == pytest.approx(O.distance_objective(x[rows[:2]], lig.xyz.mean(axis=0), 1.0, tolerance=-0.5,
                                                             weight=-1.0), abs=2e-3)
         assert got[3] == pytest.approx(O.angle_objective([x[r] for r in rows], "planar"), abs=2e-3)
+        masses = [molio.ATOMIC_MASS[lig.element[r].upper()] for r in rows[:3]]
+        assert got[4] == pytest.approx(O.distance_center_of_mass(x[rows[:3]], masses, prot.xyz[100]), abs=2e-3)
     assert len(batch.engines) == 1
 
 
