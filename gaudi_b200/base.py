@@ -334,6 +334,14 @@ class BatchEvaluator(object):
             mob, rec, _ = M.split_molecule(xyz, radius, flags, bonds, mobile_idx, params, rotatable=rotatable,
                                            origin_atom=origin, centre=centre,
                                            torsion_before_search=t_before_s)
+            if not params.same_residue:
+                res_id, seen = [], {}
+                for mi, name in enumerate(mol_names):
+                    mol = template._molecules[name].mol
+                    res_id += [seen.setdefault((mi, int(r), str(ch)), len(seen)) for r, ch in zip(mol.resseq, mol.chain)]
+                res_id = np.asarray(res_id)
+                static_idx = np.setdiff1d(np.arange(len(xyz)), mobile_idx)
+                M.exclude_same_residue(mob, rec, res_id[mobile_idx], res_id[static_idx])
             mob.tors_snap = np.asarray(snap, np.uint8)
             mob.tors_src = np.asarray(tors_src, np.int32)
             if rot is not None:

@@ -106,6 +106,7 @@ class ContactParams:
     weight: float = 1.0
     bond_separation: int = 4
     only_internal: bool = False
+    same_residue: bool = True   # DetectClash intraRes (contacts.py:142): False drops pairs inside one residue (host prep)
     cull: bool = True       # B200 path only: skip receptor tiles out of reach of a pose
     tiled: bool = False     # B200 path only: two-kernel tiled Contacts path instead of the fused one
     sequential_express: bool = False   # B200 path only: bond rotations one after another (reference order)
@@ -364,3 +365,37 @@ def empty_receptor(centre=(0.0, 0.0, 0.0)):
     return ReceptorModel(xyz=np.zeros((0, 3)), radius=np.zeros(0), flags=np.zeros(0, np.uint8),
                          bonds=np.zeros((0, 2), np.int32), rr_ptr=np.zeros(1, np.int32),
                          rr_idx=np.zeros(0, np.int32), centre=np.asarray(centre, np.float64))
+
+
+def exclude_same_residue(mob, rec, mobile_residue, static_residue):
+    """``Contacts(same_residue=False)`` = DetectClash ``intraRes=False`` (gaudi/objectives/contacts.py:142):
+    pairs of atoms of one residue are never reported.  Done entirely in the static model, in place:
+    mobile-mobile pairs through ``excl_mask``, static-static pairs dropped from the candidate CSR,
+    mobile-static pairs (a flexible side chain against its own backbone) added to ``ms_excl``.
+    ``mobile_residue`` / ``static_residue``: one integer per atom, unique per (molecule, residue)."""
+    mres = np.asarray(mobile_residue, dtype=np.int64)
+    sres = np.asarray(static_residue, dtype=np.int64)
+    m = mob.n_atoms
+    for a in range(m):
+        same = np.flatnonzero(mres == mres[a])
+        for b in same:
+            mob.excl_mask[a, int(b) >> 6] |= np.uint64(1) << np.uint64(int(b) & 63)
+    if len(rec.rr_idx):
+        rows = np.repeat(np.arange(rec.n_atoms), np.diff(rec.rr_ptr))
+        keep = sres[rows] != sres[rec.rr_idx]
+        counts = np.bincount(rows[keep], minlength=rec.n_atoms)
+        rec.rr_idx = rec.rr_idx[keep]
+        rec.rr_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    by_res = {}
+    for j, r in enumerate(sres):
+        by_res.setdefault(int(r), []).append(j)
+    old_ptr = rec.ms_excl_ptr if len(rec.ms_excl_ptr) == m + 1 else np.zeros(m + 1, dtype=np.int32)
+    ptr, idx = np.zeros(m + 1, dtype=np.int32), []
+    for a in range(m):
+        have = set(int(v) for v in rec.ms_excl_idx[old_ptr[a]:old_ptr[a + 1]])
+        have.update(by_res.get(int(mres[a]), ()))
+        idx.extend(sorted(have))
+        ptr[a + 1] = len(idx)
+    rec.ms_excl_ptr, rec.ms_excl_idx = ptr, np.asarray(idx, dtype=np.int32)
+    mob.residue, rec.residue = mres, sres          # (read by the tests' oracle adapter)
+    return mob, rec

@@ -28,8 +28,6 @@ class Contacts(ObjectiveProvider):
             raise ValueError("Contacts: radius must be >= 0 (contacts.py:90)")
         if int(bond_separation) < 2:
             raise ValueError("Contacts: bond_separation must be >= 2 (contacts.py:96)")
-        if not same_residue:
-            raise NotImplementedError("Contacts(same_residue=False) is not supported on the B200 path")
         self.which = which
         self.radius = float(radius)
         self.clash_threshold = float(clash_threshold)
@@ -37,7 +35,7 @@ class Contacts(ObjectiveProvider):
         self.cutoff = float(cutoff)
         self.hydrophobic_elements = tuple(hydrophobic_elements)
         self.bond_separation = int(bond_separation)
-        self.same_residue = True
+        self.same_residue = bool(same_residue)
         self.only_internal = bool(only_internal)
         self._probes = list(probes)
         self.threshold = hydrophobic_threshold if which == "hydrophobic" else clash_threshold
@@ -50,7 +48,7 @@ class Contacts(ObjectiveProvider):
     def model_key(self):
         """Objectives with the same key share one GPU context (both scores come out of one pass)."""
         return (tuple(self._probes), self.radius, self.clash_threshold, self.hydrophobic_threshold,
-                tuple(sorted(self.hydrophobic_elements)), self.bond_separation, self.only_internal)
+                tuple(sorted(self.hydrophobic_elements)), self.bond_separation, self.only_internal, self.same_residue)
 
     def penalty_key(self):
         """Cutoff penalty of evaluate_clashes (contacts.py:132-133); irrelevant for hydrophobic."""
@@ -62,7 +60,8 @@ class Contacts(ObjectiveProvider):
         return ContactParams(radius=self.radius, clash_threshold=self.clash_threshold,
                              hydrophobic_threshold=self.hydrophobic_threshold, cutoff=self.cutoff,
                              weight=self.weight if self.weight is not None else 1.0,
-                             bond_separation=self.bond_separation, only_internal=self.only_internal)
+                             bond_separation=self.bond_separation, only_internal=self.only_internal,
+                             same_residue=self.same_residue)
 
     def evaluate(self, individual):
         return self.environment.batch.score_of(individual, self)

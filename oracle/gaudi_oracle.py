@@ -217,7 +217,7 @@ def zone_atoms(coords, flags, radius, only_internal=False):
 
 
 def detect_clash(coords, radius, flags, atoms, graph, threshold, hbond_allowance=0.2,
-                 assumed_max_vdw=2.1, bond_separation=4):
+                 assumed_max_vdw=2.1, bond_separation=4, residue=None):
     """``DetectClash.detectClash(atoms, test=atoms, clashThreshold=threshold,
     hbondAllowance=0.2, assumedMaxVdw=2.1, bondSeparation=4, intraRes=True,
     interSubmodel=True)`` (contacts.py:140-146).
@@ -244,6 +244,8 @@ def detect_clash(coords, radius, flags, atoms, graph, threshold, hbond_allowance
         if d > max(ra, rb) + assumed_max_vdw - threshold:
             continue
         if b in graph.within(a, bond_separation):
+            continue
+        if residue is not None and residue[a] == residue[b]:      # intraRes=False (contacts.py:142, same_residue)
             continue
         clash = ra + rb - d
         if hbond_allowance:
@@ -272,8 +274,9 @@ def analyze_interactions(clashes, radius, flags, clash_threshold):
 def contacts(coords, radius, flags, graph, radius_zone=5.0, clash_threshold=0.6,
              hydrophobic_threshold=-0.4, cutoff=0.0, weight=1.0, bond_separation=4,
              only_internal=False, hbond_allowance=0.2, assumed_max_vdw=2.1,
-             return_pairs=False):
-    """Both Contacts scores of one expressed individual.
+             return_pairs=False, residue=None):
+    """Both Contacts scores of one expressed individual (``residue``: per-atom residue ids when
+    ``same_residue`` is False, contacts.py:142 ``intraRes``).
 
     ``coords/radius/flags`` cover every atom of every Molecule gene (mobile first, then
     static, by the convention of the tests).  Returns ``(clashes, hydrophobic)`` exactly
@@ -283,14 +286,14 @@ def contacts(coords, radius, flags, graph, radius_zone=5.0, clash_threshold=0.6,
     atoms = zone_atoms(coords, flags, radius_zone, only_internal)
     # which == 'clashes': threshold = clash_threshold (contacts.py:120-121)
     found_c = detect_clash(coords, radius, flags, atoms, graph, clash_threshold,
-                           hbond_allowance, assumed_max_vdw, bond_separation)
+                           hbond_allowance, assumed_max_vdw, bond_separation, residue)
     _, neg = analyze_interactions(found_c, radius, flags, clash_threshold)
     clashscore = 2.0 * sum(abs(v) for (_, _, _, v) in neg)
     if cutoff and clashscore > cutoff:
         clashscore = -1000 * weight
     # which == 'hydrophobic': threshold = hydrophobic_threshold (contacts.py:116-118)
     found_h = detect_clash(coords, radius, flags, atoms, graph, hydrophobic_threshold,
-                           hbond_allowance, assumed_max_vdw, bond_separation)
+                           hbond_allowance, assumed_max_vdw, bond_separation, residue)
     pos, _ = analyze_interactions(found_h, radius, flags, clash_threshold)
     hydro = 2.0 * sum(v for (_, _, _, v) in pos)
     if return_pairs:

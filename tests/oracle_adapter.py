@@ -74,7 +74,8 @@ def contacts(mob, rec, params, xyz_mobile, with_slack=True):
     clash, hydro, neg, pos = O.contacts(
         coords, radius, flags, graph, params.radius, params.clash_threshold,
         params.hydrophobic_threshold, 0.0, params.weight, params.bond_separation,
-        params.only_internal, params.hbond_allowance, params.assumed_max_vdw, return_pairs=True)
+        params.only_internal, params.hbond_allowance, params.assumed_max_vdw, return_pairs=True,
+        residue=(np.concatenate([mob.residue, rec.residue]) if not getattr(params, "same_residue", True) else None))
     res = SimpleNamespace(clash_raw=clash, hydro=hydro, neg=neg, pos=pos, n_clash=len(neg), n_hydro=len(pos),
                           clash_slack=0.0, hydro_slack=0.0, borderline=False)
     res.clash = clash

@@ -161,6 +161,56 @@ def test_rotamers_flexible_side_chains(cuda):
     tiled.close()
 
 
+def test_contacts_without_same_residue_pairs(cuda):
+    """Contacts(same_residue=False) = DetectClash intraRes=False (gaudi/objectives/contacts.py:142): pairs
+    inside one residue — the whole ligand, a flexible side chain against its own backbone, static
+    neighbours of one residue — are not reported.  Oracle, fused and tiled agree, and the scores differ
+    from the default."""
+    import dataclasses
+    from gaudi_b200 import base
+    from gaudi_b200.engine import Engine
+    rng = np.random.default_rng(21)
+    prot = G.load("5er1_protein_mol2")
+    lig = G.load("5er1_ligand_mol2")
+    d = np.linalg.norm(prot.xyz[:, None, :] - lig.xyz[None, ::4, :], axis=2).min(axis=1)
+    near = []
+    for a in np.argsort(d):
+        r, nm = int(prot.resseq[a]), prot.resname[a][:3].upper()
+        if nm not in ("ALA", "GLY", "PRO") and r not in near:
+            near.append(r)
+        if len(near) == 4:
+            break
+    library = {nm: rng.uniform(-180, 180, size=(5, 4)).tolist()
+               for nm in set(prot.resname[a][:3].upper() for a in range(prot.n_atoms))}
+    results = {}
+    for same in (True, False):
+        cfg = job(24, 0, rotamers=([("Protein", str(r)) for r in near], library))
+        for o in cfg.objectives:
+            o["same_residue"] = same
+        random.seed(9)
+        pop = [base.MolecularIndividual(cfg) for _ in range(24)]
+        env = base.Environment(cfg)
+        cfg._environment = env
+        scores = np.array(env.evaluate_population(pop))
+        batch = env.batch
+        eng = batch.engines[0][0]
+        assert eng.params.same_residue is same
+        for ind, got in list(zip(pop, scores))[::4]:
+            res, _ = oracle_scores(batch, ind)
+            assert abs(got[0] - res.clash) <= 6e-4 + res.clash_slack + 1e-4 * abs(res.clash), (same, got, res.clash)
+            assert abs(got[1] - res.hydro) <= 6e-4 + res.hydro_slack + 1e-4 * abs(res.hydro), (same, got, res.hydro)
+        tiled = Engine(eng.mobile, eng.receptor, dataclasses.replace(eng.params, tiled=True), device=0)
+        T, X, R = batch.pack(pop)
+        s1, c1, x1 = eng.evaluate(T, X, R, want_xyz=True)
+        s2, c2 = tiled.contacts(x1)
+        assert cuda.equal(s1, s2) and cuda.equal(c1, c2)
+        tiled.close()
+        results[same] = scores
+    assert not np.allclose(results[True], results[False])
+    # the ligand is one residue: without same-residue pairs its internal contacts are gone
+    assert (np.abs(results[False][:, 1]) <= np.abs(results[True][:, 1]) + 1e-6).all()
+
+
 def test_many_flexible_side_chains(cuda):
     """36 flexible side chains: more than the 32 bodies the candidate expansion keeps masks for, so the
     non-seed slots fall back to plain runs of 32 (gmm_set_receptor); fused == tiled bit for bit in both
