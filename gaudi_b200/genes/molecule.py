@@ -82,12 +82,14 @@ class Molecule(GeneProvider):
         else:
             handle, fullname = tempfile.mkstemp(prefix="gaudi", suffix=".{}".format(filetype))
             os.close(handle)
-        if combined_with:
-            raise NotImplementedError("Molecule.write(combined_with=...) is not available on the B200 path")
+        mol, xyz = self.mol, self.xyz()
+        if combined_with:          # the other Molecule genes' atoms in the same file, renumbered (:252-254)
+            mol = molio.combine([(self.mol, xyz)] + [(g.mol, g.xyz()) for g in combined_with])
+            xyz = mol.xyz
         if filetype == "mol2":
-            molio.write_mol2(self.mol, fullname, xyz=self.xyz(), title=self.name)
+            molio.write_mol2(mol, fullname, xyz=xyz, title=self.name)
         elif filetype == "pdb":
-            molio.write_pdb(self.mol, fullname, xyz=self.xyz())
+            molio.write_pdb(mol, fullname, xyz=xyz)
         else:
             raise ValueError("Filetype {} not recognized. Try with mol2 or pdb".format(filetype))
         return fullname

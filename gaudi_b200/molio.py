@@ -212,6 +212,29 @@ def write_mol2(mol, path, xyz=None, title="gaudi_b200"):
     return path
 
 
+def combine(parts):
+    """One ``Mol`` out of several ``(mol, xyz)`` parts, atoms renumbered 1..N in order, bonds carried
+    over: what Chimera's ``writeMol2(..., multimodelHandling='combined')`` / ``pdbWrite`` of a list of
+    molecules put into one file (gaudi/genes/molecule.py:252-258)."""
+    name, resname, resseq, chain, element, xyz, hetero, sybyl, bonds = [], [], [], [], [], [], [], [], []
+    off = 0
+    for mol, x in parts:
+        x = mol.xyz if x is None else np.asarray(x, np.float64)
+        name += list(mol.name); resname += list(mol.resname); resseq += [int(r) for r in mol.resseq]
+        chain += list(mol.chain); element += list(mol.element); xyz.append(x)
+        hetero += list(mol.hetero) if getattr(mol, "hetero", None) is not None else [False] * mol.n_atoms
+        sybyl += list(mol.sybyl) if getattr(mol, "sybyl", None) else [e.title() for e in mol.element]
+        b = getattr(mol, "bonds", None)
+        if b is not None and len(b):
+            bonds.append(np.asarray(b, np.int64).reshape(-1, 2) + off)
+        off += mol.n_atoms
+    out = Mol(name, resname, np.asarray(resseq), chain, element, np.concatenate(xyz), np.arange(1, off + 1),
+              hetero=np.asarray(hetero, bool))
+    out.sybyl = sybyl
+    out.bonds = (np.concatenate(bonds) if bonds else np.zeros((0, 2), np.int64)).astype(np.int32)
+    return out
+
+
 def write_pdb(mol, path, xyz=None):
     """Minimal PDB (ATOM/HETATM records) of ``mol`` with coordinates ``xyz``."""
     xyz = mol.xyz if xyz is None else np.asarray(xyz, np.float64)

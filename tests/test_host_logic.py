@@ -412,3 +412,24 @@ def test_coordination_plugin_site_tables():
     assert sorted(CO.GEOMETRIES) == sorted(["cube", "hexagonal bipyramid", "linear", "octahedron", "pentagonal bipyramid",
                                             "square planar", "square pyramid", "tetrahedral", "trigonal planar",
                                             "trigonal bipyramid", "trigonal prism"])
+
+
+def test_molecule_write_combined(tmp_path):
+    """Molecule.write(combined_with=[...]) (gaudi/genes/molecule.py:252-258): every molecule's atoms in
+    one file, renumbered, bonds carried over; mol2 and pdb."""
+    import golden_util as G
+    from gaudi_b200 import molio
+    lig, prot = G.load("5er1_ligand_mol2"), G.load("5er1_protein_mol2")
+    moved = lig.xyz + np.array([1.0, -2.0, 0.5])
+    both = molio.combine([(lig, moved), (prot, None)])
+    assert both.n_atoms == lig.n_atoms + prot.n_atoms and len(both.bonds) == len(lig.bonds) + len(prot.bonds)
+    assert list(both.serial) == list(range(1, both.n_atoms + 1))
+    path = molio.write_mol2(both, str(tmp_path / "both.mol2"))
+    back = molio.read_mol2(path)
+    assert back.n_atoms == both.n_atoms and len(back.bonds) == len(both.bonds)
+    assert np.abs(back.xyz[:lig.n_atoms] - moved).max() < 1e-5
+    assert np.abs(back.xyz[lig.n_atoms:] - prot.xyz).max() < 1e-5
+    # the first protein bond joins the same two protein atoms as before, shifted by the ligand's atoms
+    assert tuple(int(v) for v in back.bonds[len(lig.bonds)]) == tuple(int(v) + lig.n_atoms for v in prot.bonds[0])
+    pdb = molio.read_pdb(molio.write_pdb(both, str(tmp_path / "both.pdb")))
+    assert pdb.n_atoms == both.n_atoms and np.abs(pdb.xyz[:lig.n_atoms] - moved).max() < 2e-3
